@@ -1,0 +1,165 @@
+/* libb200vit.so -- C ABI of the B200-native ViT-B/16 training-step kernels.
+ *
+ * The reference (AvalonEnjoyer/pytorch-ViT-paper-replication) has no FFI: its hot path is Python calling
+ * torch.nn modules. The drop-in boundary is therefore the Python module API (b200vit.models.vit.ViT etc.),
+ * and THIS header is what that Python layer binds through ctypes. Every entry point below names the
+ * reference call site (file:line under the reference repo) whose arithmetic it replaces.
+ *
+ * Conventions
+ *   - All pointers are DEVICE pointers unless a parameter says "host". Nothing here allocates or frees
+ *     memory the caller can see; outputs are written into caller-provided buffers.
+ *   - `stream` is a cudaStream_t passed as void*. Calls are asynchronous on that stream.
+ *   - Return value: 0 = ok, < 0 = argument / shape / alignment error, > 0 = cudaError_t.
+ *     b200vit_last_error() returns a thread-local message for the last non-zero return.
+ *   - "bf16" buffers are __nv_bfloat16 (passed as void*); "f32" are float.
+ *   - Dropout masks are never stored: a mask is a pure function of (seed, offset, element index), so the
+ *     forward and backward entry points of one dropout site must be given the same (p, seed, offset).
+ *   - There is no CPU implementation behind any of these symbols.
+ */
+#ifndef B200VIT_H
+#define B200VIT_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ABI version of this header (bumped on any signature change). */
+int b200vit_abi_version(void);
+
+/* Message describing the last error raised on the calling thread. */
+const char* b200vit_last_error(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Dense contractions on the tcgen05 tensor cores (bf16 operands, fp32 accumulation in tensor memory).
+ *
+ *   op 0 (NT): C[M,N] = A[M,K] . B[N,K]^T    forward of nn.Linear / the patch Conv2d-as-GEMM / MHA in- and
+ *                                            out-projection  (models/vit.py:28-31, 86-90, 119, 123)
+ *   op 1 (NN): C[M,N] = A[M,K] . B[K,N]      input gradients of the same layers (autograd of the above)
+ *   op 2 (TN): C[M,N] = A[K,M]^T . B[K,N]    weight gradients (contraction over the B*T token rows)
+ *
+ * A, B: bf16 row-major with leading dimensions lda, ldb (elements, multiples of 8; 16-byte aligned bases).
+ * epilogue:
+ *   0 BF16       C bf16 = acc (+ bias[n] if bias != NULL)
+ *   1 BIAS_GELU  C bf16 = a = acc + bias (skipped if C == NULL) ; C2 bf16 = dropout(gelu_erf(a))
+ *                                                              (models/vit.py:119-122)
+ *   2 BIAS_RES   C f32 = dropout(acc + bias) + aux_f32[m,n]  (aux NULL -> no residual)
+ *                                                              (models/vit.py:123-125 and the residual adds :167-168)
+ *   3 DGELU      C bf16 = acc * dropout_mask * gelu_erf'(aux_bf16[m,n])   (backward of GELU + Dropout)
+ *   4 ACCUM      C f32 += acc, atomically; the only epilogue that allows split_k > 1 (weight gradients)
+ *   5 F32        C f32 = acc (+ bias)
+ *   6 PATCH      C f32[m + m/row_period + 1, n] = dropout(acc + bias[n] + aux_f32[(m % row_period) + 1, n]):
+ *                patch rows of the embedded sequence, position embedding added, class-token row skipped
+ *                                                              (models/vit.py:53-66)
+ * Dropout uses element index (output_row * N + n).
+ */
+int b200vit_gemm(int op, int epilogue, int M, int N, int K,
+                 const void* A, long long lda, const void* B, long long ldb,
+                 void* C, long long ldc, void* C2, long long ldc2,
+                 const float* bias, const void* aux, long long ldaux,
+                 float dropout_p, unsigned long long seed, unsigned long long offset,
+                 int row_period, int split_k, void* stream);
+
+/* fp32 -> bf16 copy (bf16 weight shadows of the fp32 master parameters). */
+int b200vit_cast_f32_to_bf16(const float* src, void* dst_bf16, long long n, void* stream);
+
+/* Patch extraction for a stride == kernel convolution: image f32 [B,C,H,W] -> patches bf16 [B*(H/P)*(W/P), C*P*P]
+ * with column order (c, i, j) = flattened Conv2d weight order.  Replaces the data movement of
+ * nn.Conv2d(k=s=P) + Flatten(2,3) + permute(0,2,1)  (models/vit.py:28-34, 53-56). */
+int b200vit_im2col_patches(const float* image, void* patches_bf16, int batch, int channels, int height, int width,
+                           int patch, void* stream);
+
+/* x[b, 0, :] = dropout(class_token + pos[0]) for every b; x is the f32 [B, T, D] embedded sequence whose patch
+ * rows the PATCH GEMM epilogue writes.  Replaces expand + torch.cat + add + Dropout for the class row
+ * (models/vit.py:50, 59, 63, 66). */
+int b200vit_class_token_rows(const float* class_token, const float* pos, float* x, int batch, int tokens, int dim,
+                             float dropout_p, unsigned long long seed, unsigned long long offset, void* stream);
+
+/* Gradients of class_token [D], position_embedding [T, D] and the conv bias [D] (g_bias may be NULL) from the
+ * gradient gx f32 [B, T, D] of the embedded sequence (autograd of models/vit.py:50-66). Outputs are overwritten. */
+int b200vit_embed_param_grads(const float* gx, float* g_cls, float* g_pos, float* g_bias, int batch, int tokens,
+                              int dim, float dropout_p, unsigned long long seed, unsigned long long offset,
+                              void* stream);
+
+/* gy bf16 [B*(T-1), D] = dropout_mask * gx[:, 1:, :]: the token-gradient operand of the conv weight gradient. */
+int b200vit_patch_grad_rows(const float* gx, void* gy_bf16, int batch, int tokens, int dim, float dropout_p,
+                            unsigned long long seed, unsigned long long offset, void* stream);
+
+/* nn.LayerNorm(dim) forward (models/vit.py:83, 115, 216; eps 1e-5, biased variance).
+ * x: f32 rows of `dim` values, `row_stride` elements apart (row_stride = T*dim normalises only class-token rows).
+ * Writes y_bf16 and/or y_f32 (dense [rows, dim]; either may be NULL) and the row statistics mean / rstd. */
+int b200vit_layernorm_fwd(const float* x, long long row_stride, const float* gamma, const float* beta,
+                          void* y_bf16, float* y_f32, float* mean, float* rstd, long long rows, int dim, float eps,
+                          void* stream);
+
+/* nn.LayerNorm backward fused with the residual-gradient add.
+ *   dy (exactly one of dy_bf16 / dy_f32, dense [rows, dim]) is the gradient w.r.t. the LayerNorm output.
+ *   gout[row*gout_stride + :] = (gin ? gin[same index] : 0) + dLN/dx ; dgamma, dbeta f32 [dim] are overwritten.
+ *   gout_bf16 (optional, dense): bf16(dropout_mask * gout); dbias_next (optional) = its column sums.
+ * Autograd counterpart of models/vit.py:93, 129, 232 plus the `+ x` of :167-168. dim <= 1024. */
+int b200vit_layernorm_bwd(const void* dy_bf16, const float* dy_f32, const float* x, long long row_stride,
+                          const float* mean, const float* rstd, const float* gamma, const float* gin, float* gout,
+                          long long gout_stride, void* gout_bf16, float* dgamma, float* dbeta, float* dbias_next,
+                          long long rows, int dim, float dropout_p, unsigned long long seed,
+                          unsigned long long offset, void* stream);
+
+/* out[n] = sum_m x[m, n] for a bf16 matrix: bias gradients of the Linear layers. `out` is overwritten. */
+int b200vit_colsum_bf16(const void* x_bf16, long long ld, float* out, long long rows, int cols, void* stream);
+
+/* out_bf16 = bf16(dropout_mask * g), colsum (optional) = column sums of out: turns the f32 residual-stream
+ * gradient into the operand of the fc2 backward GEMMs, undoing nn.Dropout of models/vit.py:125. */
+int b200vit_dropout_cast(const float* g, void* out_bf16, float* colsum, long long rows, int cols, float dropout_p,
+                         unsigned long long seed, unsigned long long offset, void* stream);
+
+/* Fused multi-head self-attention forward (the scaled_dot_product_attention inside nn.MultiheadAttention,
+ * models/vit.py:86-97; need_weights=False, no mask).
+ *   qkv bf16 [B, T, 3, H, 64] (the packed in-projection output), out bf16 [B, T, H*64], lse f32 [B, H, T]. */
+int b200vit_attention_fwd(const void* qkv_bf16, void* out_bf16, float* lse, int batch, int tokens, int heads,
+                          int head_dim, float scale, void* stream);
+
+/* Backward of the above. `delta` is SCRATCH f32 [B, H, T] provided by the caller; dqkv bf16 [B, T, 3, H, 64]. */
+int b200vit_attention_bwd(const void* qkv_bf16, const void* out_bf16, const void* dout_bf16, const float* lse,
+                          float* delta, void* dqkv_bf16, int batch, int tokens, int heads, int head_dim, float scale,
+                          void* stream);
+
+/* Classifier head on the normalised class-token rows: logits[B, C] = xn[B, D] . w[C, D]^T + b
+ * (nn.Linear(D, num_classes), models/vit.py:219-222, 235); fp32 on the master weights. */
+int b200vit_head_fwd(const float* xn, const float* w, const float* b, float* logits, int batch, int dim, int classes,
+                     void* stream);
+/* dxn / dw / db (each optional) from dlogits; outputs are overwritten. */
+int b200vit_head_bwd(const float* xn, const float* w, const float* dlogits, float* dxn, float* dw, float* db,
+                     int batch, int dim, int classes, void* stream);
+
+/* nn.CrossEntropyLoss() (mean) fused with its gradient and the accuracy counter:
+ *   *loss = mean_b(logsumexp(z_b) - z_b[y_b]) ; dlogits (optional) = (softmax(z) - onehot(y)) / B ;
+ *   *correct (optional) = #{b : argmax(z_b) == y_b}.
+ * Replaces loss_fn(y_pred, y) and the argmax(softmax(.)) == y count of going_modular/engine.py:53, 73-74, 121-125. */
+int b200vit_softmax_ce(const float* logits, const long long* labels, float* loss, float* dlogits, int* correct,
+                       int batch, int classes, void* stream);
+
+/* dst = src * (*scalar_dev): chain rule with the upstream scalar gradient of the loss. */
+int b200vit_scale_by_scalar(const float* src, const float* scalar_dev, float* dst, long long n, void* stream);
+
+/* Sum of squares over a list of f32 tensors in one launch (+ a tiny final reduction): the global gradient norm of
+ * torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0), going_modular/engine.py:63.
+ *   ptrs_dev / sizes_dev: device arrays of num_tensors pointers / element counts; max_size = largest count.
+ *   partials: SCRATCH f32 buffer with num_partials >= num_tensors * ceil(max_size / 8192) entries. */
+int b200vit_l2norm_sq(const void* const* ptrs_dev, const long long* sizes_dev, int num_tensors, long long max_size,
+                      float* partials, int num_partials, float* out_sumsq, void* stream);
+
+/* One fused optimizer step over all parameters: torch.optim.Adam as configured by the reference recipe
+ * (coupled L2 weight decay per param group; notebook optimizer cell, stepped at going_modular/engine.py:66),
+ * or AdamW when decoupled != 0.
+ *   table_dev: device array of num_tensors records {f32* p, const f32* g, f32* m, f32* v, bf16* shadow (or NULL),
+ *              long long n, int group, int pad}.
+ *   lrs / wds: HOST arrays with num_groups (<= 8) entries. step counts from 1.
+ *   If grad_sumsq != NULL and max_norm > 0 the clip coefficient min(1, max_norm / (sqrt(*grad_sumsq) * grad_scale
+ *   + 1e-6)) is applied on the fly (gradients in memory are not modified); grad_scale multiplies every gradient
+ *   first (1/world_size for summed data-parallel gradients). */
+int b200vit_adam_step(const void* table_dev, int num_tensors, long long max_size, const float* lrs_host,
+                      const float* wds_host, int num_groups, float beta1, float beta2, float eps, int step,
+                      int decoupled, const float* grad_sumsq, float max_norm, float grad_scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200VIT_H */

@@ -1,0 +1,110 @@
+"""ctypes binding of libb200vit.so (see include/b200vit.h).
+
+The library is the ONLY compute backend: if it is missing or a call fails, a RuntimeError is raised.
+There is no PyTorch / CPU fallback behind these functions.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+_LIB_PATH = Path(__file__).resolve().parent / "lib" / "libb200vit.so"
+ABI_VERSION = 1
+
+_p = C.c_void_p
+_i = C.c_int
+_ll = C.c_longlong
+_ull = C.c_ulonglong
+_f = C.c_float
+
+# name -> argtypes (return type is always int unless noted)
+_SIGNATURES = {
+    "b200vit_gemm": [_i, _i, _i, _i, _i, _p, _ll, _p, _ll, _p, _ll, _p, _ll, _p, _p, _ll, _f, _ull, _ull, _i, _i, _p],
+    "b200vit_cast_f32_to_bf16": [_p, _p, _ll, _p],
+    "b200vit_im2col_patches": [_p, _p, _i, _i, _i, _i, _i, _p],
+    "b200vit_class_token_rows": [_p, _p, _p, _i, _i, _i, _f, _ull, _ull, _p],
+    "b200vit_embed_param_grads": [_p, _p, _p, _p, _i, _i, _i, _f, _ull, _ull, _p],
+    "b200vit_patch_grad_rows": [_p, _p, _i, _i, _i, _f, _ull, _ull, _p],
+    "b200vit_layernorm_fwd": [_p, _ll, _p, _p, _p, _p, _p, _p, _ll, _i, _f, _p],
+    "b200vit_layernorm_bwd": [_p, _p, _p, _ll, _p, _p, _p, _p, _p, _ll, _p, _p, _p, _p, _ll, _i, _f, _ull, _ull, _p],
+    "b200vit_colsum_bf16": [_p, _ll, _p, _ll, _i, _p],
+    "b200vit_dropout_cast": [_p, _p, _p, _ll, _i, _f, _ull, _ull, _p],
+    "b200vit_attention_fwd": [_p, _p, _p, _i, _i, _i, _i, _f, _p],
+    "b200vit_attention_bwd": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _f, _p],
+    "b200vit_head_fwd": [_p, _p, _p, _p, _i, _i, _i, _p],
+    "b200vit_head_bwd": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _p],
+    "b200vit_softmax_ce": [_p, _p, _p, _p, _p, _i, _i, _p],
+    "b200vit_scale_by_scalar": [_p, _p, _p, _ll, _p],
+    "b200vit_l2norm_sq": [_p, _p, _i, _ll, _p, _i, _p, _p],
+    "b200vit_adam_step": [_p, _i, _ll, _p, _p, _i, _f, _f, _f, _i, _i, _p, _f, _f, _p],
+}
+
+# GEMM enums (include/b200vit.h)
+OP_NT, OP_NN, OP_TN = 0, 1, 2
+EPI_BF16, EPI_BIAS_GELU, EPI_BIAS_RES, EPI_DGELU, EPI_ACCUM, EPI_F32, EPI_PATCH = range(7)
+
+
+class AdamTensor(C.Structure):
+    """Record of b200vit_adam_step's tensor table (must match csrc/optim.cu)."""
+    _fields_ = [("p", _p), ("g", _p), ("m", _p), ("v", _p), ("shadow", _p), ("n", _ll), ("group", _i), ("pad", _i)]
+
+
+_lib = None
+_override = None  # a test double may be installed with set_library(); never done by product code
+
+
+def library_path() -> Path:
+    return Path(os.environ.get("B200VIT_LIB", str(_LIB_PATH)))
+
+
+def set_library(obj) -> None:
+    """Install an object exposing the C-ABI function names (used by tests/ to inject a CPU test double for
+    host-logic tests; product code never calls this)."""
+    global _override
+    _override = obj
+
+
+def lib():
+    """Load libb200vit.so (once) and return the ctypes handle; raise loudly if it is not there."""
+    global _lib
+    if _override is not None:
+        return _override
+    if _lib is None:
+        path = library_path()
+        if not path.exists():
+            raise RuntimeError(
+                f"libb200vit.so not found at {path}. Build it with "
+                f"`python pytorch-vit-paper-replication_b200/build.py` (or __graft_entry__.build()). "
+                f"b200vit has no CPU / PyTorch fallback."
+            )
+        handle = C.CDLL(str(path))
+        handle.b200vit_abi_version.restype = _i
+        handle.b200vit_abi_version.argtypes = []
+        handle.b200vit_last_error.restype = C.c_char_p
+        handle.b200vit_last_error.argtypes = []
+        got = handle.b200vit_abi_version()
+        if got != ABI_VERSION:
+            raise RuntimeError(f"libb200vit.so ABI version {got} != expected {ABI_VERSION}; rebuild the library")
+        for name, argtypes in _SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype = _i
+            fn.argtypes = argtypes
+        _lib = handle
+    return _lib
+
+
+def exported_symbols():
+    return ["b200vit_abi_version", "b200vit_last_error", *_SIGNATURES.keys()]
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = lib().b200vit_last_error()
+        if isinstance(msg, bytes):
+            msg = msg.decode(errors="replace")
+        raise RuntimeError(f"{what} failed (code {rc}): {msg}")
+
+
+def call(name: str, *args) -> None:
+    check(getattr(lib(), name)(*args), name)

@@ -1,0 +1,490 @@
+// tcgen05 / TMEM / TMA bf16 GEMM with fused epilogues for the ViT training step (sm_100a).
+//
+// One kernel template covers every dense contraction of the path:
+//   NT  C[M,N] = A[M,K]  . B[N,K]^T   forward Linear / Conv-as-GEMM  (reference models/vit.py:28,119,123
+//                                      and nn.MultiheadAttention in/out projections, vit.py:86)
+//   NN  C[M,N] = A[M,K]  . B[K,N]     input gradients  (what autograd derives for those Linears)
+//   TN  C[M,N] = A[K,M]^T. B[K,N]     weight gradients (contraction over the token dimension)
+// Operands are bf16 in global memory, accumulation is fp32 in tensor memory.
+//
+// Structure (persistent, warp specialised, one CTA per SM, 384 threads):
+//   warp 0      TMA producer: global -> 128B-swizzled smem ring (4 stages of A 128x64 + B 256x64)
+//   warp 1      MMA issuer: one thread issues tcgen05.mma 128x256x16, commits stages back to the ring
+//   warp 2      TMEM allocator (512 columns = two 128x256 fp32 accumulators, double buffered)
+//   warps 4-11  epilogue: tcgen05.ld accumulator -> registers -> fused math -> global
+// K-major operands are loaded with one [64 x rows] box; MN-major operands (the "N"/"T" sides above)
+// with 64x64 boxes, and the UMMA descriptors carry the major-ness, so no operand is ever transposed
+// in memory.
+#include "common.cuh"
+#include "ptx_sm100.cuh"
+
+#include <cudaTypedefs.h>
+#include <mutex>
+
+namespace b200vit {
+
+using namespace ptx;
+
+constexpr int BM = 128;
+constexpr int BN = 256;
+constexpr int BK = 64;
+constexpr int STAGES = 4;
+constexpr int UMMA_K = 16;
+constexpr int A_STAGE_BYTES = BM * BK * 2;   // 16 KB
+constexpr int B_STAGE_BYTES = BN * BK * 2;   // 32 KB
+constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+constexpr int NUM_EPI_WARPS = 8;
+constexpr int GEMM_THREADS = 128 + NUM_EPI_WARPS * 32;
+constexpr int TMEM_COLS = 512;
+constexpr int GEMM_SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+
+enum GemmOp { OP_NT = 0, OP_NN = 1, OP_TN = 2 };
+enum GemmEpi {
+    EPI_BF16 = 0,       // C bf16 = acc (+ bias[n])
+    EPI_BIAS_GELU = 1,  // C bf16 = a = acc + bias ; C2 bf16 = dropout(gelu(a))       (fc1, vit.py:119-122)
+    EPI_BIAS_RES = 2,   // C f32 = dropout(acc + bias) + aux_f32[m,n]                  (out-proj / fc2 + residual, vit.py:167-168)
+    EPI_DGELU = 3,      // C bf16 = acc * dropmask * gelu'(aux_bf16[m,n])              (backward of GELU+Dropout)
+    EPI_ACCUM = 4,      // C f32 += acc  (atomic; split-K weight gradients)
+    EPI_F32 = 5,        // C f32 = acc (+ bias[n])
+    EPI_PATCH = 6,      // C f32[m + m/P + 1, n] = dropout(acc + bias[n] + pos[m%P + 1, n])  (vit.py:53-66)
+    EPI_COUNT = 7
+};
+
+struct GemmParams {
+    int M, N, K;
+    int tiles_m, tiles_n, splits, kblocks;
+    void* C;  long long ldc;
+    void* C2; long long ldc2;
+    const float* bias;
+    const void* aux; long long ldaux;
+    DropoutParams drop;
+    int row_period;
+    int vec_ok;   // leading dimensions / N allow 16-byte vector access
+};
+
+// -------------------------------------------------------------------------------------------------
+// Epilogue: one thread owns one output row (TMEM lane) and 32 consecutive columns per call.
+// -------------------------------------------------------------------------------------------------
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int col0, float (&v)[32]) {
+    if (row >= p.M || col0 >= p.N) return;
+    const int nvalid = min(32, p.N - col0);
+    const bool full = p.vec_ok && nvalid == 32;
+
+    // ---- bias -------------------------------------------------------------------------------
+    if (EPI == EPI_BF16 || EPI == EPI_BIAS_GELU || EPI == EPI_BIAS_RES || EPI == EPI_F32 || EPI == EPI_PATCH) {
+        if (p.bias != nullptr) {
+            if (full) {
+                const float4* b4 = reinterpret_cast<const float4*>(p.bias + col0);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float4 b = __ldg(b4 + i);
+                    v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) if (i < nvalid) v[i] += __ldg(p.bias + col0 + i);
+            }
+        }
+    }
+
+    // Output row and the row used to index the dropout mask / aux tensor.
+    long long orow = row;
+    if (EPI == EPI_PATCH) orow = (long long)row + row / p.row_period + 1;
+
+    // ---- dropout multipliers (shared by several epilogues) ----------------------------------
+    auto apply_dropout = [&](float (&x)[32]) {
+        if (p.drop.p <= 0.f) return;
+        const unsigned long long e0 = (unsigned long long)orow * (unsigned long long)p.N + (unsigned long long)col0;
+        if ((p.N & 7) == 0) {
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                float m[8];
+                dropout_mult8(p.drop, (e0 >> 3) + b, m);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) x[8 * b + i] *= m[i];
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) x[i] *= dropout_mult1(p.drop, e0 + i);
+        }
+    };
+
+    auto store_bf16 = [&](void* base, long long ld, const float (&x)[32]) {
+        bf16* dst = reinterpret_cast<bf16*>(base) + orow * ld + col0;
+        if (full) {
+            uint4* d4 = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                uint4 o;
+                o.x = pack_bf16(x[8 * i], x[8 * i + 1]);
+                o.y = pack_bf16(x[8 * i + 2], x[8 * i + 3]);
+                o.z = pack_bf16(x[8 * i + 4], x[8 * i + 5]);
+                o.w = pack_bf16(x[8 * i + 6], x[8 * i + 7]);
+                d4[i] = o;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (i < nvalid) dst[i] = __float2bfloat16(x[i]);
+        }
+    };
+    auto store_f32 = [&](void* base, long long ld, const float (&x)[32]) {
+        float* dst = reinterpret_cast<float*>(base) + orow * ld + col0;
+        if (full) {
+            float4* d4 = reinterpret_cast<float4*>(dst);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) d4[i] = make_float4(x[4 * i], x[4 * i + 1], x[4 * i + 2], x[4 * i + 3]);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (i < nvalid) dst[i] = x[i];
+        }
+    };
+
+    if (EPI == EPI_BF16) {
+        store_bf16(p.C, p.ldc, v);
+    } else if (EPI == EPI_F32) {
+        store_f32(p.C, p.ldc, v);
+    } else if (EPI == EPI_BIAS_GELU) {
+        if (p.C != nullptr) store_bf16(p.C, p.ldc, v);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = gelu_exact(v[i]);
+        apply_dropout(v);
+        store_bf16(p.C2, p.ldc2, v);
+    } else if (EPI == EPI_BIAS_RES || EPI == EPI_PATCH) {
+        if (EPI == EPI_PATCH) {
+            // position embedding row (m % P) + 1 is added BEFORE dropout (vit.py:63-66)
+            const float* pos = reinterpret_cast<const float*>(p.aux) + (long long)(row % p.row_period + 1) * p.ldaux + col0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (i < nvalid) v[i] += __ldg(pos + i);
+        }
+        apply_dropout(v);
+        if (EPI == EPI_BIAS_RES && p.aux != nullptr) {
+            const float* res = reinterpret_cast<const float*>(p.aux) + orow * p.ldaux + col0;
+            if (full) {
+                const float4* r4 = reinterpret_cast<const float4*>(res);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float4 r = r4[i];
+                    v[4 * i] += r.x; v[4 * i + 1] += r.y; v[4 * i + 2] += r.z; v[4 * i + 3] += r.w;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) if (i < nvalid) v[i] += res[i];
+            }
+        }
+        store_f32(p.C, p.ldc, v);
+    } else if (EPI == EPI_DGELU) {
+        apply_dropout(v);
+        const bf16* a = reinterpret_cast<const bf16*>(p.aux) + orow * p.ldaux + col0;
+        if (full) {
+            const uint4* a4 = reinterpret_cast<const uint4*>(a);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const uint4 q = a4[i];
+                const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 f = unpack_bf16(w[j]);
+                    v[8 * i + 2 * j] *= gelu_exact_grad(f.x);
+                    v[8 * i + 2 * j + 1] *= gelu_exact_grad(f.y);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (i < nvalid) v[i] *= gelu_exact_grad(__bfloat162float(a[i]));
+        }
+        store_bf16(p.C, p.ldc, v);
+    } else if (EPI == EPI_ACCUM) {
+        float* dst = reinterpret_cast<float*>(p.C) + orow * p.ldc + col0;
+        if (full) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};"
+                             ::"l"(dst + 4 * i), "f"(v[4 * i]), "f"(v[4 * i + 1]), "f"(v[4 * i + 2]), "f"(v[4 * i + 3])
+                             : "memory");
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (i < nvalid) atomicAdd(dst + i, v[i]);
+        }
+    }
+}
+
+// -------------------------------------------------------------------------------------------------
+// The kernel
+// -------------------------------------------------------------------------------------------------
+template <bool A_MN, bool B_MN, int EPI>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const GemmParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    // 128B swizzle atoms need 1024-byte aligned stage bases.
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t smem_a = smem_base;
+    const uint32_t smem_b = smem_base + STAGES * A_STAGE_BYTES;
+    const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+    auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + s); };
+    auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + 2 + s); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmA);
+        prefetch_tmap(&tmB);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), NUM_EPI_WARPS); }
+        fence_barrier_init();
+    }
+    if (warp == 2) {
+        tmem_alloc<1>(tmem_slot, TMEM_COLS);
+        tmem_relinquish<1>();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    const int total_work = p.tiles_m * p.tiles_n * p.splits;
+
+    auto decode = [&](int w, int& m0, int& n0, int& kb0, int& kb1) {
+        const int tile = w % (p.tiles_m * p.tiles_n);
+        const int split = w / (p.tiles_m * p.tiles_n);
+        // n fastest: CTAs running together share the same A rows (L2 reuse), weights are small.
+        n0 = (tile % p.tiles_n) * BN;
+        m0 = (tile / p.tiles_n) * BM;
+        kb0 = (int)(((long long)split * p.kblocks) / p.splits);
+        kb1 = (int)(((long long)(split + 1) * p.kblocks) / p.splits);
+    };
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+                int m0, n0, kb0, kb1;
+                decode(w, m0, n0, kb0, kb1);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(empty_bar(stage), phase ^ 1u);
+                    mbar_arrive_expect_tx(full_bar(stage), STAGE_BYTES);
+                    const uint32_t sa = smem_a + stage * A_STAGE_BYTES;
+                    const uint32_t sb = smem_b + stage * B_STAGE_BYTES;
+                    const int k0 = kb * BK;
+                    if (!A_MN) {
+                        tma_load_2d(sa, &tmA, full_bar(stage), k0, m0);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < BM / 64; ++i)
+                            tma_load_2d(sa + i * (BK * 128), &tmA, full_bar(stage), m0 + i * 64, k0);
+                    }
+                    if (!B_MN) {
+                        tma_load_2d(sb, &tmB, full_bar(stage), k0, n0);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < BN / 64; ++i)
+                            tma_load_2d(sb + i * (BK * 128), &tmB, full_bar(stage), n0 + i * 64, k0);
+                    }
+                    if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+            // K-major:  8-row groups 1024 B apart (SBO), one 128B atom along K (LBO unused).
+            // MN-major: 8-k-row groups 1024 B apart (SBO), 64-wide MN atoms BK*128 B apart (LBO).
+            constexpr uint32_t a_lbo = A_MN ? BK * 128 : 0, b_lbo = B_MN ? BK * 128 : 0;
+            constexpr uint32_t a_kstep = A_MN ? UMMA_K * 128 : UMMA_K * 2;
+            constexpr uint32_t b_kstep = B_MN ? UMMA_K * 128 : UMMA_K * 2;
+            int stage = 0; uint32_t phase = 0;
+            int iter = 0;
+            for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++iter) {
+                int m0, n0, kb0, kb1;
+                decode(w, m0, n0, kb0, kb1);
+                const int acc = iter & 1;
+                const uint32_t acc_phase = (iter >> 1) & 1;
+                mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(full_bar(stage), phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_a + stage * A_STAGE_BYTES;
+                    const uint32_t sb = smem_b + stage * B_STAGE_BYTES;
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) {
+                        const uint64_t da = make_smem_desc_sw128(sa + k * a_kstep, 1024, a_lbo);
+                        const uint64_t db = make_smem_desc_sw128(sb + k * b_kstep, 1024, b_lbo);
+                        umma_bf16<1>(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(empty_bar(stage));          // frees the smem stage when the MMAs retire
+                    if (kb == kb1 - 1) umma_commit(tfull_bar(acc));  // accumulator ready
+                    if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp >= 4) {
+        // ===================== Epilogue =====================
+        const int ew = warp - 4;
+        const int quarter = warp & 3;        // TMEM lane quarter this warp may access
+        const int half = ew >> 2;            // which 128-column half of the tile
+        int iter = 0;
+        for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++iter) {
+            int m0, n0, kb0, kb1;
+            decode(w, m0, n0, kb0, kb1);
+            const int acc = iter & 1;
+            const uint32_t acc_phase = (iter >> 1) & 1;
+            mbar_wait(tfull_bar(acc), acc_phase);
+            tc_fence_after();
+            const int row = m0 + quarter * 32 + lane;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                const int col_in_tile = half * 128 + c * 32;
+                const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + col_in_tile);
+                uint32_t r[32];
+                tmem_ld_32x32(taddr, r);
+                tmem_ld_wait();
+                if (c == 3) {
+                    // all TMEM reads of this warp are done: hand the accumulator back to the MMA warp
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(tempty_bar(acc));
+                }
+                float v[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+                epilogue_chunk<EPI>(p, row, n0 + col_in_tile, v);
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc<1>(tmem_base, TMEM_COLS);
+    }
+}
+
+// -------------------------------------------------------------------------------------------------
+// Host side
+// -------------------------------------------------------------------------------------------------
+static PFN_cuTensorMapEncodeTiled get_encode_fn() {
+    static PFN_cuTensorMapEncodeTiled fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled>(ptr);
+    });
+    return fn;
+}
+
+// 2-D bf16 tensor map: inner dimension `inner` elements (contiguous), `outer` rows of `ld` elements.
+static int make_tmap_bf16(CUtensorMap* tm, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
+                          uint32_t box_inner, uint32_t box_outer) {
+    PFN_cuTensorMapEncodeTiled enc = get_encode_fn();
+    if (!enc) return set_error(-2, "cuTensorMapEncodeTiled not available (no CUDA driver?)");
+    cuuint64_t dims[2] = {inner, outer};
+    cuuint64_t strides[1] = {ld * 2};
+    cuuint32_t box[2] = {box_inner, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+        return set_error(-3, "cuTensorMapEncodeTiled failed (%d): base=%p inner=%llu outer=%llu ld=%llu", (int)r,
+                         base, (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)ld);
+    return 0;
+}
+
+typedef void (*gemm_kernel_t)(const CUtensorMap, const CUtensorMap, const GemmParams);
+
+template <bool A_MN, bool B_MN>
+static gemm_kernel_t pick_epi(int epi) {
+    switch (epi) {
+        case EPI_BF16: return gemm_tcgen05_kernel<A_MN, B_MN, EPI_BF16>;
+        case EPI_BIAS_GELU: return gemm_tcgen05_kernel<A_MN, B_MN, EPI_BIAS_GELU>;
+        case EPI_BIAS_RES: return gemm_tcgen05_kernel<A_MN, B_MN, EPI_BIAS_RES>;
+        case EPI_DGELU: return gemm_tcgen05_kernel<A_MN, B_MN, EPI_DGELU>;
+        case EPI_ACCUM: return gemm_tcgen05_kernel<A_MN, B_MN, EPI_ACCUM>;
+        case EPI_F32: return gemm_tcgen05_kernel<A_MN, B_MN, EPI_F32>;
+        case EPI_PATCH: return gemm_tcgen05_kernel<A_MN, B_MN, EPI_PATCH>;
+    }
+    return nullptr;
+}
+
+int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long lda, const void* B, long long ldb,
+                void* C, long long ldc, void* C2, long long ldc2, const float* bias, const void* aux,
+                long long ldaux, float drop_p, unsigned long long seed, unsigned long long offset, int row_period,
+                int splits, cudaStream_t stream) {
+    B200_CHECK_ARG(op >= 0 && op <= 2, "gemm: bad op %d", op);
+    B200_CHECK_ARG(epi >= 0 && epi < EPI_COUNT, "gemm: bad epilogue %d", epi);
+    B200_CHECK_ARG(M > 0 && N > 0 && K > 0, "gemm: empty problem M=%d N=%d K=%d", M, N, K);
+    B200_CHECK_ARG(A && B && C, "gemm: null operand");
+    B200_CHECK_ARG((lda % 8) == 0 && (ldb % 8) == 0, "gemm: lda/ldb must be multiples of 8 elements (TMA 16B stride), got %lld %lld", lda, ldb);
+    B200_CHECK_ARG(((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0, "gemm: A/B must be 16-byte aligned");
+    B200_CHECK_ARG(epi != EPI_BIAS_GELU || C2 != nullptr, "gemm: GELU epilogue needs the second output");
+    B200_CHECK_ARG(epi != EPI_DGELU || aux != nullptr, "gemm: dGELU epilogue needs the pre-activation");
+    B200_CHECK_ARG(epi != EPI_PATCH || (aux != nullptr && row_period > 0), "gemm: patch epilogue needs pos embedding and period");
+    B200_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "gemm: dropout p must be in [0,1)");
+
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K;
+    p.tiles_m = (M + BM - 1) / BM;
+    p.tiles_n = (N + BN - 1) / BN;
+    p.kblocks = (K + BK - 1) / BK;
+    if (splits < 1) splits = 1;
+    if (splits > p.kblocks) splits = p.kblocks;
+    B200_CHECK_ARG(splits == 1 || epi == EPI_ACCUM, "gemm: split-K needs the accumulate epilogue");
+    p.splits = splits;
+    p.C = C; p.ldc = ldc; p.C2 = C2; p.ldc2 = ldc2;
+    p.bias = bias; p.aux = aux; p.ldaux = ldaux;
+    p.drop = make_dropout(drop_p, seed, offset);
+    p.row_period = row_period;
+    const bool out_f32 = (epi == EPI_BIAS_RES || epi == EPI_ACCUM || epi == EPI_F32 || epi == EPI_PATCH);
+    const int ovec = out_f32 ? 4 : 8;
+    bool vec = (ldc % ovec) == 0 && ((uintptr_t)C % 16) == 0;
+    if (C2) vec = vec && (ldc2 % 8) == 0 && ((uintptr_t)C2 % 16) == 0;
+    if (bias) vec = vec && ((uintptr_t)bias % 16) == 0;
+    if (aux) {
+        const int avec = (epi == EPI_DGELU) ? 8 : 4;
+        vec = vec && (ldaux % avec) == 0 && ((uintptr_t)aux % 16) == 0;
+    }
+    p.vec_ok = vec ? 1 : 0;
+
+    CUtensorMap tmA, tmB;
+    int rc;
+    const bool a_mn = (op == OP_TN), b_mn = (op != OP_NT);
+    if (!a_mn) rc = make_tmap_bf16(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM);
+    else       rc = make_tmap_bf16(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK);
+    if (rc) return rc;
+    if (!b_mn) rc = make_tmap_bf16(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, BN);
+    else       rc = make_tmap_bf16(&tmB, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK);
+    if (rc) return rc;
+
+    gemm_kernel_t kern = nullptr;
+    if (op == OP_NT) kern = pick_epi<false, false>(epi);
+    else if (op == OP_NN) kern = pick_epi<false, true>(epi);
+    else kern = pick_epi<true, true>(epi);
+    B200_CHECK_ARG(kern != nullptr, "gemm: no kernel for op %d epi %d", op, epi);
+
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+    const int total = p.tiles_m * p.tiles_n * p.splits;
+    const int grid = total < sm_count() ? total : sm_count();
+    kern<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream>>>(tmA, tmB, p);
+    B200_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace b200vit

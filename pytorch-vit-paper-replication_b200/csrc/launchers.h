@@ -1,0 +1,54 @@
+// Internal launcher prototypes shared between the kernel translation units and api.cu.
+#pragma once
+#include "common.cuh"
+
+namespace b200vit {
+
+int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long lda, const void* B, long long ldb,
+                void* C, long long ldc, void* C2, long long ldc2, const float* bias, const void* aux,
+                long long ldaux, float drop_p, unsigned long long seed, unsigned long long offset, int row_period,
+                int splits, cudaStream_t stream);
+
+int cast_f32_bf16_launch(const float* src, bf16* dst, long long n, cudaStream_t stream);
+int im2col_launch(const float* image, bf16* patches, int batch, int channels, int height, int width, int patch,
+                  cudaStream_t stream);
+int cls_rows_launch(const float* cls, const float* pos, float* x, int batch, int tokens, int dim, float drop_p,
+                    unsigned long long seed, unsigned long long offset, cudaStream_t stream);
+int embed_grads_launch(const float* gx, float* g_cls, float* g_pos, float* g_bias, int batch, int tokens, int dim,
+                       float drop_p, unsigned long long seed, unsigned long long offset, cudaStream_t stream);
+int patch_grad_rows_launch(const float* gx, bf16* gy, int batch, int tokens, int dim, float drop_p,
+                           unsigned long long seed, unsigned long long offset, cudaStream_t stream);
+int colsum_bf16_launch(const bf16* x, long long ld, float* out, long long rows, int cols, cudaStream_t stream);
+int dropout_cast_launch(const float* g, bf16* out, float* colsum, long long rows, int cols, float drop_p,
+                        unsigned long long seed, unsigned long long offset, cudaStream_t stream);
+int scale_by_scalar_launch(const float* src, const float* scalar_dev, float* dst, long long n, cudaStream_t stream);
+
+int layernorm_fwd_launch(const float* x, long long row_stride, const float* gamma, const float* beta, bf16* y_bf16,
+                         float* y_f32, float* mean, float* rstd, long long rows, int dim, float eps,
+                         cudaStream_t stream);
+int layernorm_bwd_launch(const bf16* dy_bf16, const float* dy_f32, const float* x, long long row_stride,
+                         const float* mean, const float* rstd, const float* gamma, const float* gin, float* gout,
+                         long long gout_stride, bf16* gout_bf16, float* dgamma, float* dbeta, float* dbias_next,
+                         long long rows, int dim, float drop_p, unsigned long long seed, unsigned long long offset,
+                         cudaStream_t stream);
+
+int attention_fwd_launch(const bf16* qkv, bf16* out, float* lse, int batch, int tokens, int heads, int head_dim,
+                         float scale, cudaStream_t stream);
+int attention_bwd_launch(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, float* delta,
+                         bf16* dqkv, int batch, int tokens, int heads, int head_dim, float scale,
+                         cudaStream_t stream);
+
+int head_fwd_launch(const float* xn, const float* w, const float* b, float* logits, int batch, int dim, int classes,
+                    cudaStream_t stream);
+int head_bwd_launch(const float* xn, const float* w, const float* dlogits, float* dxn, float* dw, float* db,
+                    int batch, int dim, int classes, cudaStream_t stream);
+int softmax_ce_launch(const float* logits, const long long* labels, float* loss, float* dlogits, int* correct,
+                      int batch, int classes, cudaStream_t stream);
+
+int l2norm_sq_launch(const float* const* ptrs_dev, const long long* sizes_dev, int num_tensors, long long max_size,
+                     float* partials, int num_partials, float* out_sumsq, cudaStream_t stream);
+int adam_step_launch(const void* table_dev, int num_tensors, long long max_size, const float* lrs, const float* wds,
+                     int num_groups, float beta1, float beta2, float eps, int step, int decoupled,
+                     const float* grad_sumsq, float max_norm, float grad_scale, cudaStream_t stream);
+
+}  // namespace b200vit

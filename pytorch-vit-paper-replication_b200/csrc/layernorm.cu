@@ -1,0 +1,228 @@
+// LayerNorm forward / backward (nn.LayerNorm(D), eps 1e-5, biased variance: reference models/vit.py:83,115,216).
+// HBM-bound: one warp per row, float4 accesses, warp-shuffle row reductions; the backward keeps the
+// dgamma / dbeta (and optional next-bias) column partials in registers across the rows a warp visits and
+// finishes with one shared-memory reduction + one atomic per column per block.
+#include "common.cuh"
+#include "launchers.h"
+
+namespace b200vit {
+
+constexpr int LN_WARPS = 8;
+
+// ---------------------------------------------------------------------------------------------
+// forward: y = (x - mean) * rstd * gamma + beta ; writes bf16 (GEMM operand) and/or fp32, plus row stats
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(LN_WARPS * 32)
+layernorm_fwd_kernel(const float* __restrict__ x, long long row_stride, const float* __restrict__ gamma,
+                     const float* __restrict__ beta, bf16* __restrict__ y_bf16, float* __restrict__ y_f32,
+                     float* __restrict__ mean_out, float* __restrict__ rstd_out, long long rows, int D, float eps) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nv = D >> 2;
+    for (long long row = (long long)blockIdx.x * LN_WARPS + warp; row < rows; row += (long long)gridDim.x * LN_WARPS) {
+        const float4* xr = reinterpret_cast<const float4*>(x + row * row_stride);
+        float s = 0.f;
+        for (int i = lane; i < nv; i += 32) {
+            const float4 v = xr[i];
+            s += (v.x + v.y) + (v.z + v.w);
+        }
+        const float mean = warp_sum(s) / (float)D;
+        float q = 0.f;
+        for (int i = lane; i < nv; i += 32) {
+            const float4 v = xr[i];
+            const float a = v.x - mean, b = v.y - mean, c = v.z - mean, d = v.w - mean;
+            q += (a * a + b * b) + (c * c + d * d);
+        }
+        const float var = warp_sum(q) / (float)D;
+        const float rstd = rsqrtf(var + eps);
+        if (lane == 0) {
+            if (mean_out) mean_out[row] = mean;
+            if (rstd_out) rstd_out[row] = rstd;
+        }
+        for (int i = lane; i < nv; i += 32) {
+            const float4 v = xr[i];
+            const float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + i);
+            const float4 b = __ldg(reinterpret_cast<const float4*>(beta) + i);
+            float4 o;
+            o.x = (v.x - mean) * rstd * g.x + b.x;
+            o.y = (v.y - mean) * rstd * g.y + b.y;
+            o.z = (v.z - mean) * rstd * g.z + b.z;
+            o.w = (v.w - mean) * rstd * g.w + b.w;
+            if (y_f32) reinterpret_cast<float4*>(y_f32 + row * (long long)D)[i] = o;
+            if (y_bf16) {
+                uint2 p;
+                p.x = pack_bf16(o.x, o.y);
+                p.y = pack_bf16(o.z, o.w);
+                reinterpret_cast<uint2*>(y_bf16 + row * (long long)D)[i] = p;
+            }
+        }
+    }
+}
+
+int layernorm_fwd_launch(const float* x, long long row_stride, const float* gamma, const float* beta, bf16* y_bf16,
+                         float* y_f32, float* mean, float* rstd, long long rows, int dim, float eps,
+                         cudaStream_t stream) {
+    B200_CHECK_ARG(x && gamma && beta, "layernorm_fwd: null pointer");
+    B200_CHECK_ARG(y_bf16 || y_f32, "layernorm_fwd: no output requested");
+    B200_CHECK_ARG(rows > 0 && dim > 0 && (dim % 4) == 0, "layernorm_fwd: dim must be a positive multiple of 4 (got %d)", dim);
+    B200_CHECK_ARG((row_stride % 4) == 0 && row_stride >= dim, "layernorm_fwd: row stride %lld must be a multiple of 4 and >= dim", row_stride);
+    B200_CHECK_ARG(((uintptr_t)x % 16) == 0 && ((uintptr_t)gamma % 16) == 0 && ((uintptr_t)beta % 16) == 0,
+                   "layernorm_fwd: pointers must be 16-byte aligned");
+    long long blocks = (rows + LN_WARPS - 1) / LN_WARPS;
+    const long long cap = (long long)sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    layernorm_fwd_kernel<<<(unsigned)blocks, LN_WARPS * 32, 0, stream>>>(x, row_stride, gamma, beta, y_bf16, y_f32,
+                                                                        mean, rstd, rows, dim, eps);
+    B200_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// backward. With xhat = (x - mean) * rstd and dyg = dy * gamma:
+//   dx = rstd * (dyg - mean_D(dyg) - xhat * mean_D(dyg * xhat))
+//   gout = gin + dx                         (gin = gradient arriving through the residual connection)
+//   dgamma += sum_rows dy * xhat ; dbeta += sum_rows dy
+//   gout_bf16 = bf16(dropout_mask * gout) ; dbias_next += sum_rows gout_bf16   (operand + bias gradient of the
+//                                                                              Linear that produced this residual)
+// NV = float4 chunks per lane (ceil(D / 128)).
+// ---------------------------------------------------------------------------------------------
+template <int NV>
+__global__ void __launch_bounds__(LN_WARPS * 32)
+layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__ dy_f32, const float* __restrict__ x,
+                     long long row_stride, const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
+                     const float* __restrict__ gamma, const float* __restrict__ gin, float* __restrict__ gout,
+                     long long gout_stride, bf16* __restrict__ gout_bf16, float* __restrict__ dgamma,
+                     float* __restrict__ dbeta, float* __restrict__ dbias_next, long long rows, int D,
+                     DropoutParams drop) {
+    extern __shared__ float red[];  // [LN_WARPS][D]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nv = D >> 2;
+
+    float4 g4[NV];
+    float4 acc_g[NV], acc_b[NV], acc_n[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        const int i = lane + 32 * k;
+        g4[k] = (i < nv) ? __ldg(reinterpret_cast<const float4*>(gamma) + i) : make_float4(0, 0, 0, 0);
+        acc_g[k] = make_float4(0, 0, 0, 0);
+        acc_b[k] = make_float4(0, 0, 0, 0);
+        acc_n[k] = make_float4(0, 0, 0, 0);
+    }
+
+    for (long long row = (long long)blockIdx.x * LN_WARPS + warp; row < rows; row += (long long)gridDim.x * LN_WARPS) {
+        const float mean = mean_in[row], rstd = rstd_in[row];
+        const float4* xr = reinterpret_cast<const float4*>(x + row * row_stride);
+        float4 xh[NV], dy[NV];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            const int i = lane + 32 * k;
+            if (i < nv) {
+                const float4 v = xr[i];
+                xh[k] = make_float4((v.x - mean) * rstd, (v.y - mean) * rstd, (v.z - mean) * rstd, (v.w - mean) * rstd);
+                if (dy_bf16) {
+                    const uint2 q = reinterpret_cast<const uint2*>(dy_bf16 + row * (long long)D)[i];
+                    const float2 a = unpack_bf16(q.x), b = unpack_bf16(q.y);
+                    dy[k] = make_float4(a.x, a.y, b.x, b.y);
+                } else {
+                    dy[k] = reinterpret_cast<const float4*>(dy_f32 + row * (long long)D)[i];
+                }
+                const float4 g = g4[k];
+                const float a0 = dy[k].x * g.x, a1 = dy[k].y * g.y, a2 = dy[k].z * g.z, a3 = dy[k].w * g.w;
+                s1 += (a0 + a1) + (a2 + a3);
+                s2 += (a0 * xh[k].x + a1 * xh[k].y) + (a2 * xh[k].z + a3 * xh[k].w);
+                acc_g[k].x += dy[k].x * xh[k].x; acc_g[k].y += dy[k].y * xh[k].y;
+                acc_g[k].z += dy[k].z * xh[k].z; acc_g[k].w += dy[k].w * xh[k].w;
+                acc_b[k].x += dy[k].x; acc_b[k].y += dy[k].y; acc_b[k].z += dy[k].z; acc_b[k].w += dy[k].w;
+            }
+        }
+        const float c1 = warp_sum(s1) / (float)D;
+        const float c2 = warp_sum(s2) / (float)D;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            const int i = lane + 32 * k;
+            if (i < nv) {
+                const float4 g = g4[k];
+                float4 o;
+                o.x = rstd * (dy[k].x * g.x - c1 - xh[k].x * c2);
+                o.y = rstd * (dy[k].y * g.y - c1 - xh[k].y * c2);
+                o.z = rstd * (dy[k].z * g.z - c1 - xh[k].z * c2);
+                o.w = rstd * (dy[k].w * g.w - c1 - xh[k].w * c2);
+                if (gin) {
+                    const float4 r = reinterpret_cast<const float4*>(gin + row * gout_stride)[i];
+                    o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
+                }
+                reinterpret_cast<float4*>(gout + row * gout_stride)[i] = o;
+                if (gout_bf16) {
+                    float v[4] = {o.x, o.y, o.z, o.w};
+                    if (drop.p > 0.f) {
+                        const unsigned long long e0 = (unsigned long long)row * D + 4ull * i;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) v[j] *= dropout_mult1(drop, e0 + j);
+                    }
+                    uint2 pk;
+                    pk.x = pack_bf16(v[0], v[1]);
+                    pk.y = pack_bf16(v[2], v[3]);
+                    reinterpret_cast<uint2*>(gout_bf16 + row * (long long)D)[i] = pk;
+                    const float2 r0 = unpack_bf16(pk.x), r1 = unpack_bf16(pk.y);
+                    acc_n[k].x += r0.x; acc_n[k].y += r0.y; acc_n[k].z += r1.x; acc_n[k].w += r1.y;
+                }
+            }
+        }
+    }
+
+    // block reduction of the three column accumulators, one at a time through the same smem slab
+    auto reduce_store = [&](float4 (&acc)[NV], float* dst) {
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            const int i = lane + 32 * k;
+            if (i < nv) reinterpret_cast<float4*>(red + warp * D)[i] = acc[k];
+        }
+        __syncthreads();
+        for (int d = threadIdx.x; d < D; d += blockDim.x) {
+            float s = 0.f;
+#pragma unroll
+            for (int w = 0; w < LN_WARPS; ++w) s += red[w * D + d];
+            atomicAdd(dst + d, s);
+        }
+    };
+    if (dgamma) reduce_store(acc_g, dgamma);
+    if (dbeta) reduce_store(acc_b, dbeta);
+    if (dbias_next && gout_bf16) reduce_store(acc_n, dbias_next);
+}
+
+int layernorm_bwd_launch(const bf16* dy_bf16, const float* dy_f32, const float* x, long long row_stride,
+                         const float* mean, const float* rstd, const float* gamma, const float* gin, float* gout,
+                         long long gout_stride, bf16* gout_bf16, float* dgamma, float* dbeta, float* dbias_next,
+                         long long rows, int dim, float drop_p, unsigned long long seed, unsigned long long offset,
+                         cudaStream_t stream) {
+    B200_CHECK_ARG((dy_bf16 != nullptr) != (dy_f32 != nullptr), "layernorm_bwd: pass exactly one of dy_bf16 / dy_f32");
+    B200_CHECK_ARG(x && mean && rstd && gamma && gout, "layernorm_bwd: null pointer");
+    B200_CHECK_ARG(rows > 0 && dim > 0 && (dim % 4) == 0 && dim <= 1024,
+                   "layernorm_bwd: dim must be a multiple of 4 and <= 1024 (got %d)", dim);
+    B200_CHECK_ARG((row_stride % 4) == 0 && (gout_stride % 4) == 0, "layernorm_bwd: strides must be multiples of 4");
+    // dgamma / dbeta / dbias_next are accumulated with atomics: start from zero (outputs are overwritten).
+    if (dgamma) B200_CUDA(cudaMemsetAsync(dgamma, 0, sizeof(float) * dim, stream));
+    if (dbeta) B200_CUDA(cudaMemsetAsync(dbeta, 0, sizeof(float) * dim, stream));
+    if (dbias_next) B200_CUDA(cudaMemsetAsync(dbias_next, 0, sizeof(float) * dim, stream));
+    long long blocks = (rows + LN_WARPS - 1) / LN_WARPS;
+    const long long cap = (long long)sm_count() * 4;
+    if (blocks > cap) blocks = cap;
+    const DropoutParams drop = make_dropout(drop_p, seed, offset);
+    const size_t smem = sizeof(float) * LN_WARPS * dim;
+    const int nvl = (dim / 4 + 31) / 32;
+#define LN_BWD_CASE(NV)                                                                                         \
+    layernorm_bwd_kernel<NV><<<(unsigned)blocks, LN_WARPS * 32, smem, stream>>>(                                 \
+        dy_bf16, dy_f32, x, row_stride, mean, rstd, gamma, gin, gout, gout_stride, gout_bf16, dgamma, dbeta,    \
+        dbias_next, rows, dim, drop)
+    if (nvl <= 1) LN_BWD_CASE(1);
+    else if (nvl <= 2) LN_BWD_CASE(2);
+    else if (nvl <= 4) LN_BWD_CASE(4);
+    else if (nvl <= 6) LN_BWD_CASE(6);
+    else LN_BWD_CASE(8);
+#undef LN_BWD_CASE
+    B200_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace b200vit

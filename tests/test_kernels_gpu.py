@@ -1,0 +1,251 @@
+"""Per-kernel parity: each C-ABI entry point on the GPU vs a plain torch fp32 reference of the same op
+(floating-point kernels; tolerances are written next to each check)."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from b200vit import kernels as K  # noqa: E402
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+def rel_err(a, b):
+    a = a.float()
+    b = b.float()
+    return ((a - b).norm() / (b.norm() + 1e-12)).item()
+
+
+def _rand_bf16(shape, gen, scale=1.0):
+    return (torch.randn(shape, generator=gen, device="cpu") * scale).to(torch.bfloat16).to(dev())
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 512, 768), (200, 328, 200), (1024, 768, 3072), (6304, 2304, 768)])
+def test_gemm_nt_bias(M, N, K):
+    g = torch.Generator().manual_seed(1)
+    A = _rand_bf16((M, K), g)
+    B = _rand_bf16((N, K), g, 0.05)
+    bias = torch.randn(N, generator=g).to(dev())
+    C = torch.empty((M, N), dtype=torch.bfloat16, device=dev())
+    K.gemm(K.OP_NT, K.EPI_BF16, M, N, K, A, K, B, K, C, N, bias=bias)
+    ref = A.float() @ B.float().t() + bias
+    # bf16 output rounding: 2^-9 relative per element
+    assert rel_err(C, ref) < 4e-3
+    assert (C.float() - ref).abs().max().item() < 0.05 * ref.abs().max().item() + 1e-2
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 256, 128), (200, 328, 200), (6304, 768, 2304)])
+def test_gemm_nn(M, N, K):
+    g = torch.Generator().manual_seed(2)
+    A = _rand_bf16((M, K), g)
+    B = _rand_bf16((K, N), g, 0.05)
+    C = torch.empty((M, N), dtype=torch.bfloat16, device=dev())
+    K.gemm(K.OP_NN, K.EPI_BF16, M, N, K, A, K, B, N, C, N)
+    ref = A.float() @ B.float()
+    assert rel_err(C, ref) < 4e-3
+
+
+@pytest.mark.parametrize("M,N,K,split", [(256, 256, 128, 1), (200, 328, 264, 2), (768, 3072, 6304, 8), (2304, 768, 6304, 5)])
+def test_gemm_tn_accum(M, N, K, split):
+    g = torch.Generator().manual_seed(3)
+    A = _rand_bf16((K, M), g)
+    B = _rand_bf16((K, N), g, 0.05)
+    C = torch.ones((M, N), dtype=torch.float32, device=dev())
+    K.gemm(K.OP_TN, K.EPI_ACCUM, M, N, K, A, M, B, N, C, N, split_k=split)
+    ref = A.float().t() @ B.float() + 1.0
+    assert rel_err(C, ref) < 1e-4
+
+
+def test_gemm_gelu_and_dgelu():
+    g = torch.Generator().manual_seed(4)
+    M, N, Kd = 512, 768, 256
+    A = _rand_bf16((M, Kd), g)
+    B = _rand_bf16((N, Kd), g, 0.08)
+    bias = torch.randn(N, generator=g).to(dev()) * 0.1
+    a = torch.empty((M, N), dtype=torch.bfloat16, device=dev())
+    h = torch.empty((M, N), dtype=torch.bfloat16, device=dev())
+    K.gemm(K.OP_NT, K.EPI_BIAS_GELU, M, N, Kd, A, Kd, B, Kd, a, N, C2=h, ldc2=N, bias=bias)
+    a_ref = A.float() @ B.float().t() + bias
+    h_ref = torch.nn.functional.gelu(a_ref)
+    assert rel_err(a, a_ref) < 4e-3
+    assert rel_err(h, h_ref) < 5e-3
+    # backward epilogue: out = (G @ W) * gelu'(a)
+    G = _rand_bf16((M, Kd), g)
+    W = _rand_bf16((Kd, N), g, 0.08)
+    out = torch.empty((M, N), dtype=torch.bfloat16, device=dev())
+    K.gemm(K.OP_NN, K.EPI_DGELU, M, N, Kd, G, Kd, W, N, out, N, aux=a, ldaux=N)
+    x = a.float().requires_grad_(True)
+    torch.nn.functional.gelu(x).backward(G.float() @ W.float())
+    assert rel_err(out, x.grad) < 5e-3
+
+
+def test_gemm_bias_res_and_dropout_consistency():
+    g = torch.Generator().manual_seed(5)
+    M, N, Kd = 384, 768, 512
+    A = _rand_bf16((M, Kd), g)
+    B = _rand_bf16((N, Kd), g, 0.05)
+    bias = torch.randn(N, generator=g).to(dev())
+    res = torch.randn((M, N), generator=g).to(dev())
+    C = torch.empty((M, N), dtype=torch.float32, device=dev())
+    K.gemm(K.OP_NT, K.EPI_BIAS_RES, M, N, Kd, A, Kd, B, Kd, C, N, bias=bias, aux=res, ldaux=N)
+    ref = A.float() @ B.float().t() + bias + res
+    assert rel_err(C, ref) < 1e-4
+    # dropout: same (seed, offset) -> same mask in the GEMM epilogue and in dropout_cast
+    p = 0.25
+    C2 = torch.empty_like(C)
+    K.gemm(K.OP_NT, K.EPI_BIAS_RES, M, N, Kd, A, Kd, B, Kd, C2, N, bias=bias, dropout_p=p, seed=123, offset=7)
+    y = A.float() @ B.float().t() + bias
+    keep = (C2 != 0)
+    frac = keep.float().mean().item()
+    assert abs(frac - (1 - p)) < 0.01
+    assert rel_err(C2[keep], (y / (1 - p))[keep]) < 1e-4
+    ones = torch.ones((M, N), dtype=torch.float32, device=dev())
+    mask_bf16 = torch.empty((M, N), dtype=torch.bfloat16, device=dev())
+    colsum = torch.empty(N, dtype=torch.float32, device=dev())
+    K.dropout_cast(ones, mask_bf16, colsum, M, N, p, 123, 7)
+    assert torch.equal(mask_bf16 != 0, keep)
+    assert rel_err(colsum, mask_bf16.float().sum(0)) < 1e-5
+
+
+def test_patch_embedding_pieces():
+    g = torch.Generator().manual_seed(6)
+    Bn, Cc, H, P, D = 3, 3, 64, 16, 128
+    img = torch.rand((Bn, Cc, H, H), generator=g).to(dev())
+    w = (torch.randn((D, Cc, P, P), generator=g) * 0.05).to(dev())
+    bias = torch.randn(D, generator=g).to(dev())
+    Np = (H // P) ** 2
+    T = Np + 1
+    cls = torch.rand((1, 1, D), generator=g).to(dev())
+    pos = torch.rand((1, T, D), generator=g).to(dev())
+    patches = K.im2col_patches(img, P)
+    ref_patches = torch.nn.functional.unfold(img, P, stride=P).transpose(1, 2).reshape(Bn * Np, -1)
+    assert torch.equal(patches.float(), ref_patches.to(torch.bfloat16).float())
+    x = torch.full((Bn * T, D), float("nan"), dtype=torch.float32, device=dev())
+    wb = K.cast_bf16(w.reshape(D, -1).contiguous())
+    Kd = Cc * P * P
+    K.gemm(K.OP_NT, K.EPI_PATCH, Bn * Np, D, Kd, patches, Kd, wb, Kd, x, D, bias=bias, aux=pos.reshape(T, D), ldaux=D,
+           row_period=Np)
+    K.class_token_rows(cls, pos, x, Bn, T, D, 0.0, 0, 0)
+    conv = torch.nn.functional.conv2d(img, w, bias, stride=P).flatten(2).permute(0, 2, 1)
+    ref = torch.cat((cls.expand(Bn, -1, -1), conv), dim=1) + pos
+    assert rel_err(x.reshape(Bn, T, D), ref) < 3e-3
+
+
+@pytest.mark.parametrize("rows,D", [(37, 64), (1000, 768), (300, 1024)])
+def test_layernorm_fwd_bwd(rows, D):
+    g = torch.Generator().manual_seed(7)
+    x = (torch.randn((rows, D), generator=g) * 2 + 0.5).to(dev())
+    gamma = (torch.randn(D, generator=g) * 0.2 + 1).to(dev())
+    beta = torch.randn(D, generator=g).to(dev())
+    y16 = torch.empty((rows, D), dtype=torch.bfloat16, device=dev())
+    y32 = torch.empty((rows, D), dtype=torch.float32, device=dev())
+    mean = torch.empty(rows, device=dev())
+    rstd = torch.empty(rows, device=dev())
+    K.layernorm_fwd(x, D, gamma, beta, y16, y32, mean, rstd, rows, D, 1e-5)
+    xr = x.clone().requires_grad_(True)
+    gr = gamma.clone().requires_grad_(True)
+    br = beta.clone().requires_grad_(True)
+    ref = torch.nn.functional.layer_norm(xr, (D,), gr, br, 1e-5)
+    assert rel_err(y32, ref) < 1e-5          # fp32 kernel vs fp32 torch
+    assert rel_err(y16, ref) < 4e-3          # bf16 rounding
+    dy = torch.randn((rows, D), generator=g).to(dev())
+    gin = torch.randn((rows, D), generator=g).to(dev())
+    ref.backward(dy)
+    gout = torch.empty_like(x)
+    g16 = torch.empty((rows, D), dtype=torch.bfloat16, device=dev())
+    dgamma = torch.empty(D, device=dev())
+    dbeta = torch.empty(D, device=dev())
+    dbn = torch.empty(D, device=dev())
+    K.layernorm_bwd(None, dy, x, D, mean, rstd, gamma, gin, gout, D, g16, dgamma, dbeta, dbn, rows, D)
+    assert rel_err(gout, xr.grad + gin) < 1e-4
+    assert rel_err(dgamma, gr.grad) < 1e-4
+    assert rel_err(dbeta, br.grad) < 1e-4
+    assert rel_err(g16, xr.grad + gin) < 4e-3
+    assert rel_err(dbn, g16.float().sum(0)) < 1e-4
+    # bf16 dy input path
+    dy16 = dy.to(torch.bfloat16)
+    K.layernorm_bwd(dy16, None, x, D, mean, rstd, gamma, None, gout, D, None, dgamma, dbeta, None, rows, D)
+    xr.grad = None
+    torch.nn.functional.layer_norm(xr, (D,), gamma, beta, 1e-5).backward(dy16.float())
+    assert rel_err(gout, xr.grad) < 1e-4
+
+
+@pytest.mark.parametrize("Bn,T,H", [(2, 197, 12), (1, 64, 2), (3, 50, 4), (1, 577, 16)])
+def test_attention_fwd_bwd(Bn, T, H):
+    g = torch.Generator().manual_seed(8)
+    hd = 64
+    qkv = _rand_bf16((Bn, T, 3, H, hd), g, 1.0)
+    out = torch.empty((Bn, T, H * hd), dtype=torch.bfloat16, device=dev())
+    lse = torch.empty((Bn, H, T), dtype=torch.float32, device=dev())
+    scale = 1.0 / math.sqrt(hd)
+    K.attention_fwd(qkv, out, lse, Bn, T, H, hd, scale)
+    q, k, v = [qkv[:, :, i].float().permute(0, 2, 1, 3).detach().requires_grad_(True) for i in range(3)]
+    s = (q @ k.transpose(-1, -2)) * scale
+    ref = torch.softmax(s, -1) @ v
+    ref_out = ref.permute(0, 2, 1, 3).reshape(Bn, T, H * hd)
+    assert rel_err(out, ref_out) < 1e-2      # P is rounded to bf16 before the PV product
+    assert rel_err(lse, torch.logsumexp(s, -1)) < 1e-4
+    dout = _rand_bf16((Bn, T, H * hd), g, 1.0)
+    delta = torch.empty((Bn, H, T), dtype=torch.float32, device=dev())
+    dqkv = torch.empty_like(qkv)
+    K.attention_bwd(qkv, out, dout, lse, delta, dqkv, Bn, T, H, hd, scale)
+    ref.backward(dout.float().reshape(Bn, T, H, hd).permute(0, 2, 1, 3))
+    for i, t in enumerate((q, k, v)):
+        got = dqkv[:, :, i].float().permute(0, 2, 1, 3)
+        assert rel_err(got, t.grad) < 2e-2, f"d{'qkv'[i]}"
+
+
+@pytest.mark.parametrize("Bn,C", [(32, 3), (256, 1000), (7, 10)])
+def test_head_and_ce(Bn, C):
+    g = torch.Generator().manual_seed(9)
+    D = 768
+    xn = torch.randn((Bn, D), generator=g).to(dev())
+    w = (torch.randn((C, D), generator=g) * 0.05).to(dev())
+    b = torch.randn(C, generator=g).to(dev())
+    logits = torch.empty((Bn, C), device=dev())
+    K.head_fwd(xn, w, b, logits, Bn, D, C)
+    ref = xn @ w.t() + b
+    assert rel_err(logits, ref) < 1e-5
+    y = torch.randint(0, C, (Bn,), generator=g).to(dev())
+    loss = torch.empty(1, device=dev())
+    dl = torch.empty((Bn, C), device=dev())
+    correct = torch.empty(1, dtype=torch.int32, device=dev())
+    K.softmax_ce(logits, y, loss, dl, correct, Bn, C)
+    lr = ref.clone().requires_grad_(True)
+    ref_loss = torch.nn.functional.cross_entropy(lr, y)
+    ref_loss.backward()
+    assert abs(loss.item() - ref_loss.item()) < 1e-5 * max(1.0, abs(ref_loss.item()))
+    assert rel_err(dl, lr.grad) < 1e-5
+    assert correct.item() == (ref.argmax(1) == y).sum().item()
+    dxn = torch.empty_like(xn)
+    dw = torch.empty_like(w)
+    db = torch.empty_like(b)
+    K.head_bwd(xn, w, dl, dxn, dw, db, Bn, D, C)
+    assert rel_err(dxn, dl @ w) < 1e-5
+    assert rel_err(dw, dl.t() @ xn) < 1e-5
+    assert rel_err(db, dl.sum(0)) < 1e-5
+
+
+def test_colsum_and_embed_grads():
+    g = torch.Generator().manual_seed(10)
+    rows, cols = 3000, 776
+    x = _rand_bf16((rows, cols), g)
+    out = torch.empty(cols, device=dev())
+    K.colsum_bf16(x, cols, out, rows, cols)
+    assert rel_err(out, x.float().sum(0)) < 1e-5
+    Bn, T, D = 5, 17, 64
+    gx = torch.randn((Bn, T, D), generator=g).to(dev())
+    g_cls = torch.empty(D, device=dev())
+    g_pos = torch.empty((T, D), device=dev())
+    g_b = torch.empty(D, device=dev())
+    K.embed_param_grads(gx, g_cls, g_pos, g_b, Bn, T, D, 0.0, 0, 0)
+    assert rel_err(g_pos, gx.sum(0)) < 1e-6
+    assert rel_err(g_cls, gx[:, 0].sum(0)) < 1e-6
+    assert rel_err(g_b, gx[:, 1:].sum((0, 1))) < 1e-5
+    gy = torch.empty((Bn * (T - 1), D), dtype=torch.bfloat16, device=dev())
+    K.patch_grad_rows(gx, gy, Bn, T, D, 0.0, 0, 0)
+    assert torch.equal(gy.float(), gx[:, 1:].reshape(-1, D).to(torch.bfloat16).float())
