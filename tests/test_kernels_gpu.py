@@ -24,38 +24,38 @@ def _rand_bf16(shape, gen, scale=1.0):
     return (torch.randn(shape, generator=gen, device="cpu") * scale).to(torch.bfloat16).to(dev())
 
 
-@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 512, 768), (200, 328, 200), (1024, 768, 3072), (6304, 2304, 768)])
-def test_gemm_nt_bias(M, N, K):
+@pytest.mark.parametrize("M,N,Kd", [(128, 256, 64), (256, 512, 768), (200, 328, 200), (1024, 768, 3072), (6304, 2304, 768)])
+def test_gemm_nt_bias(M, N, Kd):
     g = torch.Generator().manual_seed(1)
-    A = _rand_bf16((M, K), g)
-    B = _rand_bf16((N, K), g, 0.05)
+    A = _rand_bf16((M, Kd), g)
+    B = _rand_bf16((N, Kd), g, 0.05)
     bias = torch.randn(N, generator=g).to(dev())
     C = torch.empty((M, N), dtype=torch.bfloat16, device=dev())
-    K.gemm(K.OP_NT, K.EPI_BF16, M, N, K, A, K, B, K, C, N, bias=bias)
+    K.gemm(K.OP_NT, K.EPI_BF16, M, N, Kd, A, Kd, B, Kd, C, N, bias=bias)
     ref = A.float() @ B.float().t() + bias
     # bf16 output rounding: 2^-9 relative per element
     assert rel_err(C, ref) < 4e-3
     assert (C.float() - ref).abs().max().item() < 0.05 * ref.abs().max().item() + 1e-2
 
 
-@pytest.mark.parametrize("M,N,K", [(256, 256, 128), (200, 328, 200), (6304, 768, 2304)])
-def test_gemm_nn(M, N, K):
+@pytest.mark.parametrize("M,N,Kd", [(256, 256, 128), (200, 328, 200), (6304, 768, 2304)])
+def test_gemm_nn(M, N, Kd):
     g = torch.Generator().manual_seed(2)
-    A = _rand_bf16((M, K), g)
-    B = _rand_bf16((K, N), g, 0.05)
+    A = _rand_bf16((M, Kd), g)
+    B = _rand_bf16((Kd, N), g, 0.05)
     C = torch.empty((M, N), dtype=torch.bfloat16, device=dev())
-    K.gemm(K.OP_NN, K.EPI_BF16, M, N, K, A, K, B, N, C, N)
+    K.gemm(K.OP_NN, K.EPI_BF16, M, N, Kd, A, Kd, B, N, C, N)
     ref = A.float() @ B.float()
     assert rel_err(C, ref) < 4e-3
 
 
-@pytest.mark.parametrize("M,N,K,split", [(256, 256, 128, 1), (200, 328, 264, 2), (768, 3072, 6304, 8), (2304, 768, 6304, 5)])
-def test_gemm_tn_accum(M, N, K, split):
+@pytest.mark.parametrize("M,N,Kd,split", [(256, 256, 128, 1), (200, 328, 264, 2), (768, 3072, 6304, 8), (2304, 768, 6304, 5)])
+def test_gemm_tn_accum(M, N, Kd, split):
     g = torch.Generator().manual_seed(3)
-    A = _rand_bf16((K, M), g)
-    B = _rand_bf16((K, N), g, 0.05)
+    A = _rand_bf16((Kd, M), g)
+    B = _rand_bf16((Kd, N), g, 0.05)
     C = torch.ones((M, N), dtype=torch.float32, device=dev())
-    K.gemm(K.OP_TN, K.EPI_ACCUM, M, N, K, A, M, B, N, C, N, split_k=split)
+    K.gemm(K.OP_TN, K.EPI_ACCUM, M, N, Kd, A, M, B, N, C, N, split_k=split)
     ref = A.float().t() @ B.float() + 1.0
     assert rel_err(C, ref) < 1e-4
 
