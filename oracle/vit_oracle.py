@@ -64,7 +64,9 @@ def dropout(x: Tensor, p: float, training: bool, generator: Optional[torch.Gener
     """nn.Dropout: zero with probability p, scale survivors by 1/(1-p) (models/vit.py:43,122,125)."""
     if not training or p <= 0.0:
         return x
-    keep = (torch.rand(x.shape, generator=generator) >= p).to(x.dtype)
+    # same generator consumption as ATen's CPU native_dropout (a bernoulli_(1-p) mask), so that with the same
+    # torch.manual_seed the oracle reproduces the reference's train-mode outputs, e.g. the notebook KAT
+    keep = torch.empty_like(x).bernoulli_(1.0 - p, generator=generator)
     return x * keep / (1.0 - p)
 
 

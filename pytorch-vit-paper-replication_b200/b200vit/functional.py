@@ -1,0 +1,423 @@
+"""Autograd glue between the reference-shaped nn.Modules and the CUDA kernels.
+
+Each torch.autograd.Function below is pure orchestration: it allocates output / saved buffers with torch,
+then calls the C ABI (b200vit.kernels). Forward and backward arithmetic all happens in libb200vit.so.
+
+Data layout in HBM (R = B*T token rows, D = embedding dim, M = mlp size, H heads of 64):
+  residual stream x ............ f32 [R, D]   (module inputs/outputs are the reference's f32 [B, T, D])
+  LayerNorm output ............. bf16 [R, D]  (A operand of the following GEMM, kept for its weight gradient)
+  packed q/k/v ................. bf16 [R, 3D] = [B, T, 3, H, 64]; attention reads it in place
+  attention output ............. bf16 [R, D]  (+ f32 log-sum-exp [B, H, T])
+  fc1 pre-activation a, h ...... bf16 [R, M] each (a only when a backward pass will follow)
+  weights ...................... f32 master nn.Parameters + bf16 shadows (refreshed by FusedAdam or on demand)
+"""
+from __future__ import annotations
+
+import math
+import weakref
+from typing import List, Optional, Tuple
+
+import torch
+
+from . import kernels as K
+
+LN_EPS = 1e-5  # nn.LayerNorm default, reference models/vit.py:83,115,216
+HEAD_DIM = 64
+
+# ---------------------------------------------------------------------------------------------------------
+# bf16 shadows of fp32 master weights
+# ---------------------------------------------------------------------------------------------------------
+
+
+class _Shadow:
+    __slots__ = ("tensor", "version", "ptr")
+
+    def __init__(self, tensor, version, ptr):
+        self.tensor, self.version, self.ptr = tensor, version, ptr
+
+
+_SHADOWS: "weakref.WeakKeyDictionary[torch.Tensor, _Shadow]" = weakref.WeakKeyDictionary()
+
+
+def bf16_shadow(p: torch.Tensor) -> torch.Tensor:
+    """bf16 copy of a weight, re-cast (by our cast kernel) only when the master changed (version / storage)."""
+    e = _SHADOWS.get(p)
+    ver, ptr = p._version, p.data_ptr()
+    if e is not None and e.version == ver and e.ptr == ptr and e.tensor.device == p.device:
+        return e.tensor
+    src = p.detach()
+    if not src.is_contiguous():
+        src = src.contiguous()
+    dst = e.tensor if (e is not None and e.tensor.shape == p.shape and e.tensor.device == p.device) else None
+    dst = K.cast_bf16(src, dst)
+    _SHADOWS[p] = _Shadow(dst, ver, ptr)
+    return dst
+
+
+def shadow_entry(p: torch.Tensor) -> Optional[_Shadow]:
+    return _SHADOWS.get(p)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# dropout seeds: a mask is a function of (seed, offset, element index); offsets count dropout sites
+# ---------------------------------------------------------------------------------------------------------
+_dropout_calls = 0
+
+
+def next_dropout_key() -> Tuple[int, int]:
+    """(seed, offset) for one dropout site invocation. The seed follows torch.manual_seed()."""
+    global _dropout_calls
+    _dropout_calls += 1
+    return torch.initial_seed() & 0xFFFFFFFFFFFFFFFF, _dropout_calls
+
+
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _require_cuda(t: torch.Tensor, what: str) -> None:
+    if K._C._override is None and not t.is_cuda:
+        raise RuntimeError(f"{what}: b200vit runs on CUDA (sm_100a) only; got a {t.device} tensor. "
+                           f"There is no CPU fallback -- move the model and inputs to 'cuda'.")
+
+
+def _empty(shape, dtype, like: torch.Tensor) -> torch.Tensor:
+    return torch.empty(shape, dtype=dtype, device=like.device)
+
+
+def _zeros(shape, like: torch.Tensor) -> torch.Tensor:
+    return torch.zeros(shape, dtype=torch.float32, device=like.device)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Patch embedding  (reference PatchEmbedding.forward, models/vit.py:45-67)
+# ---------------------------------------------------------------------------------------------------------
+class PatchEmbedFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, img, w, b, cls, pos, w16, patch: int, p_drop: float, training: bool):
+        _require_cuda(img, "PatchEmbedding")
+        img = _f32c(img)
+        bn, c, h, wd = img.shape
+        d = w.shape[0]
+        np_ = (h // patch) * (wd // patch)
+        t = np_ + 1
+        if pos.shape[1] != t:
+            raise RuntimeError(f"image of {h}x{wd} gives {t} tokens but position_embedding has {pos.shape[1]}")
+        kdim = c * patch * patch
+        patches = K.im2col_patches(img, patch)
+        x = _empty((bn, t, d), torch.float32, img)
+        p = float(p_drop) if training else 0.0
+        seed, off = next_dropout_key() if p > 0 else (0, 0)
+        K.gemm(K.OP_NT, K.EPI_PATCH, bn * np_, d, kdim, patches, kdim, w16, kdim, x, d, bias=b, aux=pos, ldaux=d,
+               dropout_p=p, seed=seed, offset=off, row_period=np_)
+        K.class_token_rows(cls, pos, x, bn, t, d, p, seed, off)
+        ctx.save_for_backward(patches)
+        ctx.meta = (bn, t, d, kdim, p, seed, off, w.shape)
+        return x
+
+    @staticmethod
+    def backward(ctx, gx):
+        (patches,) = ctx.saved_tensors
+        bn, t, d, kdim, p, seed, off, wshape = ctx.meta
+        gx = _f32c(gx)
+        g_cls = _empty((1, 1, d), torch.float32, gx)
+        g_pos = _empty((1, t, d), torch.float32, gx)
+        g_b = _empty((d,), torch.float32, gx)
+        K.embed_param_grads(gx, g_cls, g_pos, g_b, bn, t, d, p, seed, off)
+        rows = bn * (t - 1)
+        gy = _empty((rows, d), torch.bfloat16, gx)
+        K.patch_grad_rows(gx, gy, bn, t, d, p, seed, off)
+        gw = _zeros((d, kdim), gx)
+        K.gemm(K.OP_TN, K.EPI_ACCUM, d, kdim, rows, gy, d, patches, kdim, gw, kdim,
+               split_k=K.split_k_for(d, kdim, rows, gx.device))
+        return None, gw.view(wshape), g_b, g_cls, g_pos, None, None, None, None
+
+
+# ---------------------------------------------------------------------------------------------------------
+# MSA / MLP halves of an encoder block (reference models/vit.py:92-98, 128-131, 166-169)
+# ---------------------------------------------------------------------------------------------------------
+def _msa_forward(x2d, bn, t, heads, ln_w, ln_b, w_in16, b_in, w_out16, b_out, residual):
+    r, d = x2d.shape
+    if d != heads * HEAD_DIM:
+        raise NotImplementedError(f"b200vit attention kernels need head_dim == 64 (embedding_dim {d}, heads {heads})")
+    ln = _empty((r, d), torch.bfloat16, x2d)
+    mean = _empty((r,), torch.float32, x2d)
+    rstd = _empty((r,), torch.float32, x2d)
+    K.layernorm_fwd(x2d, d, ln_w, ln_b, ln, None, mean, rstd, r, d, LN_EPS)
+    qkv = _empty((r, 3 * d), torch.bfloat16, x2d)
+    K.gemm(K.OP_NT, K.EPI_BF16, r, 3 * d, d, ln, d, w_in16, d, qkv, 3 * d, bias=b_in)
+    o = _empty((r, d), torch.bfloat16, x2d)
+    lse = _empty((bn, heads, t), torch.float32, x2d)
+    K.attention_fwd(qkv, o, lse, bn, t, heads, HEAD_DIM, 1.0 / math.sqrt(HEAD_DIM))
+    y = _empty((r, d), torch.float32, x2d)
+    K.gemm(K.OP_NT, K.EPI_BIAS_RES, r, d, d, o, d, w_out16, d, y, d, bias=b_out, aux=residual, ldaux=d)
+    return y, (x2d, mean, rstd, ln, qkv, o, lse)
+
+
+def _msa_backward(g, saved, bn, t, heads, ln_w, w_in16, w_out16, has_residual, g16=None, db_out=None):
+    x2d, mean, rstd, ln, qkv, o, lse = saved
+    r, d = x2d.shape
+    dev = x2d.device
+    if g16 is None:
+        g16 = _empty((r, d), torch.bfloat16, x2d)
+        db_out = _empty((d,), torch.float32, x2d)
+        K.dropout_cast(g, g16, db_out, r, d, 0.0, 0, 0)
+    dw_out = _zeros((d, d), x2d)
+    K.gemm(K.OP_TN, K.EPI_ACCUM, d, d, r, g16, d, o, d, dw_out, d, split_k=K.split_k_for(d, d, r, dev))
+    do = _empty((r, d), torch.bfloat16, x2d)
+    K.gemm(K.OP_NN, K.EPI_BF16, r, d, d, g16, d, w_out16, d, do, d)
+    delta = _empty((bn, heads, t), torch.float32, x2d)
+    dqkv = _empty((r, 3 * d), torch.bfloat16, x2d)
+    K.attention_bwd(qkv, o, do, lse, delta, dqkv, bn, t, heads, HEAD_DIM, 1.0 / math.sqrt(HEAD_DIM))
+    db_in = _empty((3 * d,), torch.float32, x2d)
+    K.colsum_bf16(dqkv, 3 * d, db_in, r, 3 * d)
+    dw_in = _zeros((3 * d, d), x2d)
+    K.gemm(K.OP_TN, K.EPI_ACCUM, 3 * d, d, r, dqkv, 3 * d, ln, d, dw_in, d, split_k=K.split_k_for(3 * d, d, r, dev))
+    dln = _empty((r, d), torch.bfloat16, x2d)
+    K.gemm(K.OP_NN, K.EPI_BF16, r, d, 3 * d, dqkv, 3 * d, w_in16, d, dln, d)
+    gx = _empty((r, d), torch.float32, x2d)
+    dgamma = _empty((d,), torch.float32, x2d)
+    dbeta = _empty((d,), torch.float32, x2d)
+    K.layernorm_bwd(dln, None, x2d, d, mean, rstd, ln_w, g if has_residual else None, gx, d, None, dgamma, dbeta,
+                    None, r, d)
+    return gx, (dgamma, dbeta, dw_in, db_in, dw_out, db_out)
+
+
+def _mlp_forward(x2d, ln_w, ln_b, w1_16, b1, w2_16, b2, p, residual, keep_preact):
+    r, d = x2d.shape
+    m = w1_16.shape[0]
+    ln = _empty((r, d), torch.bfloat16, x2d)
+    mean = _empty((r,), torch.float32, x2d)
+    rstd = _empty((r,), torch.float32, x2d)
+    K.layernorm_fwd(x2d, d, ln_w, ln_b, ln, None, mean, rstd, r, d, LN_EPS)
+    key1 = next_dropout_key() if p > 0 else (0, 0)
+    key2 = next_dropout_key() if p > 0 else (0, 0)
+    a = _empty((r, m), torch.bfloat16, x2d) if keep_preact else None
+    h = _empty((r, m), torch.bfloat16, x2d)
+    K.gemm(K.OP_NT, K.EPI_BIAS_GELU, r, m, d, ln, d, w1_16, d, a, m, C2=h, ldc2=m, bias=b1, dropout_p=p,
+           seed=key1[0], offset=key1[1])
+    y = _empty((r, d), torch.float32, x2d)
+    K.gemm(K.OP_NT, K.EPI_BIAS_RES, r, d, m, h, m, w2_16, m, y, d, bias=b2, aux=residual, ldaux=d, dropout_p=p,
+           seed=key2[0], offset=key2[1])
+    return y, (x2d, mean, rstd, ln, a, h), (p, key1, key2)
+
+
+def _mlp_backward(g, saved, drop, ln_w, w1_16, w2_16, has_residual, want_bf16_out):
+    x2d, mean, rstd, ln, a, h = saved
+    p, key1, key2 = drop
+    r, d = x2d.shape
+    m = w1_16.shape[0]
+    dev = x2d.device
+    g16 = _empty((r, d), torch.bfloat16, x2d)
+    db2 = _empty((d,), torch.float32, x2d)
+    K.dropout_cast(g, g16, db2, r, d, p, key2[0], key2[1])
+    dw2 = _zeros((d, m), x2d)
+    K.gemm(K.OP_TN, K.EPI_ACCUM, d, m, r, g16, d, h, m, dw2, m, split_k=K.split_k_for(d, m, r, dev))
+    da = _empty((r, m), torch.bfloat16, x2d)
+    K.gemm(K.OP_NN, K.EPI_DGELU, r, m, d, g16, d, w2_16, m, da, m, aux=a, ldaux=m, dropout_p=p, seed=key1[0],
+           offset=key1[1])
+    db1 = _empty((m,), torch.float32, x2d)
+    K.colsum_bf16(da, m, db1, r, m)
+    dw1 = _zeros((m, d), x2d)
+    K.gemm(K.OP_TN, K.EPI_ACCUM, m, d, r, da, m, ln, d, dw1, d, split_k=K.split_k_for(m, d, r, dev))
+    dln = g16  # reuse: g16 is dead after the two GEMMs above (same shape / dtype)
+    K.gemm(K.OP_NN, K.EPI_BF16, r, d, m, da, m, w1_16, d, dln, d)
+    gx = _empty((r, d), torch.float32, x2d)
+    dgamma = _empty((d,), torch.float32, x2d)
+    dbeta = _empty((d,), torch.float32, x2d)
+    gx16 = _empty((r, d), torch.bfloat16, x2d) if want_bf16_out else None
+    dbn = _empty((d,), torch.float32, x2d) if want_bf16_out else None
+    K.layernorm_bwd(dln, None, x2d, d, mean, rstd, ln_w, g if has_residual else None, gx, d, gx16, dgamma, dbeta,
+                    dbn, r, d)
+    return gx, (dgamma, dbeta, dw1, db1, dw2, db2), gx16, dbn
+
+
+class MSAFn(torch.autograd.Function):
+    """MultiHeadSelfAttentionBlock.forward (models/vit.py:92-98): LN -> self-attention, no residual."""
+
+    @staticmethod
+    def forward(ctx, x, ln_w, ln_b, w_in, b_in, w_out, b_out, w_in16, w_out16, heads: int):
+        _require_cuda(x, "MultiHeadSelfAttentionBlock")
+        x = _f32c(x)
+        bn, t, d = x.shape
+        y, saved = _msa_forward(x.view(bn * t, d), bn, t, heads, ln_w, ln_b, w_in16, b_in, w_out16, b_out, None)
+        ctx.save_for_backward(ln_w, w_in16, w_out16, *saved)
+        ctx.meta = (bn, t, heads)
+        return y.view(bn, t, d)
+
+    @staticmethod
+    def backward(ctx, g):
+        ln_w, w_in16, w_out16, *saved = ctx.saved_tensors
+        bn, t, heads = ctx.meta
+        d = g.shape[-1]
+        gx, (dgam, dbet, dw_in, db_in, dw_out, db_out) = _msa_backward(
+            _f32c(g).view(bn * t, d), tuple(saved), bn, t, heads, ln_w, w_in16, w_out16, has_residual=False)
+        return gx.view(bn, t, d), dgam, dbet, dw_in, db_in, dw_out, db_out, None, None, None
+
+
+class MLPFn(torch.autograd.Function):
+    """MLPBlock.forward (models/vit.py:128-131): LN -> Linear -> GELU -> Dropout -> Linear -> Dropout."""
+
+    @staticmethod
+    def forward(ctx, x, ln_w, ln_b, w1, b1, w2, b2, w1_16, w2_16, p: float, training: bool):
+        _require_cuda(x, "MLPBlock")
+        x = _f32c(x)
+        shape = x.shape
+        d = shape[-1]
+        x2d = x.view(-1, d)
+        needs_bwd = any(ctx.needs_input_grad)
+        y, saved, drop = _mlp_forward(x2d, ln_w, ln_b, w1_16, b1, w2_16, b2, float(p) if training else 0.0, None,
+                                      keep_preact=needs_bwd)
+        if needs_bwd:
+            ctx.save_for_backward(ln_w, w1_16, w2_16, *saved)
+        ctx.drop = drop
+        return y.view(shape)
+
+    @staticmethod
+    def backward(ctx, g):
+        ln_w, w1_16, w2_16, *saved = ctx.saved_tensors
+        shape = g.shape
+        d = shape[-1]
+        gx, (dgam, dbet, dw1, db1, dw2, db2), _, _ = _mlp_backward(
+            _f32c(g).view(-1, d), tuple(saved), ctx.drop, ln_w, w1_16, w2_16, has_residual=False, want_bf16_out=False)
+        return gx.view(shape), dgam, dbet, dw1, db1, dw2, db2, None, None, None, None
+
+
+class EncoderBlockFn(torch.autograd.Function):
+    """TransformerEncoderBlock.forward (models/vit.py:166-169) as one autograd node:
+    x1 = msa(x) + x ; x2 = mlp(x1) + x1, with both residual adds fused into GEMM epilogues."""
+
+    @staticmethod
+    def forward(ctx, x, a_ln_w, a_ln_b, w_in, b_in, w_out, b_out, m_ln_w, m_ln_b, w1, b1, w2, b2,
+                w_in16, w_out16, w1_16, w2_16, heads: int, p: float, training: bool):
+        _require_cuda(x, "TransformerEncoderBlock")
+        x = _f32c(x)
+        bn, t, d = x.shape
+        x2d = x.view(bn * t, d)
+        needs_bwd = any(ctx.needs_input_grad)
+        x1, s_msa = _msa_forward(x2d, bn, t, heads, a_ln_w, a_ln_b, w_in16, b_in, w_out16, b_out, x2d)
+        x2, s_mlp, drop = _mlp_forward(x1, m_ln_w, m_ln_b, w1_16, b1, w2_16, b2, float(p) if training else 0.0, x1,
+                                       keep_preact=needs_bwd)
+        if needs_bwd:
+            ctx.save_for_backward(a_ln_w, m_ln_w, w_in16, w_out16, w1_16, w2_16, *s_msa, *s_mlp)
+        ctx.meta = (bn, t, heads, len(s_msa))
+        ctx.drop = drop
+        return x2.view(bn, t, d)
+
+    @staticmethod
+    def backward(ctx, g):
+        a_ln_w, m_ln_w, w_in16, w_out16, w1_16, w2_16, *rest = ctx.saved_tensors
+        bn, t, heads, n_msa = ctx.meta
+        s_msa, s_mlp = tuple(rest[:n_msa]), tuple(rest[n_msa:])
+        d = g.shape[-1]
+        g2 = _f32c(g).view(bn * t, d)
+        g1, (m_dgam, m_dbet, dw1, db1, dw2, db2), g1_16, db_out = _mlp_backward(
+            g2, s_mlp, ctx.drop, m_ln_w, w1_16, w2_16, has_residual=True, want_bf16_out=True)
+        g0, (a_dgam, a_dbet, dw_in, db_in, dw_out, db_out) = _msa_backward(
+            g1, s_msa, bn, t, heads, a_ln_w, w_in16, w_out16, has_residual=True, g16=g1_16, db_out=db_out)
+        return (g0.view(bn, t, d), a_dgam, a_dbet, dw_in, db_in, dw_out, db_out, m_dgam, m_dbet, dw1, db1, dw2, db2,
+                None, None, None, None, None, None, None)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# final LayerNorm (+ classifier head)  (models/vit.py:232-235 ; headless: models/vit_no_classifier.py:225-226)
+# ---------------------------------------------------------------------------------------------------------
+class HeadFn(torch.autograd.Function):
+    """logits = Linear(LayerNorm(x)[:, 0]). Only the class-token row of each image is normalised: the reference
+    normalises all T rows and discards T-1 of them; the result is identical."""
+
+    @staticmethod
+    def forward(ctx, x, ln_w, ln_b, w, b):
+        _require_cuda(x, "ViT head")
+        x = _f32c(x)
+        bn, t, d = x.shape
+        c = w.shape[0]
+        xn = _empty((bn, d), torch.float32, x)
+        mean = _empty((bn,), torch.float32, x)
+        rstd = _empty((bn,), torch.float32, x)
+        K.layernorm_fwd(x, t * d, ln_w, ln_b, None, xn, mean, rstd, bn, d, LN_EPS)
+        logits = _empty((bn, c), torch.float32, x)
+        K.head_fwd(xn, w, b, logits, bn, d, c)
+        ctx.save_for_backward(x, ln_w, w, xn, mean, rstd)
+        return logits
+
+    @staticmethod
+    def backward(ctx, gl):
+        x, ln_w, w, xn, mean, rstd = ctx.saved_tensors
+        bn, t, d = x.shape
+        c = w.shape[0]
+        gl = _f32c(gl)
+        dxn = _empty((bn, d), torch.float32, x)
+        dw = _empty((c, d), torch.float32, x)
+        db = _empty((c,), torch.float32, x)
+        K.head_bwd(xn, w, gl, dxn, dw, db, bn, d, c)
+        gx = _zeros((bn, t, d), x)   # only class-token rows receive gradient
+        dgam = _empty((d,), torch.float32, x)
+        dbet = _empty((d,), torch.float32, x)
+        K.layernorm_bwd(None, dxn, x, t * d, mean, rstd, ln_w, None, gx, t * d, None, dgam, dbet, None, bn, d)
+        return gx, dgam, dbet, dw, db
+
+
+class LayerNormFn(torch.autograd.Function):
+    """Full-sequence nn.LayerNorm with f32 output (headless ViT, models/vit_no_classifier.py:225-226)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        _require_cuda(x, "LayerNorm")
+        x = _f32c(x)
+        d = x.shape[-1]
+        rows = x.numel() // d
+        y = torch.empty_like(x)
+        mean = _empty((rows,), torch.float32, x)
+        rstd = _empty((rows,), torch.float32, x)
+        K.layernorm_fwd(x, d, w, b, None, y, mean, rstd, rows, d, LN_EPS)
+        ctx.save_for_backward(x, w, mean, rstd)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        x, w, mean, rstd = ctx.saved_tensors
+        d = x.shape[-1]
+        rows = x.numel() // d
+        g = _f32c(g)
+        gx = torch.empty_like(x)
+        dgam = _empty((d,), torch.float32, x)
+        dbet = _empty((d,), torch.float32, x)
+        K.layernorm_bwd(None, g, x, d, mean, rstd, w, None, gx, d, None, dgam, dbet, None, rows, d)
+        return gx, dgam, dbet
+
+
+# ---------------------------------------------------------------------------------------------------------
+# fused softmax cross-entropy  (nn.CrossEntropyLoss(), engine.py:53)
+# ---------------------------------------------------------------------------------------------------------
+class CrossEntropyFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target, stats: Optional[dict]):
+        _require_cuda(logits, "CrossEntropyLoss")
+        logits = _f32c(logits)
+        if logits.dim() != 2:
+            raise ValueError("b200vit CrossEntropyLoss expects logits [batch, classes]")
+        if target.dtype != torch.int64:
+            target = target.long()
+        target = target.contiguous()
+        bn, c = logits.shape
+        loss = _empty((1,), torch.float32, logits)
+        need_grad = ctx.needs_input_grad[0]
+        dl = _empty((bn, c), torch.float32, logits) if need_grad else None
+        correct = torch.empty((1,), dtype=torch.int32, device=logits.device)
+        K.softmax_ce(logits, target, loss, dl, correct, bn, c)
+        if stats is not None:
+            stats["correct"] = correct
+            stats["batch"] = bn
+        if need_grad:
+            ctx.save_for_backward(dl)
+        return loss.view(())
+
+    @staticmethod
+    def backward(ctx, g):
+        (dl,) = ctx.saved_tensors
+        out = torch.empty_like(dl)
+        K.scale_by_scalar(dl, _f32c(g).reshape(1), out)
+        return out, None, None
