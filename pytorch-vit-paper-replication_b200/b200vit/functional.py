@@ -30,18 +30,27 @@ HEAD_DIM = 64
 
 
 class _Shadow:
-    __slots__ = ("tensor", "version", "ptr")
+    __slots__ = ("tensor", "version", "ptr", "owner")
 
-    def __init__(self, tensor, version, ptr):
-        self.tensor, self.version, self.ptr = tensor, version, ptr
+    def __init__(self, tensor, version, ptr, owner):
+        self.tensor, self.version, self.ptr, self.owner = tensor, version, ptr, owner
 
 
-_SHADOWS: "weakref.WeakKeyDictionary[torch.Tensor, _Shadow]" = weakref.WeakKeyDictionary()
+# keyed by id(parameter): tensors cannot be WeakKeyDictionary keys (== on tensors is elementwise)
+_SHADOWS: "dict[int, _Shadow]" = {}
+
+
+def _lookup(p: torch.Tensor) -> Optional[_Shadow]:
+    e = _SHADOWS.get(id(p))
+    if e is not None and e.owner() is not p:   # id reused by another object after the old parameter died
+        del _SHADOWS[id(p)]
+        return None
+    return e
 
 
 def bf16_shadow(p: torch.Tensor) -> torch.Tensor:
     """bf16 copy of a weight, re-cast (by our cast kernel) only when the master changed (version / storage)."""
-    e = _SHADOWS.get(p)
+    e = _lookup(p)
     ver, ptr = p._version, p.data_ptr()
     if e is not None and e.version == ver and e.ptr == ptr and e.tensor.device == p.device:
         return e.tensor
@@ -50,12 +59,13 @@ def bf16_shadow(p: torch.Tensor) -> torch.Tensor:
         src = src.contiguous()
     dst = e.tensor if (e is not None and e.tensor.shape == p.shape and e.tensor.device == p.device) else None
     dst = K.cast_bf16(src, dst)
-    _SHADOWS[p] = _Shadow(dst, ver, ptr)
+    key = id(p)
+    _SHADOWS[key] = _Shadow(dst, ver, ptr, weakref.ref(p, lambda _r, k=key: _SHADOWS.pop(k, None)))
     return dst
 
 
 def shadow_entry(p: torch.Tensor) -> Optional[_Shadow]:
-    return _SHADOWS.get(p)
+    return _lookup(p)
 
 
 # ---------------------------------------------------------------------------------------------------------
