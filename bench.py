@@ -1,0 +1,396 @@
+#!/usr/bin/env python
+"""Headline benchmark: ViT-B/16 training images/sec on B200 (BASELINE.json metric), one JSON line on rank 0.
+
+    python bench.py --gpus 1 --steps 20 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...     # the reference's CPU path (oracle port) on the host cores
+
+Workload at N=1: BASELINE.json configs[1] -- ViT-B/16, 3-class head, bf16 GEMM operands / fp32 accumulation,
+batch 256, synthetic 224x224 images, dropout as shipped (0.1 / 0.1 / 0), the notebook's optimizer recipe
+(Adam with coupled L2 0.03 on matrices, warm-up + linear decay stepped per batch, clip at global norm 1) run through
+b200vit.going_modular.engine.train_step. N>1: the same per-GPU batch on every rank (weak scaling) under
+b200vit.dp.DataParallel, gradients summed with NCCL and averaged inside FusedAdam.
+
+A "step" = one optimizer step = one batch through forward, loss, backward, clip, Adam, LR schedule.
+  value : images/sec with the batches already resident in HBM (CUDA-event timed, max over ranks)
+  e2e   : the same metric through the public API with HOST (pinned) batches: the per-step H2D copy and the
+          per-step D2H read of loss/accuracy are inside the timed region
+  roofline : the tcgen05 GEMM kernel (95 % of the FLOPs): algorithmic FLOPs of every GEMM launch of one step /
+             CUDA-event time of those launches replayed back to back in this process, vs the measured bf16 peak
+  cpu_baseline : the oracle port of the reference train_step timed on the host cores (bounded sample)
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+for _p in (str(ROOT / "pytorch-vit-paper-replication_b200"), str(ROOT)):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+METRIC = "ViT-B/16 train images/sec"
+UNIT = "images/sec"
+NOMINAL_BF16_TFLOPS = 2250.0
+
+
+# ---------------------------------------------------------------------------------------------------------
+# FLOP model: 2mnk per GEMM, attention 2*H*T^2*hd per QK^T and per PV, backward = 2x forward
+# except the patch embedding (no image gradient); elementwise work not counted.
+# ---------------------------------------------------------------------------------------------------------
+def train_gflop_per_image(image=224, patch=16, layers=12, d=768, heads=12, mlp=3072, classes=3):
+    t = (image // patch) ** 2 + 1
+    npatch = t - 1
+    hd = d // heads
+    patch_f = 2 * npatch * d * (3 * patch * patch)
+    layer = 2 * t * d * 3 * d + 2 * 2 * heads * t * t * hd + 2 * t * d * d + 2 * 2 * t * d * mlp
+    head = 2 * d * classes
+    fwd = patch_f + layers * layer + head
+    train = 2 * patch_f + 3 * (layers * layer + head)
+    return fwd / 1e9, train / 1e9
+
+
+def gemm_shapes_per_step(batch, image=224, patch=16, layers=12, d=768, mlp=3072):
+    """(op, epi, M, N, K, count) of every tcgen05 GEMM launch in one training step."""
+    from b200vit import kernels as K
+    t = (image // patch) ** 2 + 1
+    r = batch * t
+    rp = batch * (t - 1)
+    kp = 3 * patch * patch
+    L = layers
+    return [
+        ("patch_fwd", K.OP_NT, K.EPI_PATCH, rp, d, kp, 1), ("patch_wgrad", K.OP_TN, K.EPI_ACCUM, d, kp, rp, 1),
+        ("qkv_fwd", K.OP_NT, K.EPI_BF16, r, 3 * d, d, L), ("proj_fwd", K.OP_NT, K.EPI_BIAS_RES, r, d, d, L),
+        ("fc1_fwd", K.OP_NT, K.EPI_BIAS_GELU, r, mlp, d, L), ("fc2_fwd", K.OP_NT, K.EPI_BIAS_RES, r, d, mlp, L),
+        ("fc2_wgrad", K.OP_TN, K.EPI_ACCUM, d, mlp, r, L), ("fc2_dgrad", K.OP_NN, K.EPI_DGELU, r, mlp, d, L),
+        ("fc1_wgrad", K.OP_TN, K.EPI_ACCUM, mlp, d, r, L), ("fc1_dgrad", K.OP_NN, K.EPI_BF16, r, d, mlp, L),
+        ("proj_wgrad", K.OP_TN, K.EPI_ACCUM, d, d, r, L), ("proj_dgrad", K.OP_NN, K.EPI_BF16, r, d, d, L),
+        ("qkv_wgrad", K.OP_TN, K.EPI_ACCUM, 3 * d, d, r, L), ("qkv_dgrad", K.OP_NN, K.EPI_BF16, r, d, 3 * d, L),
+    ]
+
+
+def measure_gemm_roofline(batch, dev, peaks):
+    """Replay every GEMM launch shape of one step (real epilogues, dropout 0.1 where the step has it) and time each
+    with CUDA events on the launching stream."""
+    from b200vit import kernels as K
+    total_flops = 0.0
+    total_ms = 0.0
+    detail = {}
+    for name, op, epi, M, N, Kd, count in gemm_shapes_per_step(batch):
+        if op == K.OP_NT:
+            A = torch.randn(M, Kd, device=dev).bfloat16(); B = torch.randn(N, Kd, device=dev).bfloat16(); lda, ldb = Kd, Kd
+        elif op == K.OP_NN:
+            A = torch.randn(M, Kd, device=dev).bfloat16(); B = torch.randn(Kd, N, device=dev).bfloat16(); lda, ldb = Kd, N
+        else:
+            A = torch.randn(Kd, M, device=dev).bfloat16(); B = torch.randn(Kd, N, device=dev).bfloat16(); lda, ldb = M, N
+        f32 = epi in (K.EPI_BIAS_RES, K.EPI_ACCUM, K.EPI_PATCH)
+        rows_out = M + M // 196 + 1 if epi == K.EPI_PATCH else M
+        C = torch.zeros(rows_out, N, device=dev, dtype=torch.float32 if f32 else torch.bfloat16)
+        C2 = torch.empty(M, N, device=dev, dtype=torch.bfloat16) if epi == K.EPI_BIAS_GELU else None
+        bias = torch.randn(N, device=dev) if op == K.OP_NT else None
+        aux, ldaux, period, p = None, 0, 0, 0.0
+        if epi == K.EPI_BIAS_RES:
+            aux, ldaux = torch.randn(M, N, device=dev), N
+        if epi == K.EPI_DGELU:
+            aux, ldaux = torch.randn(M, N, device=dev).bfloat16(), N
+        if epi == K.EPI_PATCH:
+            aux, ldaux, period = torch.randn(197, N, device=dev), N, 196
+        if name in ("fc1_fwd", "fc2_fwd", "fc2_dgrad", "patch_fwd"):
+            p = 0.1
+        split = K.split_k_for(M, N, Kd, dev) if epi == K.EPI_ACCUM else 1
+
+        def run():
+            K.gemm(op, epi, M, N, Kd, A, lda, B, ldb, C, N, C2=C2, ldc2=N, bias=bias, aux=aux, ldaux=ldaux,
+                   dropout_p=p, seed=1, offset=2, row_period=period, split_k=split)
+        for _ in range(2):
+            run()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 5
+        e0.record()
+        for _ in range(reps):
+            run()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        fl = 2.0 * M * N * Kd
+        detail[name] = {"us": round(ms * 1e3, 1), "tflops": round(fl / ms / 1e9, 1), "launches_per_step": count}
+        total_flops += fl * count
+        total_ms += ms * count
+        del A, B, C, C2, aux
+    achieved = total_flops / total_ms / 1e9
+    peak = peaks.get("bf16_tflops_sustained") or 1400.0
+    return {
+        "bound": "tensor", "achieved": round(achieved, 1), "peak": peak, "unit": "TFLOP/s",
+        "frac": round(achieved / peak, 4), "traffic": None,
+        "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)" if "bf16_tflops_sustained" in peaks
+        else "B200_PROFILING.md fallback 1.4 PFLOP/s sustained (of fallback)",
+        "kernel": "gemm_tcgen05_kernel (all %d GEMM launches of one step, FLOP-weighted)" % sum(
+            c for *_, c in gemm_shapes_per_step(batch)),
+        "gemm_ms_per_step": round(total_ms, 3), "per_shape": detail,
+    }
+
+
+# ---------------------------------------------------------------------------------------------------------
+# clocks
+# ---------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        # median over the samples taken under load (upper half of the clock samples)
+        busy = sorted(sm)[len(sm) // 2:] if sm else []
+        return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# CPU baseline = oracle port of the reference train_step
+# ---------------------------------------------------------------------------------------------------------
+def cpu_reference_steps(steps: int, warmup: int, batch: int = 32):
+    """Time the oracle restatement of engine.train_step (reference recipe, dropout as shipped) on the host cores."""
+    from oracle import vit_oracle as O
+    from b200vit.models.vit import ViT        # constructor only (parameter init); no b200vit compute runs here
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(42)
+    sd = ViT(num_classes=3).state_dict()
+    cfg = O.ViTConfig(num_classes=3)
+    tr = O.OracleTrainer(sd, cfg, total_steps=1000)
+    g = torch.Generator().manual_seed(0)
+    X = torch.rand(batch, 3, 224, 224, generator=g)
+    y = torch.randint(0, 3, (batch,), generator=g)
+    for _ in range(warmup):
+        tr.step(X, y, training_dropout=True)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        tr.step(X, y, training_dropout=True)
+    dt = time.perf_counter() - t0
+    return {"value": round(batch * steps / dt, 3), "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{steps} train steps of batch {batch} (ViT-B/16 3-class fp32, dropout 0.1/0.1/0, after {warmup} warm-up)",
+            "s_per_step": round(dt / steps, 3)}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps = max(1, min(args.steps, 3))
+    warmup = 1 if args.warmup > 0 else 0
+    cb = cpu_reference_steps(steps, warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": round(cb["s_per_step"] * 1e3, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "ViT-B/16 3-class training step (reference recipe) on host cores, bounded sample: batch 32 "
+                               "per step", "batch_per_step": 32},
+        "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200vit", choices=["b200vit", "reference"])
+    ap.add_argument("--batch", type=int, default=256, help="per-GPU batch")
+    ap.add_argument("--classes", type=int, default=3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-roofline", action="store_true")
+    args = ap.parse_args()
+
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+
+    import torch.distributed as dist
+    from b200vit import _C
+    from b200vit.going_modular import engine
+    from b200vit.models.vit import ViT
+    from b200vit.nn import CrossEntropyLoss
+    from b200vit.optim import FusedAdam
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        sys.exit("bench.py needs a CUDA device: b200vit has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    W = max(3, args.warmup)
+    K_steps = args.steps
+    B = args.batch
+
+    peaks = {}
+    pk = ROOT / "MEASURED_PEAKS.json"
+    if pk.exists():
+        try:
+            peaks = json.loads(pk.read_text())
+        except Exception:
+            peaks = {}
+
+    torch.manual_seed(42)
+    model = ViT(num_classes=args.classes).to(dev)      # dropout as shipped: 0.1 / 0.1 / 0
+    net = model
+    if world > 1:
+        from b200vit.dp import DataParallel
+        net = DataParallel(model)
+    decay, no_decay = [], []
+    for name, p in model.named_parameters():
+        (no_decay if (p.ndim == 1 or name.endswith(".bias")) else decay).append(p)
+    opt = FusedAdam([{"params": decay, "weight_decay": 0.03}, {"params": no_decay, "weight_decay": 0.0}], lr=1e-3)
+    if world > 1:
+        opt.grad_scale = net.grad_scale
+    total = 2 * (W + K_steps) + 8
+    warm_n = int(0.05 * total)
+    sched = torch.optim.lr_scheduler.SequentialLR(opt, schedulers=[
+        torch.optim.lr_scheduler.LinearLR(opt, start_factor=1e-6, end_factor=1.0, total_iters=max(1, warm_n)),
+        torch.optim.lr_scheduler.LinearLR(opt, start_factor=1.0, end_factor=0.0, total_iters=total - warm_n)],
+        milestones=[max(1, warm_n)])
+    loss_fn = CrossEntropyLoss()
+
+    g = torch.Generator().manual_seed(1234 + rank)
+    n_pool = 4   # distinct host batches, cycled
+    host = [(torch.rand(B, 3, 224, 224, generator=g).pin_memory(), torch.randint(0, args.classes, (B,), generator=g).pin_memory())
+            for _ in range(n_pool)]
+    resident = [(x.to(dev), y.to(dev)) for x, y in host]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms: float) -> float:
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    # ---- device-resident run ("value") ---------------------------------------------------------------
+    engine.train_step(net, [resident[i % n_pool] for i in range(W)], loss_fn, opt, sched, dev)
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    l0 = _C.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    train_loss, train_acc = engine.train_step(net, [resident[i % n_pool] for i in range(K_steps)], loss_fn, opt, sched, dev)
+    e1.record()
+    barrier()
+    launches = _C.launch_count - l0
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    ms_step = ms_total / K_steps
+    value = world * B * K_steps / (ms_total / 1e3)
+
+    # ---- end-to-end run: host batches, per-step H2D and per-step D2H of the metrics ---------------------
+    for i in range(2):
+        engine.train_step(net, [host[i % n_pool]], loss_fn, opt, sched, dev)
+    barrier()
+    e0.record()
+    for i in range(K_steps):
+        engine.train_step(net, [host[i % n_pool]], loss_fn, opt, sched, dev)   # returns (loss, acc): D2H every step
+    e1.record()
+    barrier()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+    e2e_value = world * B * K_steps / (ms_e2e / 1e3)
+    h2d = B * 3 * 224 * 224 * 4 + B * 8
+    d2h = 8
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    _, train_gf = train_gflop_per_image(classes=args.classes)
+    tflops = value * train_gf / 1e3
+    roof = None
+    if not args.no_roofline:
+        del resident
+        torch.cuda.empty_cache()
+        roof = measure_gemm_roofline(B, dev, peaks)
+        roof["gemm_share_of_step"] = round(roof["gemm_ms_per_step"] / ms_step, 3)
+    cb = None
+    if not args.no_cpu_baseline and world == 1:
+        cb = cpu_reference_steps(steps=2, warmup=1)
+
+    line = {
+        "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": K_steps, "warmup": W,
+        "ms_per_step": round(ms_step, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": f"ViT-B/16 {args.classes}-class bf16 training, batch {B} per GPU x {world} B200 "
+                               f"(BASELINE.json configs[1]{'' if world == 1 else ', weak-scaled data parallel'})",
+                   "global_batch": B * world, "tokens": 197, "parallelism": f"dp{world}",
+                   "dropout": "0.1/0.1/0 as shipped", "optimizer": "FusedAdam (Adam, coupled L2 0.03/0) + clip 1.0 + per-step LR schedule",
+                   "l2": "inputs and activations per step (>1 GB) exceed the 126 MB L2; no explicit flush"},
+        "mfu": {"train_gflop_per_image": round(train_gf, 3), "achieved_tflops_per_gpu": round(tflops / world, 1),
+                "vs_nominal_2250": round(tflops / world / NOMINAL_BF16_TFLOPS, 4),
+                "vs_measured_sustained": round(tflops / world / peaks["bf16_tflops_sustained"], 4) if "bf16_tflops_sustained" in peaks else None},
+        "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": round(ms_e2e / K_steps, 3)},
+        "gpu_launches": launches,
+        "clocks": clocks,
+        "roofline": roof,
+        "cpu_baseline": cb,
+        "final_train_loss": round(train_loss, 4),
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

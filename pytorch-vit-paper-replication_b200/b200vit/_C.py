@@ -106,5 +106,12 @@ def check(rc: int, what: str) -> None:
         raise RuntimeError(f"{what} failed (code {rc}): {msg}")
 
 
+# CUDA kernels launched by one successful call of each entry point (memsets are not counted).
+KERNELS_PER_CALL = {"b200vit_attention_bwd": 3, "b200vit_l2norm_sq": 2, "b200vit_head_bwd": 2}
+launch_count = 0
+
+
 def call(name: str, *args) -> None:
+    global launch_count
     check(getattr(lib(), name)(*args), name)
+    launch_count += KERNELS_PER_CALL.get(name, 1)

@@ -1,0 +1,132 @@
+"""Plain data parallelism for the training step: one process per GPU, full replica per rank, one bucketed
+gradient all-reduce per optimizer step overlapped with the rest of backward.
+
+The reference has no distributed code at all (single `model.to(device)`, going_modular/engine.py:180); this
+wrapper is the one exchange step that data-parallel training of its hot path needs. It is module-agnostic:
+
+    model = DataParallel(ViT(...).to(dev))          # broadcasts rank 0's weights
+    opt = FusedAdam(model.parameters(), ...); opt.grad_scale = model.grad_scale   # = 1/world (sum -> mean)
+    engine.train_step(model, loader, loss_fn, opt, sched, dev)                    # unchanged
+
+Mechanics
+  * parameters are grouped, in reverse registration order (~ the order backward produces gradients), into
+    buckets of ~`bucket_mb` MB backed by one flat fp32 buffer each;
+  * a post-accumulate-grad hook moves each fresh gradient into its slice of the bucket and makes `p.grad` a
+    view of that slice (so the reduced values are seen by clip_grad_norm_ / any optimizer without a copy back);
+  * when a bucket is complete its flat buffer is all-reduced (SUM) asynchronously: NCCL runs it on its own
+    stream behind the gradients already produced, while backward keeps going;
+  * an end-of-backward engine callback waits for the outstanding reductions, so gradients are final when
+    `loss.backward()` returns (the reference engine calls clip_grad_norm_ right after, engine.py:60-63).
+Gradients hold the SUM over ranks; `grad_scale` (1/world) is applied by FusedAdam on the fly, or call
+`average_gradients()` before a stock optimizer.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+from torch import nn
+
+
+class _Bucket:
+    def __init__(self, params: List[nn.Parameter]):
+        self.params = params
+        n = sum(p.numel() for p in params)
+        self.flat = torch.zeros(n, dtype=params[0].dtype, device=params[0].device)
+        self.views = []
+        off = 0
+        for p in params:
+            self.views.append(self.flat[off:off + p.numel()].view(p.shape))
+            off += p.numel()
+        self.pending = len(params)
+        self.work = None
+
+
+class DataParallel(nn.Module):
+    def __init__(self, module: nn.Module, process_group=None, bucket_mb: float = 25.0, broadcast: bool = True):
+        super().__init__()
+        if not dist.is_initialized():
+            raise RuntimeError("DataParallel needs torch.distributed to be initialised (one process per GPU)")
+        self.module = module
+        self.group = process_group
+        self.world = dist.get_world_size(process_group)
+        self.grad_scale = 1.0 / self.world
+        self.sync = True
+        if broadcast:
+            for t in list(module.parameters()) + list(module.buffers()):
+                dist.broadcast(t.data, src=dist.get_global_rank(process_group, 0) if process_group else 0,
+                               group=process_group)
+        params = [p for p in module.parameters() if p.requires_grad]
+        limit = int(bucket_mb * 1024 * 1024)
+        self.buckets: List[_Bucket] = []
+        cur, cur_bytes = [], 0
+        for p in reversed(params):
+            cur.append(p)
+            cur_bytes += p.numel() * p.element_size()
+            if cur_bytes >= limit:
+                self.buckets.append(_Bucket(cur))
+                cur, cur_bytes = [], 0
+        if cur:
+            self.buckets.append(_Bucket(cur))
+        self._where = {}
+        for b in self.buckets:
+            for i, p in enumerate(b.params):
+                self._where[p] = (b, i)
+                p.register_post_accumulate_grad_hook(self._on_grad)
+        self._callback_queued = False
+
+    # -- hooks ---------------------------------------------------------------------------------------
+    def _on_grad(self, p: nn.Parameter) -> None:
+        b, i = self._where[p]
+        view = b.views[i]
+        if p.grad.data_ptr() != view.data_ptr():
+            view.copy_(p.grad)
+            p.grad = view
+        if not self.sync:
+            return
+        if not self._callback_queued:
+            torch.autograd.Variable._execution_engine.queue_callback(self._finish)
+            self._callback_queued = True
+        b.pending -= 1
+        if b.pending == 0:
+            b.work = dist.all_reduce(b.flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+
+    def _finish(self) -> None:
+        for b in self.buckets:
+            if b.work is None and b.pending != len(b.params):
+                # some parameters of this bucket got no gradient this step: reduce what is there (others are zero)
+                for p, v in zip(b.params, b.views):
+                    if p.grad is None:
+                        v.zero_()
+                b.work = dist.all_reduce(b.flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        for b in self.buckets:
+            if b.work is not None:
+                b.work.wait()
+                b.work = None
+            b.pending = len(b.params)
+        self._callback_queued = False
+
+    # -- API -----------------------------------------------------------------------------------------
+    def forward(self, *args, **kwargs):
+        return self.module(*args, **kwargs)
+
+    def average_gradients(self) -> None:
+        """Turn the summed gradients into means (only needed with optimizers that have no grad_scale)."""
+        for b in self.buckets:
+            b.flat.mul_(self.grad_scale)
+
+    class _NoSync:
+        def __init__(self, dp):
+            self.dp = dp
+
+        def __enter__(self):
+            self.prev = self.dp.sync
+            self.dp.sync = False
+
+        def __exit__(self, *a):
+            self.dp.sync = self.prev
+
+    def no_sync(self):
+        """Context manager: accumulate gradients locally without communication (gradient accumulation)."""
+        return DataParallel._NoSync(self)
