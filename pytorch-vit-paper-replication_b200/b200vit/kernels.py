@@ -53,11 +53,8 @@ def sm_count(device) -> int:
 
 
 def split_k_for(m: int, n: int, k: int, device=None) -> int:
-    """Split-K factor for weight-gradient GEMMs: enough (tile, split) work items to fill every SM ~2 times."""
-    tiles = math.ceil(m / 128) * math.ceil(n / 256)
-    kblocks = math.ceil(k / 64)
-    want = max(1, (2 * sm_count(device or "cuda")) // tiles)
-    return max(1, min(want, kblocks // 4 if kblocks >= 8 else 1))
+    """Split-K factor for weight-gradient GEMMs: 0 = let the library pick (enough work items for ~2 waves)."""
+    return 0
 
 
 def gemm(op: int, epi: int, M: int, N: int, K: int, A: torch.Tensor, lda: int, B: torch.Tensor, ldb: int,

@@ -20,6 +20,7 @@
 
 #include <cudaTypedefs.h>
 #include <mutex>
+#include <stdlib.h>
 
 namespace b200vit {
 
@@ -37,6 +38,14 @@ constexpr int NUM_EPI_WARPS = 8;
 constexpr int GEMM_THREADS = 128 + NUM_EPI_WARPS * 32;
 constexpr int TMEM_COLS = 512;
 constexpr int GEMM_SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+
+// 2-CTA (cta_group::2) variant: a CTA pair owns a 256x256 output tile. Each CTA stages its own 128 rows of A and
+// HALF of the B tile (128 of the 256 N-rows); the pair's tensor cores read both halves, so every CTA moves
+// 32 KB per k-block instead of 48 KB (1.5x less L2->smem and smem traffic per FLOP) and the ring gets 6 stages.
+constexpr int STAGES2 = 6;
+constexpr int B2_STAGE_BYTES = (BN / 2) * BK * 2;   // 16 KB
+constexpr int STAGE2_BYTES = A_STAGE_BYTES + B2_STAGE_BYTES;
+constexpr int GEMM2_SMEM_BYTES = STAGES2 * STAGE2_BYTES + 1024 + 256;
 
 enum GemmOp { OP_NT = 0, OP_NN = 1, OP_TN = 2 };
 enum GemmEpi {
@@ -374,6 +383,175 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
 }
 
+
+// -------------------------------------------------------------------------------------------------
+// The 2-CTA kernel (cluster of 2, cta_group::2 MMA, UMMA 256x256x16)
+// -------------------------------------------------------------------------------------------------
+template <bool A_MN, bool B_MN, int EPI>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const GemmParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t smem_a = smem_base;
+    const uint32_t smem_b = smem_base + STAGES2 * A_STAGE_BYTES;
+    const uint32_t bar_base = smem_base + STAGES2 * STAGE2_BYTES;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };                       // used in the leader CTA
+    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES2 + s); };          // one per CTA
+    auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * STAGES2 + s); };      // one per CTA
+    auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * STAGES2 + 2 + s); }; // used in the leader CTA
+    const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES2 + 4);
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmA);
+        prefetch_tmap(&tmB);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < STAGES2; ++s) { mbar_init(full_bar(s), 2); mbar_init(empty_bar(s), 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 2 * NUM_EPI_WARPS); }
+        fence_barrier_init();
+    }
+    if (warp == 2) {
+        tmem_alloc<2>(tmem_slot, TMEM_COLS);
+        tmem_relinquish<2>();
+    }
+    tc_fence_before();
+    cluster_sync_all();     // barriers of both CTAs are initialised before any remote arrive / multicast commit
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    const int tiles_m2 = (p.M + 2 * BM - 1) / (2 * BM);
+    const int total_work = tiles_m2 * p.tiles_n * p.splits;
+    const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+
+    auto decode = [&](int w, int& m0, int& n0, int& kb0, int& kb1) {
+        const int tile = w % (tiles_m2 * p.tiles_n);
+        const int split = w / (tiles_m2 * p.tiles_n);
+        n0 = (tile % p.tiles_n) * BN;
+        m0 = (tile / p.tiles_n) * (2 * BM) + (int)rank * BM;     // this CTA's 128 rows of the pair tile
+        kb0 = (int)(((long long)split * p.kblocks) / p.splits);
+        kb1 = (int)(((long long)(split + 1) * p.kblocks) / p.splits);
+    };
+
+    if (warp == 0) {
+        // ===================== TMA producer (both CTAs) =====================
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int w = cluster_id; w < total_work; w += num_clusters) {
+                int m0, n0, kb0, kb1;
+                decode(w, m0, n0, kb0, kb1);
+                const int nb0 = n0 + (int)rank * (BN / 2);           // this CTA's half of the B tile
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(empty_bar(stage), phase ^ 1u);
+                    // all transaction bytes of the pair are counted on the LEADER's barrier
+                    const uint32_t fb = full_bar(stage) & 0xFEFFFFFFu;
+                    if (leader) mbar_arrive_expect_tx(full_bar(stage), 2 * STAGE2_BYTES);
+                    const uint32_t sa = smem_a + stage * A_STAGE_BYTES;
+                    const uint32_t sb = smem_b + stage * B2_STAGE_BYTES;
+                    const int k0 = kb * BK;
+                    if (!A_MN) {
+                        tma_load_2d_2sm(sa, &tmA, fb, k0, m0);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < BM / 64; ++i)
+                            tma_load_2d_2sm(sa + i * (BK * 128), &tmA, fb, m0 + i * 64, k0);
+                    }
+                    if (!B_MN) {
+                        tma_load_2d_2sm(sb, &tmB, fb, k0, nb0);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < (BN / 2) / 64; ++i)
+                            tma_load_2d_2sm(sb + i * (BK * 128), &tmB, fb, nb0 + i * 64, k0);
+                    }
+                    if (!leader) mbar_arrive_cluster(full_bar(stage), 0);
+                    if (++stage == STAGES2) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===================== MMA issuer (leader CTA only) =====================
+        if (lane == 0 && leader) {
+            constexpr uint32_t idesc = make_idesc_bf16(2 * BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+            constexpr uint32_t a_lbo = A_MN ? BK * 128 : 0, b_lbo = B_MN ? BK * 128 : 0;
+            constexpr uint32_t a_kstep = A_MN ? UMMA_K * 128 : UMMA_K * 2;
+            constexpr uint32_t b_kstep = B_MN ? UMMA_K * 128 : UMMA_K * 2;
+            int stage = 0; uint32_t phase = 0;
+            int iter = 0;
+            for (int w = cluster_id; w < total_work; w += num_clusters, ++iter) {
+                int m0, n0, kb0, kb1;
+                decode(w, m0, n0, kb0, kb1);
+                const int acc = iter & 1;
+                const uint32_t acc_phase = (iter >> 1) & 1;
+                mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + acc * BN;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(full_bar(stage), phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_a + stage * A_STAGE_BYTES;
+                    const uint32_t sb = smem_b + stage * B2_STAGE_BYTES;
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) {
+                        const uint64_t da = make_smem_desc_sw128(sa + k * a_kstep, 1024, a_lbo);
+                        const uint64_t db = make_smem_desc_sw128(sb + k * b_kstep, 1024, b_lbo);
+                        umma_bf16<2>(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit_2sm(empty_bar(stage), 0x3);                      // frees the stage in BOTH CTAs
+                    if (kb == kb1 - 1) umma_commit_2sm(tfull_bar(acc), 0x3);     // accumulator ready in BOTH CTAs
+                    if (++stage == STAGES2) { stage = 0; phase ^= 1u; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp >= 4) {
+        // ===================== Epilogue (both CTAs, own 128 rows) =====================
+        const int ew = warp - 4;
+        const int quarter = warp & 3;
+        const int half = ew >> 2;
+        int iter = 0;
+        for (int w = cluster_id; w < total_work; w += num_clusters, ++iter) {
+            int m0, n0, kb0, kb1;
+            decode(w, m0, n0, kb0, kb1);
+            const int acc = iter & 1;
+            const uint32_t acc_phase = (iter >> 1) & 1;
+            mbar_wait(tfull_bar(acc), acc_phase);
+            tc_fence_after();
+            const int row = m0 + quarter * 32 + lane;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                const int col_in_tile = half * 128 + c * 32;
+                const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + col_in_tile);
+                uint32_t r[32];
+                tmem_ld_32x32(taddr, r);
+                tmem_ld_wait();
+                if (c == 3) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(tempty_bar(acc), 0);    // the MMA issuer lives in CTA 0
+                }
+                float v[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+                epilogue_chunk<EPI>(p, row, n0 + col_in_tile, v);
+            }
+        }
+    }
+
+    tc_fence_before();
+    cluster_sync_all();     // nobody leaves (or frees TMEM) while the peer may still read its smem / signal its barriers
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc<2>(tmem_base, TMEM_COLS);
+    }
+}
+
 // -------------------------------------------------------------------------------------------------
 // Host side
 // -------------------------------------------------------------------------------------------------
@@ -424,6 +602,29 @@ static gemm_kernel_t pick_epi(int epi) {
     return nullptr;
 }
 
+template <bool A_MN, bool B_MN>
+static gemm_kernel_t pick_epi_2cta(int epi) {
+    switch (epi) {
+        case EPI_BF16: return gemm_tcgen05_2cta_kernel<A_MN, B_MN, EPI_BF16>;
+        case EPI_BIAS_GELU: return gemm_tcgen05_2cta_kernel<A_MN, B_MN, EPI_BIAS_GELU>;
+        case EPI_BIAS_RES: return gemm_tcgen05_2cta_kernel<A_MN, B_MN, EPI_BIAS_RES>;
+        case EPI_DGELU: return gemm_tcgen05_2cta_kernel<A_MN, B_MN, EPI_DGELU>;
+        case EPI_ACCUM: return gemm_tcgen05_2cta_kernel<A_MN, B_MN, EPI_ACCUM>;
+        case EPI_F32: return gemm_tcgen05_2cta_kernel<A_MN, B_MN, EPI_F32>;
+        case EPI_PATCH: return gemm_tcgen05_2cta_kernel<A_MN, B_MN, EPI_PATCH>;
+    }
+    return nullptr;
+}
+
+static int gemm_mode() {   // B200VIT_GEMM_MODE=1 forces the 1-CTA kernel (debugging / A-B measurements)
+    static int mode = -1;
+    if (mode < 0) {
+        const char* e = getenv("B200VIT_GEMM_MODE");
+        mode = e ? atoi(e) : 0;
+    }
+    return mode;
+}
+
 int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long lda, const void* B, long long ldb,
                 void* C, long long ldc, void* C2, long long ldc2, const float* bias, const void* aux,
                 long long ldaux, float drop_p, unsigned long long seed, unsigned long long offset, int row_period,
@@ -444,7 +645,18 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
     p.tiles_m = (M + BM - 1) / BM;
     p.tiles_n = (N + BN - 1) / BN;
     p.kblocks = (K + BK - 1) / BK;
-    if (splits < 1) splits = 1;
+    const bool two_cta = (M > BM) && gemm_mode() != 1;
+    if (splits <= 0) {
+        // auto: enough (tile, split) work items to fill every SM (or SM pair) about twice
+        splits = 1;
+        if (epi == EPI_ACCUM) {
+            const int units = two_cta ? sm_count() / 2 : sm_count();
+            const int tiles = (two_cta ? (M + 2 * BM - 1) / (2 * BM) : p.tiles_m) * p.tiles_n;
+            splits = (2 * units) / tiles;
+            if (splits > p.kblocks / 4) splits = p.kblocks / 4;
+            if (splits < 1) splits = 1;
+        }
+    }
     if (splits > p.kblocks) splits = p.kblocks;
     B200_CHECK_ARG(splits == 1 || epi == EPI_ACCUM, "gemm: split-K needs the accumulate epilogue");
     p.splits = splits;
@@ -469,20 +681,36 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
     if (!a_mn) rc = make_tmap_bf16(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM);
     else       rc = make_tmap_bf16(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK);
     if (rc) return rc;
-    if (!b_mn) rc = make_tmap_bf16(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, BN);
+    // K-major B box: 256 rows for the 1-CTA kernel, 128 (this CTA's half) for the 2-CTA kernel
+    if (!b_mn) rc = make_tmap_bf16(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, two_cta ? BN / 2 : BN);
     else       rc = make_tmap_bf16(&tmB, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK);
     if (rc) return rc;
 
     gemm_kernel_t kern = nullptr;
-    if (op == OP_NT) kern = pick_epi<false, false>(epi);
-    else if (op == OP_NN) kern = pick_epi<false, true>(epi);
-    else kern = pick_epi<true, true>(epi);
+    if (two_cta) {
+        if (op == OP_NT) kern = pick_epi_2cta<false, false>(epi);
+        else if (op == OP_NN) kern = pick_epi_2cta<false, true>(epi);
+        else kern = pick_epi_2cta<true, true>(epi);
+    } else {
+        if (op == OP_NT) kern = pick_epi<false, false>(epi);
+        else if (op == OP_NN) kern = pick_epi<false, true>(epi);
+        else kern = pick_epi<true, true>(epi);
+    }
     B200_CHECK_ARG(kern != nullptr, "gemm: no kernel for op %d epi %d", op, epi);
 
-    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
-    const int total = p.tiles_m * p.tiles_n * p.splits;
-    const int grid = total < sm_count() ? total : sm_count();
-    kern<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream>>>(tmA, tmB, p);
+    if (two_cta) {
+        B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM2_SMEM_BYTES));
+        const int tiles_m2 = (M + 2 * BM - 1) / (2 * BM);
+        const int total = tiles_m2 * p.tiles_n * p.splits;
+        const int pairs = sm_count() / 2;
+        const int grid = 2 * (total < pairs ? total : pairs);
+        kern<<<grid, GEMM_THREADS, GEMM2_SMEM_BYTES, stream>>>(tmA, tmB, p);   // cluster dims are compiled in
+    } else {
+        B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+        const int total = p.tiles_m * p.tiles_n * p.splits;
+        const int grid = total < sm_count() ? total : sm_count();
+        kern<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream>>>(tmA, tmB, p);
+    }
     B200_LAUNCH_CHECK();
     return 0;
 }

@@ -85,8 +85,8 @@ int layernorm_fwd_launch(const float* x, long long row_stride, const float* gamm
 //                                                                              Linear that produced this residual)
 // NV = float4 chunks per lane (ceil(D / 128)).
 // ---------------------------------------------------------------------------------------------
-template <int NV>
-__global__ void __launch_bounds__(LN_WARPS * 32)
+template <int NV, bool HAS_NEXT>
+__global__ void __launch_bounds__(LN_WARPS * 32, (NV <= 6 && !HAS_NEXT) ? 2 : 1)
 layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__ dy_f32, const float* __restrict__ x,
                      long long row_stride, const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
                      const float* __restrict__ gamma, const float* __restrict__ gin, float* __restrict__ gout,
@@ -97,15 +97,13 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nv = D >> 2;
 
-    float4 g4[NV];
-    float4 acc_g[NV], acc_b[NV], acc_n[NV];
+    const float4* gamma4 = reinterpret_cast<const float4*>(gamma);   // re-read per row (L1-resident) to save registers
+    float4 acc_g[NV], acc_b[NV], acc_n[HAS_NEXT ? NV : 1];
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
-        const int i = lane + 32 * k;
-        g4[k] = (i < nv) ? __ldg(reinterpret_cast<const float4*>(gamma) + i) : make_float4(0, 0, 0, 0);
         acc_g[k] = make_float4(0, 0, 0, 0);
         acc_b[k] = make_float4(0, 0, 0, 0);
-        acc_n[k] = make_float4(0, 0, 0, 0);
+        if (HAS_NEXT) acc_n[k] = make_float4(0, 0, 0, 0);
     }
 
     for (long long row = (long long)blockIdx.x * LN_WARPS + warp; row < rows; row += (long long)gridDim.x * LN_WARPS) {
@@ -126,7 +124,7 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
                 } else {
                     dy[k] = reinterpret_cast<const float4*>(dy_f32 + row * (long long)D)[i];
                 }
-                const float4 g = g4[k];
+                const float4 g = __ldg(gamma4 + i);
                 const float a0 = dy[k].x * g.x, a1 = dy[k].y * g.y, a2 = dy[k].z * g.z, a3 = dy[k].w * g.w;
                 s1 += (a0 + a1) + (a2 + a3);
                 s2 += (a0 * xh[k].x + a1 * xh[k].y) + (a2 * xh[k].z + a3 * xh[k].w);
@@ -141,7 +139,7 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
         for (int k = 0; k < NV; ++k) {
             const int i = lane + 32 * k;
             if (i < nv) {
-                const float4 g = g4[k];
+                const float4 g = __ldg(gamma4 + i);
                 float4 o;
                 o.x = rstd * (dy[k].x * g.x - c1 - xh[k].x * c2);
                 o.y = rstd * (dy[k].y * g.y - c1 - xh[k].y * c2);
@@ -152,7 +150,7 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
                     o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
                 }
                 reinterpret_cast<float4*>(gout + row * gout_stride)[i] = o;
-                if (gout_bf16) {
+                if (HAS_NEXT) {
                     float v[4] = {o.x, o.y, o.z, o.w};
                     if (drop.p > 0.f) {
                         const unsigned long long e0 = (unsigned long long)row * D + 4ull * i;
@@ -171,7 +169,7 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
     }
 
     // block reduction of the three column accumulators, one at a time through the same smem slab
-    auto reduce_store = [&](float4 (&acc)[NV], float* dst) {
+    auto reduce_store = [&](float4* acc, float* dst) {
         __syncthreads();
 #pragma unroll
         for (int k = 0; k < NV; ++k) {
@@ -188,7 +186,7 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
     };
     if (dgamma) reduce_store(acc_g, dgamma);
     if (dbeta) reduce_store(acc_b, dbeta);
-    if (dbias_next && gout_bf16) reduce_store(acc_n, dbias_next);
+    if (HAS_NEXT && dbias_next) reduce_store(acc_n, dbias_next);
 }
 
 int layernorm_bwd_launch(const bf16* dy_bf16, const float* dy_f32, const float* x, long long row_stride,
@@ -206,15 +204,22 @@ int layernorm_bwd_launch(const bf16* dy_bf16, const float* dy_f32, const float* 
     if (dbeta) B200_CUDA(cudaMemsetAsync(dbeta, 0, sizeof(float) * dim, stream));
     if (dbias_next) B200_CUDA(cudaMemsetAsync(dbias_next, 0, sizeof(float) * dim, stream));
     long long blocks = (rows + LN_WARPS - 1) / LN_WARPS;
-    const long long cap = (long long)sm_count() * 4;
+    const long long cap = (long long)sm_count() * 8;
     if (blocks > cap) blocks = cap;
     const DropoutParams drop = make_dropout(drop_p, seed, offset);
     const size_t smem = sizeof(float) * LN_WARPS * dim;
     const int nvl = (dim / 4 + 31) / 32;
 #define LN_BWD_CASE(NV)                                                                                         \
-    layernorm_bwd_kernel<NV><<<(unsigned)blocks, LN_WARPS * 32, smem, stream>>>(                                 \
-        dy_bf16, dy_f32, x, row_stride, mean, rstd, gamma, gin, gout, gout_stride, gout_bf16, dgamma, dbeta,    \
-        dbias_next, rows, dim, drop)
+    do {                                                                                                        \
+        if (gout_bf16)                                                                                          \
+            layernorm_bwd_kernel<NV, true><<<(unsigned)blocks, LN_WARPS * 32, smem, stream>>>(                   \
+                dy_bf16, dy_f32, x, row_stride, mean, rstd, gamma, gin, gout, gout_stride, gout_bf16, dgamma,   \
+                dbeta, dbias_next, rows, dim, drop);                                                            \
+        else                                                                                                    \
+            layernorm_bwd_kernel<NV, false><<<(unsigned)blocks, LN_WARPS * 32, smem, stream>>>(                  \
+                dy_bf16, dy_f32, x, row_stride, mean, rstd, gamma, gin, gout, gout_stride, gout_bf16, dgamma,   \
+                dbeta, dbias_next, rows, dim, drop);                                                            \
+    } while (0)
     if (nvl <= 1) LN_BWD_CASE(1);
     else if (nvl <= 2) LN_BWD_CASE(2);
     else if (nvl <= 4) LN_BWD_CASE(4);
