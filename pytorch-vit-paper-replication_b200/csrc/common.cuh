@@ -61,62 +61,86 @@ __device__ __forceinline__ float2 unpack_bf16(uint32_t v) {
     return __bfloat1622float2(t);
 }
 
-// Exact (erf) GELU and its derivative: nn.GELU() default, reference models/vit.py:121.
+// erf-form GELU and its derivative (nn.GELU() default, reference models/vit.py:121). erf is evaluated with the
+// Abramowitz-Stegun 7.1.26 rational form (|error| <= 1.5e-7, far below the bf16 rounding of every consumer):
+// one MUFU.RCP + one MUFU.EX2 + a 5-term Horner polynomial, no branches. With u = |x|/sqrt(2),
+//   E = exp(-u^2) = exp(-x^2/2),  erf(u) = 1 - poly(t) E,  t = 1/(1 + 0.3275911 u)
+// and the same E gives the Gaussian density needed by the derivative.
+__device__ __forceinline__ float fast_rcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float fast_ex2(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ void gelu_terms(float x, float& one_minus_pe, float& e) {
+    const float u = fabsf(x) * 0.70710678118654752f;
+    const float t = fast_rcp(fmaf(0.3275911f, u, 1.0f));
+    float poly = fmaf(t, 1.061405429f, -1.453152027f);
+    poly = fmaf(poly, t, 1.421413741f);
+    poly = fmaf(poly, t, -0.284496736f);
+    poly = fmaf(poly, t, 0.254829592f);
+    poly *= t;
+    e = fast_ex2(u * u * -1.4426950408889634f);
+    one_minus_pe = fmaf(-poly, e, 1.0f);          // erf(|x|/sqrt2)
+}
 __device__ __forceinline__ float gelu_exact(float x) {
-    return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
+    float erf_abs, e;
+    gelu_terms(x, erf_abs, e);
+    return 0.5f * fmaf(fabsf(x), erf_abs, x);      // 0.5 x (1 + erf(x/sqrt2))
 }
 __device__ __forceinline__ float gelu_exact_grad(float x) {
-    const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
-    const float pdf = 0.3989422804014327f * __expf(-0.5f * x * x);
-    return cdf + x * pdf;
+    float erf_abs, e;
+    gelu_terms(x, erf_abs, e);
+    const float cdf = fmaf(copysignf(0.5f, x), erf_abs, 0.5f);
+    return fmaf(x * 0.3989422804014327f, e, cdf);  // cdf + x pdf
 }
 
 // ---------------------------------------------------------------------------------------------
-// Counter-based dropout mask (Philox4x32-10). One Philox block yields 4x32 random bits = eight
-// 16-bit lanes; element e of a tensor uses block e/8, lane e%8, so any kernel (forward epilogue,
-// backward epilogue, standalone) regenerates the same mask from (seed, offset) alone and no
-// mask tensor is ever stored. keep  <=>  lane16 >= thr16 where thr16 = round(p * 65536).
+// Counter-based dropout mask. Element e of a tensor belongs to block e/8, lane e%8; a block draws 4x32 random
+// bits = eight 16-bit lanes from a 32-bit avalanche hash of (counter ^ key), where key is derived on the host
+// from (seed, offset). Any kernel (forward epilogue, backward epilogue, standalone) regenerates the same mask
+// from (seed, offset) alone, so no mask tensor is ever stored. keep <=> lane16 >= thr16, thr16 = round(p*65536).
 // Semantics mirror nn.Dropout (models/vit.py:43,122,125): kept values are scaled by 1/(1-p).
+// (A 10-round Philox here cost more instructions than the GELU it sits next to in the fc1 epilogue.)
 // ---------------------------------------------------------------------------------------------
 struct DropoutParams {
     float p;            // drop probability; 0 disables
     float scale;        // 1/(1-p)
     uint32_t thr16;     // drop if lane16 < thr16
-    uint64_t seed;
-    uint64_t offset;    // distinguishes dropout sites / steps
+    uint32_t key_lo;    // hash key derived from (seed, offset)
+    uint32_t key_hi;
 };
 
-__device__ __forceinline__ uint4 philox4x32_10(uint64_t seed, uint64_t offset, uint64_t ctr) {
-    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
-    uint32_t c0 = (uint32_t)ctr, c1 = (uint32_t)(ctr >> 32);
-    uint32_t c2 = (uint32_t)offset, c3 = (uint32_t)(offset >> 32);
-#pragma unroll
-    for (int r = 0; r < 10; ++r) {
-        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-        const uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
-        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
-        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
-    }
-    return make_uint4(c0, c1, c2, c3);
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {     // "lowbias32" integer hash
+    x ^= x >> 16; x *= 0x7feb352du;
+    x ^= x >> 15; x *= 0x846ca68bu;
+    x ^= x >> 16;
+    return x;
+}
+__device__ __forceinline__ uint32_t dropout_word(const DropoutParams& d, uint64_t blk, uint32_t j) {
+    const uint32_t ctr = ((uint32_t)blk << 2) | j;
+    const uint32_t hi = (uint32_t)(blk >> 30);              // zero for tensors below 2^33 elements
+    return mix32(ctr ^ d.key_lo ^ (hi * 0x9E3779B9u + (hi ? d.key_hi : 0u)));
 }
 
 // Multipliers (0 or scale) for the 8 consecutive elements [8*blk, 8*blk+8).
 __device__ __forceinline__ void dropout_mult8(const DropoutParams& d, uint64_t blk, float (&m)[8]) {
-    const uint4 r = philox4x32_10(d.seed, d.offset, blk);
-    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        m[2 * i]     = ((w[i] & 0xFFFFu) >= d.thr16) ? d.scale : 0.0f;
-        m[2 * i + 1] = ((w[i] >> 16)     >= d.thr16) ? d.scale : 0.0f;
+    for (uint32_t i = 0; i < 4; ++i) {
+        const uint32_t w = dropout_word(d, blk, i);
+        m[2 * i]     = ((w & 0xFFFFu) >= d.thr16) ? d.scale : 0.0f;
+        m[2 * i + 1] = ((w >> 16)     >= d.thr16) ? d.scale : 0.0f;
     }
 }
-// Multiplier for a single element (slow path, used by small kernels).
+// Multiplier for a single element (used by small kernels).
 __device__ __forceinline__ float dropout_mult1(const DropoutParams& d, uint64_t elem) {
-    const uint4 r = philox4x32_10(d.seed, d.offset, elem >> 3);
-    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
     const uint32_t lane = (uint32_t)(elem & 7);
-    const uint32_t v = (lane & 1) ? (w[lane >> 1] >> 16) : (w[lane >> 1] & 0xFFFFu);
+    const uint32_t w = dropout_word(d, elem >> 3, lane >> 1);
+    const uint32_t v = (lane & 1) ? (w >> 16) : (w & 0xFFFFu);
     return (v >= d.thr16) ? d.scale : 0.0f;
 }
 
@@ -126,8 +150,13 @@ inline DropoutParams make_dropout(float p, uint64_t seed, uint64_t offset) {
     d.scale = (p > 0.f && p < 1.f) ? 1.0f / (1.0f - p) : (p >= 1.f ? 0.f : 1.0f);
     double t = (double)p * 65536.0 + 0.5;
     d.thr16 = p <= 0.f ? 0u : (t >= 65536.0 ? 65536u : (uint32_t)t);
-    d.seed = seed;
-    d.offset = offset;
+    // splitmix64 of (seed, offset) -> 64-bit key
+    uint64_t z = seed * 0x9E3779B97F4A7C15ull + offset * 0xD1B54A32D192ED03ull + 0x2545F4914F6CDD1Dull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    d.key_lo = (uint32_t)z;
+    d.key_hi = (uint32_t)(z >> 32);
     return d;
 }
 

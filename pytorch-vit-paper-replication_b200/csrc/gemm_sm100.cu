@@ -37,7 +37,8 @@ constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
 constexpr int NUM_EPI_WARPS = 8;
 constexpr int GEMM_THREADS = 128 + NUM_EPI_WARPS * 32;
 constexpr int TMEM_COLS = 512;
-constexpr int GEMM_SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int EPI_STAGE_BYTES = 4096;   // per epilogue warp: one 32x32 chunk (fp32 or bf16), XOR-swizzled
+constexpr int GEMM_SMEM_BYTES = STAGES * STAGE_BYTES + NUM_EPI_WARPS * EPI_STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 
 // 2-CTA (cta_group::2) variant: a CTA pair owns a 256x256 output tile. Each CTA stages its own 128 rows of A and
 // HALF of the B tile (128 of the 256 N-rows); the pair's tensor cores read both halves, so every CTA moves
@@ -45,7 +46,7 @@ constexpr int GEMM_SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 25
 constexpr int STAGES2 = 6;
 constexpr int B2_STAGE_BYTES = (BN / 2) * BK * 2;   // 16 KB
 constexpr int STAGE2_BYTES = A_STAGE_BYTES + B2_STAGE_BYTES;
-constexpr int GEMM2_SMEM_BYTES = STAGES2 * STAGE2_BYTES + 1024 + 256;
+constexpr int GEMM2_SMEM_BYTES = STAGES2 * STAGE2_BYTES + NUM_EPI_WARPS * EPI_STAGE_BYTES + 1024 + 256;
 
 enum GemmOp { OP_NT = 0, OP_NN = 1, OP_TN = 2 };
 enum GemmEpi {
@@ -72,39 +73,186 @@ struct GemmParams {
 };
 
 // -------------------------------------------------------------------------------------------------
-// Epilogue: one thread owns one output row (TMEM lane) and 32 consecutive columns per call.
+// Epilogue. After tcgen05.ld a thread holds one ROW (TMEM lane) x 32 consecutive columns of the tile. Accessing
+// global memory from that layout makes every warp instruction touch 32 different rows (32 LSU wavefronts per
+// instruction) -- measured to dominate the K=768 GEMMs. So every global access of the epilogue is done in a
+// row-major "cooperative" layout instead (lane -> (row = it*4 + lane/8, 16-byte chunk = lane%8) for fp32 tiles,
+// (it*8 + lane/4, lane%4) for bf16 tiles: 4 resp. 8 full rows per instruction), and a 4 KB XOR-swizzled staging
+// tile per epilogue warp in shared memory transposes between the two layouts (bank-conflict free both ways).
+// Auxiliary operands (residual / position embedding / pre-activation) are fetched one chunk AHEAD in the
+// cooperative layout, so their HBM latency overlaps the TMEM load and the math of the previous chunk.
 // -------------------------------------------------------------------------------------------------
-template <int EPI>
-__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int col0, float (&v)[32]) {
-    if (row >= p.M || col0 >= p.N) return;
-    const int nvalid = min(32, p.N - col0);
-    const bool full = p.vec_ok && nvalid == 32;
+__device__ __forceinline__ uint32_t stg_off_f32(int row, int chunk) { return row * 128 + ((chunk ^ (row & 7)) << 4); }
+__device__ __forceinline__ uint32_t stg_off_b16(int row, int chunk) { return row * 64 + ((chunk ^ ((row >> 1) & 3)) << 4); }
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+    uint4 r;
+    asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr) : "memory");
+    return r;
+}
 
-    // ---- bias -------------------------------------------------------------------------------
-    if (EPI == EPI_BF16 || EPI == EPI_BIAS_GELU || EPI == EPI_BIAS_RES || EPI == EPI_F32 || EPI == EPI_PATCH) {
-        if (p.bias != nullptr) {
-            if (full) {
-                const float4* b4 = reinterpret_cast<const float4*>(p.bias + col0);
+// registers of prefetched auxiliary operand per 32x32 chunk, cooperative layout
+template <int EPI> struct AuxRegs {
+    static constexpr bool F32 = (EPI == EPI_BIAS_RES || EPI == EPI_PATCH);
+    static constexpr bool B16 = (EPI == EPI_DGELU);
+    static constexpr int N = F32 ? 32 : (B16 ? 16 : 1);
+};
+
+template <int EPI>
+__device__ __forceinline__ long long epi_out_row(const GemmParams& p, int r) {
+    return EPI == EPI_PATCH ? (long long)r + r / p.row_period + 1 : (long long)r;
+}
+
+// Coalesced fetch of the aux tile of one chunk into registers (cooperative layout); zero where out of range.
+template <int EPI>
+__device__ __forceinline__ void aux_prefetch(const GemmParams& p, int lane, int row_base, int col0,
+                                             uint32_t (&a)[AuxRegs<EPI>::N]) {
+    if (!(AuxRegs<EPI>::F32 || AuxRegs<EPI>::B16)) return;
+    if (p.aux == nullptr || col0 >= p.N) return;
+    if (AuxRegs<EPI>::F32) {
+        const float* aux = reinterpret_cast<const float*>(p.aux);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const float4 b = __ldg(b4 + i);
-                    v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
+        for (int it = 0; it < 8; ++it) {
+            const int r = it * 4 + (lane >> 3), ch = lane & 7;
+            const int gr = row_base + r, col = col0 + ch * 4;
+            uint4 q = make_uint4(0, 0, 0, 0);
+            if (gr < p.M && col < p.N) {
+                const long long ar = EPI == EPI_PATCH ? (long long)(gr % p.row_period + 1) : (long long)gr;
+                const float* src = aux + ar * p.ldaux + col;
+                if (p.vec_ok && col + 4 <= p.N) {
+                    q = *reinterpret_cast<const uint4*>(src);
+                } else {
+                    q.x = __float_as_uint(src[0]);
+                    if (col + 1 < p.N) q.y = __float_as_uint(src[1]);
+                    if (col + 2 < p.N) q.z = __float_as_uint(src[2]);
+                    if (col + 3 < p.N) q.w = __float_as_uint(src[3]);
                 }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 32; ++i) if (i < nvalid) v[i] += __ldg(p.bias + col0 + i);
             }
+            a[4 * it] = q.x; a[4 * it + 1] = q.y; a[4 * it + 2] = q.z; a[4 * it + 3] = q.w;
+        }
+    } else {
+        const bf16* aux = reinterpret_cast<const bf16*>(p.aux);
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const int r = it * 8 + (lane >> 2), ch = lane & 3;
+            const int gr = row_base + r, col = col0 + ch * 8;
+            uint4 q = make_uint4(0, 0, 0, 0);
+            if (gr < p.M && col < p.N) {
+                const bf16* src = aux + (long long)gr * p.ldaux + col;
+                if (p.vec_ok && col + 8 <= p.N) {
+                    q = *reinterpret_cast<const uint4*>(src);
+                } else {
+                    uint32_t w[4] = {0, 0, 0, 0};
+                    for (int j = 0; j < 8 && col + j < p.N; ++j)
+                        w[j >> 1] |= (uint32_t)__bfloat16_as_ushort(src[j]) << (16 * (j & 1));
+                    q = make_uint4(w[0], w[1], w[2], w[3]);
+                }
+            }
+            a[4 * it] = q.x; a[4 * it + 1] = q.y; a[4 * it + 2] = q.z; a[4 * it + 3] = q.w;
         }
     }
+}
 
-    // Output row and the row used to index the dropout mask / aux tensor.
-    long long orow = row;
-    if (EPI == EPI_PATCH) orow = (long long)row + row / p.row_period + 1;
+template <int EPI>
+__device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg, int lane, int row_base, int col0,
+                                               float (&v)[32], const uint32_t (&auxr)[AuxRegs<EPI>::N]) {
+    if (col0 >= p.N) return;                       // warp-uniform
+    const int row = row_base + lane;
+    const bool fullw = p.vec_ok && col0 + 32 <= p.N;   // warp-uniform: every 16-byte piece of the chunk is valid
 
-    // ---- dropout multipliers (shared by several epilogues) ----------------------------------
+    // ---- cooperative movers (whole warp) -----------------------------------------------------------
+    auto store_f32_tile = [&](float* base, long long ld) {
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int r = it * 4 + (lane >> 3), ch = lane & 7;
+            const int gr = row_base + r, col = col0 + ch * 4;
+            const uint4 q = lds128(stg + stg_off_f32(r, ch));
+            if (gr < p.M && col < p.N) {
+                float* dst = base + epi_out_row<EPI>(p, gr) * ld + col;
+                if (fullw || (p.vec_ok && col + 4 <= p.N)) {
+                    *reinterpret_cast<uint4*>(dst) = q;
+                } else {
+                    dst[0] = __uint_as_float(q.x);
+                    if (col + 1 < p.N) dst[1] = __uint_as_float(q.y);
+                    if (col + 2 < p.N) dst[2] = __uint_as_float(q.z);
+                    if (col + 3 < p.N) dst[3] = __uint_as_float(q.w);
+                }
+            }
+        }
+    };
+    auto accum_f32_tile = [&](float* base, long long ld) {
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int r = it * 4 + (lane >> 3), ch = lane & 7;
+            const int gr = row_base + r, col = col0 + ch * 4;
+            const uint4 q = lds128(stg + stg_off_f32(r, ch));
+            if (gr < p.M && col < p.N) {
+                float* dst = base + (long long)gr * ld + col;
+                if (fullw || (p.vec_ok && col + 4 <= p.N)) {
+                    asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};"
+                                 ::"l"(dst), "f"(__uint_as_float(q.x)), "f"(__uint_as_float(q.y)),
+                                   "f"(__uint_as_float(q.z)), "f"(__uint_as_float(q.w)) : "memory");
+                } else {
+                    atomicAdd(dst, __uint_as_float(q.x));
+                    if (col + 1 < p.N) atomicAdd(dst + 1, __uint_as_float(q.y));
+                    if (col + 2 < p.N) atomicAdd(dst + 2, __uint_as_float(q.z));
+                    if (col + 3 < p.N) atomicAdd(dst + 3, __uint_as_float(q.w));
+                }
+            }
+        }
+    };
+    auto store_b16_tile = [&](bf16* base, long long ld) {
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const int r = it * 8 + (lane >> 2), ch = lane & 3;
+            const int gr = row_base + r, col = col0 + ch * 8;
+            const uint4 q = lds128(stg + stg_off_b16(r, ch));
+            if (gr < p.M && col < p.N) {
+                bf16* dst = base + epi_out_row<EPI>(p, gr) * ld + col;
+                if (fullw || (p.vec_ok && col + 8 <= p.N)) {
+                    *reinterpret_cast<uint4*>(dst) = q;
+                } else {
+                    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+                    for (int j = 0; j < 8 && col + j < p.N; ++j)
+                        dst[j] = __ushort_as_bfloat16((unsigned short)(w[j >> 1] >> (16 * (j & 1))));
+                }
+            }
+        }
+    };
+    auto put_row_f32 = [&](const float (&x)[32]) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+            sts128(stg + stg_off_f32(lane, c), __float_as_uint(x[4 * c]), __float_as_uint(x[4 * c + 1]),
+                   __float_as_uint(x[4 * c + 2]), __float_as_uint(x[4 * c + 3]));
+    };
+    auto put_row_b16 = [&](const float (&x)[32]) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            sts128(stg + stg_off_b16(lane, c), pack_bf16(x[8 * c], x[8 * c + 1]), pack_bf16(x[8 * c + 2], x[8 * c + 3]),
+                   pack_bf16(x[8 * c + 4], x[8 * c + 5]), pack_bf16(x[8 * c + 6], x[8 * c + 7]));
+    };
+    // aux registers (cooperative layout) -> staging -> my row
+    auto aux_to_stage = [&]() {
+        if (AuxRegs<EPI>::F32) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it)
+                sts128(stg + stg_off_f32(it * 4 + (lane >> 3), lane & 7), auxr[(4 * it) % AuxRegs<EPI>::N],
+                       auxr[(4 * it + 1) % AuxRegs<EPI>::N], auxr[(4 * it + 2) % AuxRegs<EPI>::N],
+                       auxr[(4 * it + 3) % AuxRegs<EPI>::N]);
+        } else if (AuxRegs<EPI>::B16) {
+#pragma unroll
+            for (int it = 0; it < 4; ++it)
+                sts128(stg + stg_off_b16(it * 8 + (lane >> 2), lane & 3), auxr[(4 * it) % AuxRegs<EPI>::N],
+                       auxr[(4 * it + 1) % AuxRegs<EPI>::N], auxr[(4 * it + 2) % AuxRegs<EPI>::N],
+                       auxr[(4 * it + 3) % AuxRegs<EPI>::N]);
+        }
+        __syncwarp();
+    };
     auto apply_dropout = [&](float (&x)[32]) {
         if (p.drop.p <= 0.f) return;
-        const unsigned long long e0 = (unsigned long long)orow * (unsigned long long)p.N + (unsigned long long)col0;
+        const unsigned long long e0 = (unsigned long long)epi_out_row<EPI>(p, row) * (unsigned long long)p.N + (unsigned long long)col0;
         if ((p.N & 7) == 0) {
 #pragma unroll
             for (int b = 0; b < 4; ++b) {
@@ -119,102 +267,88 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, int row, int
         }
     };
 
-    auto store_bf16 = [&](void* base, long long ld, const float (&x)[32]) {
-        bf16* dst = reinterpret_cast<bf16*>(base) + orow * ld + col0;
-        if (full) {
-            uint4* d4 = reinterpret_cast<uint4*>(dst);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                uint4 o;
-                o.x = pack_bf16(x[8 * i], x[8 * i + 1]);
-                o.y = pack_bf16(x[8 * i + 2], x[8 * i + 3]);
-                o.z = pack_bf16(x[8 * i + 4], x[8 * i + 5]);
-                o.w = pack_bf16(x[8 * i + 6], x[8 * i + 7]);
-                d4[i] = o;
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) if (i < nvalid) dst[i] = __float2bfloat16(x[i]);
-        }
-    };
-    auto store_f32 = [&](void* base, long long ld, const float (&x)[32]) {
-        float* dst = reinterpret_cast<float*>(base) + orow * ld + col0;
-        if (full) {
-            float4* d4 = reinterpret_cast<float4*>(dst);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) d4[i] = make_float4(x[4 * i], x[4 * i + 1], x[4 * i + 2], x[4 * i + 3]);
-        } else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) if (i < nvalid) dst[i] = x[i];
-        }
-    };
-
-    if (EPI == EPI_BF16) {
-        store_bf16(p.C, p.ldc, v);
-    } else if (EPI == EPI_F32) {
-        store_f32(p.C, p.ldc, v);
-    } else if (EPI == EPI_BIAS_GELU) {
-        if (p.C != nullptr) store_bf16(p.C, p.ldc, v);
-#pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = gelu_exact(v[i]);
-        apply_dropout(v);
-        store_bf16(p.C2, p.ldc2, v);
-    } else if (EPI == EPI_BIAS_RES || EPI == EPI_PATCH) {
-        if (EPI == EPI_PATCH) {
-            // position embedding row (m % P) + 1 is added BEFORE dropout (vit.py:63-66)
-            const float* pos = reinterpret_cast<const float*>(p.aux) + (long long)(row % p.row_period + 1) * p.ldaux + col0;
-#pragma unroll
-            for (int i = 0; i < 32; ++i) if (i < nvalid) v[i] += __ldg(pos + i);
-        }
-        apply_dropout(v);
-        if (EPI == EPI_BIAS_RES && p.aux != nullptr) {
-            const float* res = reinterpret_cast<const float*>(p.aux) + orow * p.ldaux + col0;
-            if (full) {
-                const float4* r4 = reinterpret_cast<const float4*>(res);
+    // ---- bias ---------------------------------------------------------------------------------------
+    if (EPI == EPI_BF16 || EPI == EPI_BIAS_GELU || EPI == EPI_BIAS_RES || EPI == EPI_F32 || EPI == EPI_PATCH) {
+        if (p.bias != nullptr) {
+            if (fullw) {
+                const float4* b4 = reinterpret_cast<const float4*>(p.bias + col0);
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    const float4 r = r4[i];
-                    v[4 * i] += r.x; v[4 * i + 1] += r.y; v[4 * i + 2] += r.z; v[4 * i + 3] += r.w;
+                    const float4 b = __ldg(b4 + i);
+                    v[4 * i] += b.x; v[4 * i + 1] += b.y; v[4 * i + 2] += b.z; v[4 * i + 3] += b.w;
                 }
             } else {
 #pragma unroll
-                for (int i = 0; i < 32; ++i) if (i < nvalid) v[i] += res[i];
+                for (int i = 0; i < 32; ++i) if (col0 + i < p.N) v[i] += __ldg(p.bias + col0 + i);
             }
         }
-        store_f32(p.C, p.ldc, v);
+    }
+
+    if (EPI == EPI_BF16) {
+        put_row_b16(v);
+        __syncwarp();
+        store_b16_tile(reinterpret_cast<bf16*>(p.C), p.ldc);
+        __syncwarp();
+    } else if (EPI == EPI_F32) {
+        put_row_f32(v);
+        __syncwarp();
+        store_f32_tile(reinterpret_cast<float*>(p.C), p.ldc);
+        __syncwarp();
+    } else if (EPI == EPI_BIAS_GELU) {
+        if (p.C != nullptr) {
+            put_row_b16(v);
+            __syncwarp();
+            store_b16_tile(reinterpret_cast<bf16*>(p.C), p.ldc);
+            __syncwarp();
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = gelu_exact(v[i]);
+        apply_dropout(v);
+        put_row_b16(v);
+        __syncwarp();
+        store_b16_tile(reinterpret_cast<bf16*>(p.C2), p.ldc2);
+        __syncwarp();
+    } else if (EPI == EPI_BIAS_RES || EPI == EPI_PATCH) {
+        if (EPI == EPI_BIAS_RES) apply_dropout(v);
+        if (EPI == EPI_PATCH || p.aux != nullptr) {
+            aux_to_stage();
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const uint4 q = lds128(stg + stg_off_f32(lane, c));
+                v[4 * c] += __uint_as_float(q.x); v[4 * c + 1] += __uint_as_float(q.y);
+                v[4 * c + 2] += __uint_as_float(q.z); v[4 * c + 3] += __uint_as_float(q.w);
+            }
+            __syncwarp();
+        }
+        if (EPI == EPI_PATCH) apply_dropout(v);   // position embedding is added BEFORE dropout (vit.py:63-66)
+        put_row_f32(v);
+        __syncwarp();
+        store_f32_tile(reinterpret_cast<float*>(p.C), p.ldc);
+        __syncwarp();
     } else if (EPI == EPI_DGELU) {
         apply_dropout(v);
-        const bf16* a = reinterpret_cast<const bf16*>(p.aux) + orow * p.ldaux + col0;
-        if (full) {
-            const uint4* a4 = reinterpret_cast<const uint4*>(a);
+        aux_to_stage();
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const uint4 q = a4[i];
-                const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+        for (int c = 0; c < 4; ++c) {
+            const uint4 q = lds128(stg + stg_off_b16(lane, c));
+            const uint32_t w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float2 f = unpack_bf16(w[j]);
-                    v[8 * i + 2 * j] *= gelu_exact_grad(f.x);
-                    v[8 * i + 2 * j + 1] *= gelu_exact_grad(f.y);
-                }
+            for (int j = 0; j < 4; ++j) {
+                const float2 f = unpack_bf16(w[j]);
+                v[8 * c + 2 * j] *= gelu_exact_grad(f.x);
+                v[8 * c + 2 * j + 1] *= gelu_exact_grad(f.y);
             }
-        } else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) if (i < nvalid) v[i] *= gelu_exact_grad(__bfloat162float(a[i]));
         }
-        store_bf16(p.C, p.ldc, v);
+        __syncwarp();
+        put_row_b16(v);
+        __syncwarp();
+        store_b16_tile(reinterpret_cast<bf16*>(p.C), p.ldc);
+        __syncwarp();
     } else if (EPI == EPI_ACCUM) {
-        float* dst = reinterpret_cast<float*>(p.C) + orow * p.ldc + col0;
-        if (full) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-                asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};"
-                             ::"l"(dst + 4 * i), "f"(v[4 * i]), "f"(v[4 * i + 1]), "f"(v[4 * i + 2]), "f"(v[4 * i + 3])
-                             : "memory");
-        } else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) if (i < nvalid) atomicAdd(dst + i, v[i]);
-        }
+        put_row_f32(v);
+        __syncwarp();
+        accum_f32_tile(reinterpret_cast<float*>(p.C), p.ldc);
+        __syncwarp();
     }
 }
 
@@ -230,7 +364,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t smem_a = smem_base;
     const uint32_t smem_b = smem_base + STAGES * A_STAGE_BYTES;
-    const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;
+    const uint32_t smem_stage = smem_base + STAGES * STAGE_BYTES;
+    const uint32_t bar_base = smem_stage + NUM_EPI_WARPS * EPI_STAGE_BYTES;
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
     auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + s); };
@@ -351,15 +486,21 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             decode(w, m0, n0, kb0, kb1);
             const int acc = iter & 1;
             const uint32_t acc_phase = (iter >> 1) & 1;
+            const int row_base = m0 + quarter * 32;
+            const uint32_t stg = smem_stage + ew * EPI_STAGE_BYTES;
+            uint32_t aux_next[AuxRegs<EPI>::N], aux_cur[AuxRegs<EPI>::N];
+            aux_prefetch<EPI>(p, lane, row_base, n0 + half * 128, aux_next);   // before the accumulator is even ready
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
-            const int row = m0 + quarter * 32 + lane;
 #pragma unroll 1
             for (int c = 0; c < 4; ++c) {
                 const int col_in_tile = half * 128 + c * 32;
                 const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + col_in_tile);
                 uint32_t r[32];
                 tmem_ld_32x32(taddr, r);
+#pragma unroll
+                for (int i = 0; i < AuxRegs<EPI>::N; ++i) aux_cur[i] = aux_next[i];
+                if (c < 3) aux_prefetch<EPI>(p, lane, row_base, n0 + col_in_tile + 32, aux_next);
                 tmem_ld_wait();
                 if (c == 3) {
                     // all TMEM reads of this warp are done: hand the accumulator back to the MMA warp
@@ -370,7 +511,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 float v[32];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-                epilogue_chunk<EPI>(p, row, n0 + col_in_tile, v);
+                epilogue_chunk<EPI>(p, stg, lane, row_base, n0 + col_in_tile, v, aux_cur);
             }
         }
     }
@@ -395,7 +536,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t smem_a = smem_base;
     const uint32_t smem_b = smem_base + STAGES2 * A_STAGE_BYTES;
-    const uint32_t bar_base = smem_base + STAGES2 * STAGE2_BYTES;
+    const uint32_t smem_stage = smem_base + STAGES2 * STAGE2_BYTES;
+    const uint32_t bar_base = smem_stage + NUM_EPI_WARPS * EPI_STAGE_BYTES;
     auto full_bar = [&](int s) { return bar_base + 8u * s; };                       // used in the leader CTA
     auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES2 + s); };          // one per CTA
     auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * STAGES2 + s); };      // one per CTA
@@ -521,15 +663,21 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             decode(w, m0, n0, kb0, kb1);
             const int acc = iter & 1;
             const uint32_t acc_phase = (iter >> 1) & 1;
+            const int row_base = m0 + quarter * 32;
+            const uint32_t stg = smem_stage + ew * EPI_STAGE_BYTES;
+            uint32_t aux_next[AuxRegs<EPI>::N], aux_cur[AuxRegs<EPI>::N];
+            aux_prefetch<EPI>(p, lane, row_base, n0 + half * 128, aux_next);   // before the accumulator is even ready
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
-            const int row = m0 + quarter * 32 + lane;
 #pragma unroll 1
             for (int c = 0; c < 4; ++c) {
                 const int col_in_tile = half * 128 + c * 32;
                 const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + col_in_tile);
                 uint32_t r[32];
                 tmem_ld_32x32(taddr, r);
+#pragma unroll
+                for (int i = 0; i < AuxRegs<EPI>::N; ++i) aux_cur[i] = aux_next[i];
+                if (c < 3) aux_prefetch<EPI>(p, lane, row_base, n0 + col_in_tile + 32, aux_next);
                 tmem_ld_wait();
                 if (c == 3) {
                     tc_fence_before();
@@ -539,7 +687,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                 float v[32];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-                epilogue_chunk<EPI>(p, row, n0 + col_in_tile, v);
+                epilogue_chunk<EPI>(p, stg, lane, row_base, n0 + col_in_tile, v, aux_cur);
             }
         }
     }

@@ -1,7 +1,7 @@
 // LayerNorm forward / backward (nn.LayerNorm(D), eps 1e-5, biased variance: reference models/vit.py:83,115,216).
 // HBM-bound: one warp per row, float4 accesses, warp-shuffle row reductions; the backward keeps the
-// dgamma / dbeta (and optional next-bias) column partials in registers across the rows a warp visits and
-// finishes with one shared-memory reduction + one atomic per column per block.
+// dgamma / dbeta (and optional next-bias) column partials in per-warp shared-memory slabs across the rows a
+// warp visits and finishes with one cross-warp reduction + one atomic per column per block.
 #include "common.cuh"
 #include "launchers.h"
 
@@ -86,37 +86,39 @@ int layernorm_fwd_launch(const float* x, long long row_stride, const float* gamm
 // NV = float4 chunks per lane (ceil(D / 128)).
 // ---------------------------------------------------------------------------------------------
 template <int NV, bool HAS_NEXT>
-__global__ void __launch_bounds__(LN_WARPS * 32, (NV <= 6 && !HAS_NEXT) ? 2 : 1)
+__global__ void __launch_bounds__(LN_WARPS * 32, 2)
 layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__ dy_f32, const float* __restrict__ x,
                      long long row_stride, const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
                      const float* __restrict__ gamma, const float* __restrict__ gin, float* __restrict__ gout,
                      long long gout_stride, bf16* __restrict__ gout_bf16, float* __restrict__ dgamma,
                      float* __restrict__ dbeta, float* __restrict__ dbias_next, long long rows, int D,
                      DropoutParams drop) {
-    extern __shared__ float red[];  // [LN_WARPS][D]
+    // Column accumulators live in shared memory, one private slab per warp ([acc][warp][D]): keeping them in
+    // registers (24 values per lane per accumulator at D=768) starved the kernel of occupancy.
+    extern __shared__ float sacc[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nv = D >> 2;
-
-    const float4* gamma4 = reinterpret_cast<const float4*>(gamma);   // re-read per row (L1-resident) to save registers
-    float4 acc_g[NV], acc_b[NV], acc_n[HAS_NEXT ? NV : 1];
-#pragma unroll
-    for (int k = 0; k < NV; ++k) {
-        acc_g[k] = make_float4(0, 0, 0, 0);
-        acc_b[k] = make_float4(0, 0, 0, 0);
-        if (HAS_NEXT) acc_n[k] = make_float4(0, 0, 0, 0);
+    float4* acc_g = reinterpret_cast<float4*>(sacc + (size_t)(0 * LN_WARPS + warp) * D);
+    float4* acc_b = reinterpret_cast<float4*>(sacc + (size_t)(1 * LN_WARPS + warp) * D);
+    float4* acc_n = reinterpret_cast<float4*>(sacc + (size_t)(2 * LN_WARPS + warp) * D);
+    for (int i = lane; i < nv; i += 32) {
+        acc_g[i] = make_float4(0, 0, 0, 0);
+        acc_b[i] = make_float4(0, 0, 0, 0);
+        if (HAS_NEXT) acc_n[i] = make_float4(0, 0, 0, 0);
     }
+    __syncwarp();
+    const float4* gamma4 = reinterpret_cast<const float4*>(gamma);
 
     for (long long row = (long long)blockIdx.x * LN_WARPS + warp; row < rows; row += (long long)gridDim.x * LN_WARPS) {
         const float mean = mean_in[row], rstd = rstd_in[row];
         const float4* xr = reinterpret_cast<const float4*>(x + row * row_stride);
-        float4 xh[NV], dy[NV];
-        float s1 = 0.f, s2 = 0.f;
+        float4 xh[NV], dy[NV], res[NV];
+        // issue every global load of the row up front
 #pragma unroll
         for (int k = 0; k < NV; ++k) {
             const int i = lane + 32 * k;
             if (i < nv) {
-                const float4 v = xr[i];
-                xh[k] = make_float4((v.x - mean) * rstd, (v.y - mean) * rstd, (v.z - mean) * rstd, (v.w - mean) * rstd);
+                xh[k] = xr[i];
                 if (dy_bf16) {
                     const uint2 q = reinterpret_cast<const uint2*>(dy_bf16 + row * (long long)D)[i];
                     const float2 a = unpack_bf16(q.x), b = unpack_bf16(q.y);
@@ -124,13 +126,25 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
                 } else {
                     dy[k] = reinterpret_cast<const float4*>(dy_f32 + row * (long long)D)[i];
                 }
+                res[k] = gin ? reinterpret_cast<const float4*>(gin + row * gout_stride)[i] : make_float4(0, 0, 0, 0);
+            }
+        }
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            const int i = lane + 32 * k;
+            if (i < nv) {
+                const float4 v = xh[k];
+                xh[k] = make_float4((v.x - mean) * rstd, (v.y - mean) * rstd, (v.z - mean) * rstd, (v.w - mean) * rstd);
                 const float4 g = __ldg(gamma4 + i);
                 const float a0 = dy[k].x * g.x, a1 = dy[k].y * g.y, a2 = dy[k].z * g.z, a3 = dy[k].w * g.w;
                 s1 += (a0 + a1) + (a2 + a3);
                 s2 += (a0 * xh[k].x + a1 * xh[k].y) + (a2 * xh[k].z + a3 * xh[k].w);
-                acc_g[k].x += dy[k].x * xh[k].x; acc_g[k].y += dy[k].y * xh[k].y;
-                acc_g[k].z += dy[k].z * xh[k].z; acc_g[k].w += dy[k].w * xh[k].w;
-                acc_b[k].x += dy[k].x; acc_b[k].y += dy[k].y; acc_b[k].z += dy[k].z; acc_b[k].w += dy[k].w;
+                float4 ag = acc_g[i], ab = acc_b[i];
+                ag.x += dy[k].x * xh[k].x; ag.y += dy[k].y * xh[k].y; ag.z += dy[k].z * xh[k].z; ag.w += dy[k].w * xh[k].w;
+                ab.x += dy[k].x; ab.y += dy[k].y; ab.z += dy[k].z; ab.w += dy[k].w;
+                acc_g[i] = ag;
+                acc_b[i] = ab;
             }
         }
         const float c1 = warp_sum(s1) / (float)D;
@@ -141,14 +155,10 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
             if (i < nv) {
                 const float4 g = __ldg(gamma4 + i);
                 float4 o;
-                o.x = rstd * (dy[k].x * g.x - c1 - xh[k].x * c2);
-                o.y = rstd * (dy[k].y * g.y - c1 - xh[k].y * c2);
-                o.z = rstd * (dy[k].z * g.z - c1 - xh[k].z * c2);
-                o.w = rstd * (dy[k].w * g.w - c1 - xh[k].w * c2);
-                if (gin) {
-                    const float4 r = reinterpret_cast<const float4*>(gin + row * gout_stride)[i];
-                    o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
-                }
+                o.x = rstd * (dy[k].x * g.x - c1 - xh[k].x * c2) + res[k].x;
+                o.y = rstd * (dy[k].y * g.y - c1 - xh[k].y * c2) + res[k].y;
+                o.z = rstd * (dy[k].z * g.z - c1 - xh[k].z * c2) + res[k].z;
+                o.w = rstd * (dy[k].w * g.w - c1 - xh[k].w * c2) + res[k].w;
                 reinterpret_cast<float4*>(gout + row * gout_stride)[i] = o;
                 if (HAS_NEXT) {
                     float v[4] = {o.x, o.y, o.z, o.w};
@@ -162,31 +172,27 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
                     pk.y = pack_bf16(v[2], v[3]);
                     reinterpret_cast<uint2*>(gout_bf16 + row * (long long)D)[i] = pk;
                     const float2 r0 = unpack_bf16(pk.x), r1 = unpack_bf16(pk.y);
-                    acc_n[k].x += r0.x; acc_n[k].y += r0.y; acc_n[k].z += r1.x; acc_n[k].w += r1.y;
+                    float4 an = acc_n[i];
+                    an.x += r0.x; an.y += r0.y; an.z += r1.x; an.w += r1.y;
+                    acc_n[i] = an;
                 }
             }
         }
     }
 
-    // block reduction of the three column accumulators, one at a time through the same smem slab
-    auto reduce_store = [&](float4* acc, float* dst) {
-        __syncthreads();
+    __syncthreads();
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+        float sg = 0.f, sb = 0.f, sn = 0.f;
 #pragma unroll
-        for (int k = 0; k < NV; ++k) {
-            const int i = lane + 32 * k;
-            if (i < nv) reinterpret_cast<float4*>(red + warp * D)[i] = acc[k];
+        for (int w = 0; w < LN_WARPS; ++w) {
+            sg += sacc[(size_t)(0 * LN_WARPS + w) * D + d];
+            sb += sacc[(size_t)(1 * LN_WARPS + w) * D + d];
+            if (HAS_NEXT) sn += sacc[(size_t)(2 * LN_WARPS + w) * D + d];
         }
-        __syncthreads();
-        for (int d = threadIdx.x; d < D; d += blockDim.x) {
-            float s = 0.f;
-#pragma unroll
-            for (int w = 0; w < LN_WARPS; ++w) s += red[w * D + d];
-            atomicAdd(dst + d, s);
-        }
-    };
-    if (dgamma) reduce_store(acc_g, dgamma);
-    if (dbeta) reduce_store(acc_b, dbeta);
-    if (HAS_NEXT && dbias_next) reduce_store(acc_n, dbias_next);
+        if (dgamma) atomicAdd(dgamma + d, sg);
+        if (dbeta) atomicAdd(dbeta + d, sb);
+        if (HAS_NEXT && dbias_next) atomicAdd(dbias_next + d, sn);
+    }
 }
 
 int layernorm_bwd_launch(const bf16* dy_bf16, const float* dy_f32, const float* x, long long row_stride,
@@ -204,13 +210,15 @@ int layernorm_bwd_launch(const bf16* dy_bf16, const float* dy_f32, const float* 
     if (dbeta) B200_CUDA(cudaMemsetAsync(dbeta, 0, sizeof(float) * dim, stream));
     if (dbias_next) B200_CUDA(cudaMemsetAsync(dbias_next, 0, sizeof(float) * dim, stream));
     long long blocks = (rows + LN_WARPS - 1) / LN_WARPS;
-    const long long cap = (long long)sm_count() * 8;
+    const long long cap = (long long)sm_count() * 2;   // persistent: 2 resident blocks per SM, rows strided
     if (blocks > cap) blocks = cap;
     const DropoutParams drop = make_dropout(drop_p, seed, offset);
-    const size_t smem = sizeof(float) * LN_WARPS * dim;
+    const size_t smem = sizeof(float) * (gout_bf16 ? 3 : 2) * LN_WARPS * dim;
     const int nvl = (dim / 4 + 31) / 32;
 #define LN_BWD_CASE(NV)                                                                                         \
     do {                                                                                                        \
+        B200_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<NV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * 4 * LN_WARPS * 1024)); \
+        B200_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<NV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 4 * LN_WARPS * 1024)); \
         if (gout_bf16)                                                                                          \
             layernorm_bwd_kernel<NV, true><<<(unsigned)blocks, LN_WARPS * 32, smem, stream>>>(                   \
                 dy_bf16, dy_f32, x, row_stride, mean, rstd, gamma, gin, gout, gout_stride, gout_bf16, dgamma,   \
