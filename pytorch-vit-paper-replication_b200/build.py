@@ -26,6 +26,7 @@ SOURCES = [
     "api.cu",
     "gemm_sm100.cu",
     "attention.cu",
+    "attention_tc.cu",
     "layernorm.cu",
     "elementwise.cu",
     "head_loss.cu",

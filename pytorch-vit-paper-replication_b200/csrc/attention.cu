@@ -11,6 +11,8 @@
 #include "common.cuh"
 #include "launchers.h"
 
+#include <stdlib.h>
+
 namespace b200vit {
 
 constexpr int AT_BLOCK = 64;     // rows per tile (queries or keys)
@@ -613,6 +615,16 @@ attention_bwd_resident_kernel(const bf16* __restrict__ qkv, const bf16* __restri
 
 constexpr int AT_RESIDENT_MAX_T = 256;
 
+// B200VIT_ATTN_MODE=1 selects the mma.sync kernels for short sequences too (A/B measurements, debugging).
+static int attention_mode() {
+    static int mode = -1;
+    if (mode < 0) {
+        const char* e = getenv("B200VIT_ATTN_MODE");
+        mode = e ? atoi(e) : 0;
+    }
+    return mode;
+}
+
 // ---------------------------------------------------------------------------------------------
 int attention_fwd_launch(const bf16* qkv, bf16* out, float* lse, int batch, int tokens, int heads, int head_dim,
                          float scale, cudaStream_t stream) {
@@ -620,6 +632,8 @@ int attention_fwd_launch(const bf16* qkv, bf16* out, float* lse, int batch, int 
     B200_CHECK_ARG(head_dim == AT_HD, "attention_fwd: head_dim must be 64 (got %d)", head_dim);
     B200_CHECK_ARG(batch > 0 && tokens > 0 && heads > 0, "attention_fwd: bad sizes");
     B200_CHECK_ARG(((uintptr_t)qkv % 16) == 0 && ((uintptr_t)out % 16) == 0, "attention_fwd: unaligned pointer");
+    if (tokens <= AT_RESIDENT_MAX_T && attention_mode() == 0)
+        return attention_fwd_tc_launch(qkv, out, lse, batch, tokens, heads, scale, stream);
     if (tokens <= AT_RESIDENT_MAX_T) {
         const int Tp = (tokens + 15) & ~15;
         const int ntiles = Tp / 16;
@@ -645,6 +659,8 @@ int attention_bwd_launch(const bf16* qkv, const bf16* out, const bf16* dout, con
     B200_CHECK_ARG(qkv && out && dout && lse && delta && dqkv, "attention_bwd: null pointer");
     B200_CHECK_ARG(head_dim == AT_HD, "attention_bwd: head_dim must be 64 (got %d)", head_dim);
     B200_CHECK_ARG(batch > 0 && tokens > 0 && heads > 0, "attention_bwd: bad sizes");
+    if (tokens <= AT_RESIDENT_MAX_T && attention_mode() == 0)
+        return attention_bwd_tc_launch(qkv, out, dout, lse, dqkv, batch, tokens, heads, scale, stream);
     if (tokens <= AT_RESIDENT_MAX_T) {
         // delta is computed inside the fused kernel (kept in shared memory); the scratch buffer is not touched
         const int Tp = (tokens + 15) & ~15;

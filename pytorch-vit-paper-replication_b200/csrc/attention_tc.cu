@@ -1,0 +1,585 @@
+// tcgen05 / TMEM fused attention forward for short sequences (T <= 256, head_dim 64): the 197-token ViT case.
+// One CTA per (batch, head, 128-query tile):
+//   warp 0      issues the TMA loads (Q tile, all K, all V of the head) and both UMMAs
+//   warp 1      TMEM allocator (256 columns -> two CTAs co-reside per SM and overlap each other's phases)
+//   warps 2-5   softmax + epilogue: thread <-> query row (TMEM lane)
+// Dataflow:  S = Q K^T (UMMA 128 x Nk x 64, smem x smem -> TMEM fp32)
+//            P = exp2((S - rowmax) * scale*log2e) as bf16 pairs written IN PLACE over S with tcgen05.st
+//            O = P V   (UMMA 128 x 64 x Nk, A from TMEM, V as MN-major smem operand) ; out = O / rowsum
+// The whole key range of a head (Nk = T rounded to 16 <= 256) fits one accumulator, so the softmax is a plain
+// two-pass row softmax: no online rescaling. Scores never leave the SM; only O and the log-sum-exp do.
+// (Reference semantics: scaled_dot_product_attention inside nn.MultiheadAttention, models/vit.py:86-97.)
+#include "common.cuh"
+#include "launchers.h"
+#include "ptx_sm100.cuh"
+
+#include <cudaTypedefs.h>
+#include <mutex>
+
+namespace b200vit {
+
+using namespace ptx;
+
+constexpr int ATC_BM = 128;
+constexpr int ATC_THREADS = 320;    // warp 0: TMA producer, warp 1: TMEM alloc + MMA issue, warps 2-9: two softmax groups
+constexpr int ATC_TMEM_COLS = 512;  // two 256-column slots, one per 128-query tile of the head in flight
+constexpr int ATC_O_COL = 128;      // O accumulator columns [128, 192) of a slot: dead upper half of S by then
+constexpr int ATC_Q_ROWS = 256;     // Q stage holds up to two 128-row tiles (rows >= T are zero-filled by TMA)
+
+// Persistent: each CTA (one per SM) walks over (batch, head) work items. Per head the producer stages Q (all
+// rows), K and V once (2-deep smem ring); the MMA thread issues S = Q_t K^T for both query tiles into the two TMEM
+// slots; softmax group g (4 warps, thread <-> query row) owns tile g: P = exp2(...) written in place as bf16,
+// then O = P V (A operand from TMEM), then the epilogue. The two groups, the MMA thread and the producer run
+// decoupled through mbarriers, so loads, tensor work and softmax of neighbouring tiles / heads overlap.
+__global__ void __launch_bounds__(ATC_THREADS, 1)
+attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
+                        bf16* __restrict__ out, float* __restrict__ lse, int num_heads_total, int T, int Nk, int H,
+                        float scale_log2, float scale) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t kv_bytes = (uint32_t)Nk * 128u;
+    const uint32_t kv_stride = (kv_bytes + 1023u) & ~1023u;
+    const uint32_t stage_bytes = ATC_Q_ROWS * 128 + 2 * kv_stride;
+    const uint32_t bar_base = smem_base + 2 * stage_bytes;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 16u + 8u * s; };
+    auto s_ready = [&](int g) { return bar_base + 32u + 8u * g; };
+    auto p_ready = [&](int g) { return bar_base + 48u + 8u * g; };
+    auto o_ready = [&](int g) { return bar_base + 64u + 8u * g; };
+    auto slot_free = [&](int g) { return bar_base + 80u + 8u * g; };
+    const uint32_t tmem_slot = bar_base + 96u;
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nt = (T + ATC_BM - 1) / ATC_BM;          // query tiles per head: 1 or 2
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmQ);
+        prefetch_tmap(&tmKV);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(full_bar(i), 1);
+            mbar_init(empty_bar(i), 1);
+            mbar_init(s_ready(i), 1);
+            mbar_init(p_ready(i), 4);
+            mbar_init(o_ready(i), 1);
+            mbar_init(slot_free(i), 4);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc<1>(tmem_slot, ATC_TMEM_COLS);
+        tmem_relinquish<1>();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int it = 0;
+            for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
+                const int s = it & 1;
+                const uint32_t ph = (it >> 1) & 1;
+                const int b = w / H, h = w % H;
+                mbar_wait(empty_bar(s), ph ^ 1u);
+                const uint32_t sQ = smem_base + s * stage_bytes, sK = sQ + ATC_Q_ROWS * 128, sV = sK + kv_stride;
+                mbar_arrive_expect_tx(full_bar(s), (uint32_t)nt * ATC_BM * 128 + 2 * kv_bytes);
+                tma_load_4d(sQ, &tmQ, full_bar(s), 0, 0, h, b);
+                tma_load_4d(sK, &tmKV, full_bar(s), 0, 0, H + h, b);
+                tma_load_4d(sV, &tmKV, full_bar(s), 0, 0, 2 * H + h, b);
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc_s = make_idesc_bf16(ATC_BM, Nk, 0, 0);
+            const uint32_t idesc_o = make_idesc_bf16(ATC_BM, 64, 0, 1);
+            int it = 0;
+            for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
+                const int s = it & 1;
+                const uint32_t ph = (it >> 1) & 1, hp = it & 1;
+                const uint32_t sQ = smem_base + s * stage_bytes, sK = sQ + ATC_Q_ROWS * 128, sV = sK + kv_stride;
+                mbar_wait(full_bar(s), ph);
+                tc_fence_after();
+                for (int g = 0; g < nt; ++g) {
+                    mbar_wait(slot_free(g), hp ^ 1u);
+                    tc_fence_after();
+                    // S = Q_g K^T : A = Q rows [128 g, 128 g + 128) K-major, B = K [Nk x 64] K-major
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_bf16<1>(tmem + g * 256, make_smem_desc_sw128(sQ + g * (ATC_BM * 128) + k * 32, 1024, 0),
+                                     make_smem_desc_sw128(sK + k * 32, 1024, 0), idesc_s, k > 0 ? 1u : 0u);
+                    umma_commit(s_ready(g));
+                }
+                for (int g = 0; g < nt; ++g) {
+                    mbar_wait(p_ready(g), hp);
+                    tc_fence_after();
+                    // O = P V : A = P in TMEM (bf16 pairs: 8 columns per 16 keys), B = V [Nk keys x 64] MN-major
+                    for (int k = 0; k < Nk / 16; ++k)
+                        umma_bf16_ts(tmem + g * 256 + ATC_O_COL, tmem + g * 256 + k * 8,
+                                     make_smem_desc_sw128(sV + k * 2048, 1024, 0), idesc_o, k > 0 ? 1u : 0u);
+                    umma_commit(o_ready(g));
+                }
+                umma_commit(empty_bar(s));      // every MMA that reads this smem stage has retired
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===================== softmax + epilogue groups =====================
+        const int g = (warp - 2) >> 2;
+        const int quarter = warp & 3;
+        if (g < nt) {
+            const uint32_t tbase = tmem + g * 256 + ((uint32_t)(quarter * 32) << 16);
+            const int r_in_head = g * ATC_BM + quarter * 32 + lane;       // query index inside the head
+            int it = 0;
+            for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
+                const uint32_t hp = it & 1;
+                const int b = w / H, h = w % H;
+                mbar_wait(s_ready(g), hp);
+                tc_fence_after();
+                // pass 1: row max over the valid keys
+                float mx = -INFINITY;
+                int c = 0;
+                for (; c + 32 <= Nk; c += 32) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(tbase + c, r);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (c + i < T) mx = fmaxf(mx, __uint_as_float(r[i]));
+                }
+                if (c < Nk) {
+                    uint32_t r[16];
+                    tmem_ld_32x16(tbase + c, r);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (c + i < T) mx = fmaxf(mx, __uint_as_float(r[i]));
+                }
+                // pass 2: P = exp2((S - max) * scale*log2e) as bf16 pairs, written over S columns already consumed
+                const float mneg = -mx * scale_log2;
+                float sum = 0.f;
+                auto do16 = [&](const uint32_t* r, int c0) {
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float p0 = (c0 + 2 * i < T) ? fast_ex2(fmaf(__uint_as_float(r[2 * i]), scale_log2, mneg)) : 0.f;
+                        const float p1 = (c0 + 2 * i + 1 < T) ? fast_ex2(fmaf(__uint_as_float(r[2 * i + 1]), scale_log2, mneg)) : 0.f;
+                        pk[i] = pack_bf16(p0, p1);
+                        const float2 rr = unpack_bf16(pk[i]);     // sum what the PV product will actually see
+                        sum += rr.x + rr.y;
+                    }
+                    tmem_st_32x8(tbase + (c0 >> 1), pk);
+                };
+                c = 0;
+                for (; c + 32 <= Nk; c += 32) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(tbase + c, r);
+                    tmem_ld_wait();
+                    do16(r, c);
+                    do16(r + 16, c + 16);
+                }
+                if (c < Nk) {
+                    uint32_t r[16];
+                    tmem_ld_32x16(tbase + c, r);
+                    tmem_ld_wait();
+                    do16(r, c);
+                }
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(p_ready(g));
+                const float inv = 1.0f / sum;
+                const bool row_ok = r_in_head < T;
+                if (row_ok) lse[(long long)w * T + r_in_head] = mx * scale + logf(sum);
+                // epilogue: O / sum -> bf16 -> out[b, row, h, :]
+                mbar_wait(o_ready(g), hp);
+                tc_fence_after();
+                bf16* dst = out + (((long long)b * T + r_in_head) * H + h) * 64;
+#pragma unroll
+                for (int c2 = 0; c2 < 64; c2 += 32) {
+                    uint32_t r[32];
+                    tmem_ld_32x32(tbase + ATC_O_COL + c2, r);
+                    tmem_ld_wait();
+                    if (c2 == 32) {       // all TMEM reads of this tile are done: hand the slot back
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(slot_free(g));
+                    }
+                    if (row_ok) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            uint4 o;
+                            o.x = pack_bf16(__uint_as_float(r[8 * i]) * inv, __uint_as_float(r[8 * i + 1]) * inv);
+                            o.y = pack_bf16(__uint_as_float(r[8 * i + 2]) * inv, __uint_as_float(r[8 * i + 3]) * inv);
+                            o.z = pack_bf16(__uint_as_float(r[8 * i + 4]) * inv, __uint_as_float(r[8 * i + 5]) * inv);
+                            o.w = pack_bf16(__uint_as_float(r[8 * i + 6]) * inv, __uint_as_float(r[8 * i + 7]) * inv);
+                            reinterpret_cast<uint4*>(dst + c2)[i] = o;
+                        }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<1>(tmem, ATC_TMEM_COLS);
+    }
+}
+
+// =============================================================================================
+// Backward (persistent). Per (batch, head) the producer stages the FULL Q, K, V and dO tiles of the head once
+// (2-deep ring) and computes the per-token statistics lse*log2e and delta = rowsum(dO * O) * scale; the head is
+// then processed as 2*nt work items that all read those resident tiles:
+//   items 0..nt-1   "KV" item, 128 keys:    S^T = K_t Q^T, dP^T = V_t dO^T  ->  dV_t = P^T dO, dK_t = dS^T Q
+//   items nt..2nt-1 "Q" item, 128 queries:  S   = Q_t K^T, dP   = dO_t V^T  ->  dQ_t = dS K
+// Both are the same program on different operands: acc0 = X Y^T, acc1 = X' Y'^T (UMMA 128 x Nk x 64 into two
+// 256-column TMEM regions); 16 math warps (4 TMEM lane quarters x 4 column quarters) turn (acc0, acc1) into
+// P = exp2(acc0*c - lse) and dS = P (acc1*scale - delta), store them as bf16 pairs IN PLACE (each column quarter
+// packs into the front of its own column range), and the second round of UMMAs (A operand from TMEM, B = the
+// resident full tiles re-used as MN-major operands) produces the 128 x 64 gradients. The statistics index
+// (lse, delta) is the column for KV items and the row for Q items.
+// =============================================================================================
+constexpr int ATB_MATH_WARPS = 16;
+constexpr int ATB_THREADS = 64 + ATB_MATH_WARPS * 32;   // warp 0: TMA + statistics, warp 1: TMEM alloc + MMA issue
+constexpr int ATB_TMEM_COLS = 512;
+constexpr int ATB_OUT_COL = 192;      // gradient accumulators live in columns [192, 256) of each region
+constexpr int ATB_TAIL_PAD = 8192;    // a 128-row X tile starting at row 128 over-reads a 208-row stage by 6 KB
+
+__global__ void __launch_bounds__(ATB_THREADS, 1)
+attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
+                        const bf16* __restrict__ out, const bf16* __restrict__ dout, const float* __restrict__ lse,
+                        bf16* __restrict__ dqkv, int num_heads_total, int T, int Nk, int H, float scale_log2,
+                        float scale) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t tile_bytes = (uint32_t)Nk * 128u;
+    const uint32_t tile_stride = (tile_bytes + 1023u) & ~1023u;
+    const uint32_t stage_bytes = 4 * tile_stride;                       // Q, K, V, dO
+    const uint32_t stat_base = smem_base + 2 * stage_bytes + ATB_TAIL_PAD;   // per stage: lse2 [Nk], delta*scale [Nk]
+    const uint32_t bar_base = stat_base + 2u * 2u * Nk * 4u;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto stat_bar = [&](int s) { return bar_base + 16u + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 32u + 8u * s; };
+    const uint32_t s_ready = bar_base + 48u, p_ready = bar_base + 56u, o_ready = bar_base + 64u, t_free = bar_base + 72u;
+    const uint32_t tmem_slot = bar_base + 80u;
+    uint8_t* gen = smem_raw - smem_u32(smem_raw);                       // generic pointer = gen + shared address
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen + tmem_slot);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nt = (T + ATC_BM - 1) / ATC_BM;
+    const int nitems = 2 * nt;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmQKV);
+        prefetch_tmap(&tmDO);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(full_bar(i), 1);
+            mbar_init(stat_bar(i), 1);
+            mbar_init(empty_bar(i), 1);
+        }
+        mbar_init(s_ready, 1);
+        mbar_init(p_ready, ATB_MATH_WARPS);
+        mbar_init(o_ready, 1);
+        mbar_init(t_free, ATB_MATH_WARPS);
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc<1>(tmem_slot, ATB_TMEM_COLS);
+        tmem_relinquish<1>();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot_ptr;
+    const uint32_t acc0 = tmem, acc1 = tmem + 256;
+
+    // column quarters: 16-column chunks dealt 4,3,3,3 (for Nk = 208); cq range = [cq_begin(q), cq_begin(q+1))
+    const int nchunks = Nk / 16;
+    auto cq_begin = [&](int q) { return 16 * ((nchunks * q + 3) / 4); };
+    auto packed_col = [&](int src_col) {       // where the bf16 pair holding source column src_col lives
+        int q = 3;
+        while (q > 0 && src_col < cq_begin(q)) --q;
+        const int c0 = cq_begin(q);
+        return c0 + ((src_col - c0) >> 1);
+    };
+
+    if (warp == 0) {
+        // ===================== TMA producer + per-token statistics =====================
+        const float LOG2E = 1.4426950408889634f;
+        const long long os = (long long)H * 64;
+        int it = 0;
+        for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
+            const int s = it & 1;
+            const uint32_t ph = (it >> 1) & 1;
+            const int b = w / H, h = w % H;
+            if (lane == 0) mbar_wait(empty_bar(s), ph ^ 1u);
+            __syncwarp();
+            if (lane == 0) {
+                const uint32_t sQ = smem_base + s * stage_bytes;
+                mbar_arrive_expect_tx(full_bar(s), 4 * tile_bytes);
+                tma_load_4d(sQ, &tmQKV, full_bar(s), 0, 0, h, b);
+                tma_load_4d(sQ + tile_stride, &tmQKV, full_bar(s), 0, 0, H + h, b);
+                tma_load_4d(sQ + 2 * tile_stride, &tmQKV, full_bar(s), 0, 0, 2 * H + h, b);
+                tma_load_4d(sQ + 3 * tile_stride, &tmDO, full_bar(s), 0, 0, h, b);
+            }
+            float* sLse2 = reinterpret_cast<float*>(gen + stat_base + (uint32_t)s * 2u * Nk * 4u);
+            float* sDelta = sLse2 + Nk;
+            const bf16* gO = out + (long long)b * T * os + (long long)h * 64;
+            const bf16* gdO = dout + (long long)b * T * os + (long long)h * 64;
+            const float* L = lse + (long long)w * T;
+            // one lane per token row (rows are 128 B): all loads of a lane are independent -> deep memory parallelism
+            for (int t = lane; t < Nk; t += 32) {
+                float d = 0.f;
+                if (t < T) {
+                    const uint4* po = reinterpret_cast<const uint4*>(gO + (long long)t * os);
+                    const uint4* pd = reinterpret_cast<const uint4*>(gdO + (long long)t * os);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const uint4 a = __ldg(po + i), c = __ldg(pd + i);
+                        const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, cw[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const float2 fa = unpack_bf16(aw[k]), fc = unpack_bf16(cw[k]);
+                            d = fmaf(fa.x, fc.x, fmaf(fa.y, fc.y, d));
+                        }
+                    }
+                }
+                sDelta[t] = d * scale;
+                sLse2[t] = t < T ? L[t] * LOG2E : INFINITY;       // +inf -> P = 0 for padded positions
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(stat_bar(s));
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc1 = make_idesc_bf16(ATC_BM, Nk, 0, 0);
+            const uint32_t idesc2 = make_idesc_bf16(ATC_BM, 64, 0, 1);
+            const int ksteps = Nk / 16;
+            int it = 0, j = 0;
+            for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
+                const int s = it & 1;
+                const uint32_t ph = (it >> 1) & 1;
+                const uint32_t sQ = smem_base + s * stage_bytes, sK = sQ + tile_stride, sV = sK + tile_stride,
+                               sdO = sV + tile_stride;
+                mbar_wait(full_bar(s), ph);
+                tc_fence_after();
+                for (int item = 0; item < nitems; ++item, ++j) {
+                    const bool kv_item = item < nt;
+                    const uint32_t roff = (uint32_t)(kv_item ? item : item - nt) * (ATC_BM * 128);
+                    const uint32_t sX = (kv_item ? sK : sQ) + roff, sX2 = (kv_item ? sV : sdO) + roff;
+                    const uint32_t sY = kv_item ? sQ : sK, sY2 = kv_item ? sdO : sV;
+                    mbar_wait(t_free, (uint32_t)(j & 1) ^ 1u);
+                    tc_fence_after();
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_bf16<1>(acc0, make_smem_desc_sw128(sX + k * 32, 1024, 0),
+                                     make_smem_desc_sw128(sY + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_bf16<1>(acc1, make_smem_desc_sw128(sX2 + k * 32, 1024, 0),
+                                     make_smem_desc_sw128(sY2 + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
+                    umma_commit(s_ready);
+                    mbar_wait(p_ready, (uint32_t)(j & 1));
+                    tc_fence_after();
+                    if (kv_item) {
+                        for (int k = 0; k < ksteps; ++k)      // dV_t = P^T dO
+                            umma_bf16_ts(acc0 + ATB_OUT_COL, acc0 + packed_col(16 * k),
+                                         make_smem_desc_sw128(sY2 + k * 2048, 1024, 0), idesc2, k > 0 ? 1u : 0u);
+                    }
+                    for (int k = 0; k < ksteps; ++k)          // dK_t = dS^T Q   or   dQ_t = dS K
+                        umma_bf16_ts(acc1 + ATB_OUT_COL, acc1 + packed_col(16 * k),
+                                     make_smem_desc_sw128(sY + k * 2048, 1024, 0), idesc2, k > 0 ? 1u : 0u);
+                    umma_commit(o_ready);
+                }
+                umma_commit(empty_bar(s));      // every MMA reading this stage has retired
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===================== math + epilogue warps =====================
+        const int mw = warp - 2;
+        const int quarter = warp & 3;            // TMEM lane quarter this warp may access
+        const int cq = mw >> 2;                  // column quarter
+        const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
+        const int c_begin = cq_begin(cq), c_end = cq == 3 ? Nk : cq_begin(cq + 1);
+        const long long rs = 3LL * H * 64;
+        int it = 0, j = 0;
+        for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
+            const int s = it & 1;
+            const uint32_t ph = (it >> 1) & 1;
+            const int b = w / H, h = w % H;
+            const float* sLse2 = reinterpret_cast<const float*>(gen + stat_base + (uint32_t)s * 2u * Nk * 4u);
+            const float* sDelta = sLse2 + Nk;
+            mbar_wait(stat_bar(s), ph);
+            for (int item = 0; item < nitems; ++item, ++j) {
+                const bool kv_item = item < nt;
+                const int row = (kv_item ? item : item - nt) * ATC_BM + quarter * 32 + lane;
+                const bool row_ok = row < T;
+                const float row_lse2 = sLse2[min(row, Nk - 1)], row_delta = sDelta[min(row, Nk - 1)];
+                mbar_wait(s_ready, (uint32_t)(j & 1));
+                tc_fence_after();
+                for (int c = c_begin; c < c_end; c += 16) {
+                    uint32_t sv[16], dp[16];
+                    tmem_ld_32x16(acc0 + lane_off + c, sv);
+                    tmem_ld_32x16(acc1 + lane_off + c, dp);
+                    float l2[16], dl[16];
+                    if (kv_item) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float4 a = reinterpret_cast<const float4*>(sLse2 + c)[i];
+                            const float4 d = reinterpret_cast<const float4*>(sDelta + c)[i];
+                            l2[4 * i] = a.x; l2[4 * i + 1] = a.y; l2[4 * i + 2] = a.z; l2[4 * i + 3] = a.w;
+                            dl[4 * i] = d.x; dl[4 * i + 1] = d.y; dl[4 * i + 2] = d.z; dl[4 * i + 3] = d.w;
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) { l2[i] = row_lse2; dl[i] = row_delta; }
+                    }
+                    tmem_ld_wait();
+                    float p[16], ds[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        p[i] = fast_ex2(fmaf(__uint_as_float(sv[i]), scale_log2, -l2[i]));
+                        ds[i] = p[i] * fmaf(__uint_as_float(dp[i]), scale, -dl[i]);
+                    }
+                    if (!kv_item && c + 16 > T) {      // Q item: padded key columns must not contribute to dQ
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) if (c + i >= T) ds[i] = 0.f;
+                    }
+                    uint32_t pk[8];
+                    const int pc = c_begin + ((c - c_begin) >> 1);
+                    if (kv_item) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) pk[i] = pack_bf16(p[2 * i], p[2 * i + 1]);
+                        tmem_st_32x8(acc0 + lane_off + pc, pk);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) pk[i] = pack_bf16(ds[2 * i], ds[2 * i + 1]);
+                    tmem_st_32x8(acc1 + lane_off + pc, pk);
+                }
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(p_ready);
+
+                // epilogue: each column quarter converts 16 of the 64 gradient columns
+                mbar_wait(o_ready, (uint32_t)(j & 1));
+                tc_fence_after();
+                uint32_t r0[16], r1[16];
+                tmem_ld_32x16(acc1 + lane_off + ATB_OUT_COL + cq * 16, r1);
+                if (kv_item) tmem_ld_32x16(acc0 + lane_off + ATB_OUT_COL + cq * 16, r0);
+                tmem_ld_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(t_free);
+                if (row_ok) {
+                    bf16* base = dqkv + ((long long)b * T + row) * rs + (long long)h * 64 + cq * 16;
+                    auto emit = [&](const uint32_t (&r)[16], bf16* dst) {
+                        uint4 o0, o1;
+                        o0.x = pack_bf16(__uint_as_float(r[0]), __uint_as_float(r[1]));
+                        o0.y = pack_bf16(__uint_as_float(r[2]), __uint_as_float(r[3]));
+                        o0.z = pack_bf16(__uint_as_float(r[4]), __uint_as_float(r[5]));
+                        o0.w = pack_bf16(__uint_as_float(r[6]), __uint_as_float(r[7]));
+                        o1.x = pack_bf16(__uint_as_float(r[8]), __uint_as_float(r[9]));
+                        o1.y = pack_bf16(__uint_as_float(r[10]), __uint_as_float(r[11]));
+                        o1.z = pack_bf16(__uint_as_float(r[12]), __uint_as_float(r[13]));
+                        o1.w = pack_bf16(__uint_as_float(r[14]), __uint_as_float(r[15]));
+                        reinterpret_cast<uint4*>(dst)[0] = o0;
+                        reinterpret_cast<uint4*>(dst)[1] = o1;
+                    };
+                    if (kv_item) {
+                        emit(r1, base + (long long)H * 64);        // dK
+                        emit(r0, base + 2LL * H * 64);             // dV
+                    } else {
+                        emit(r1, base);                            // dQ
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<1>(tmem, ATB_TMEM_COLS);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+static PFN_cuTensorMapEncodeTiled atc_encode_fn() {
+    static PFN_cuTensorMapEncodeTiled fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled>(ptr);
+    });
+    return fn;
+}
+
+// 4-D view of a packed [B, T, S, 64] bf16 tensor (S slabs of 64 per token: 3*H for qkv, H for out/dout):
+// dims (d, t, slab, b); a box is [rows x 64] of one slab; rows beyond T are zero-filled by TMA.
+int make_tmap_rows64(CUtensorMap* tm, const void* base, int B, int T, int slabs, int box_rows) {
+    PFN_cuTensorMapEncodeTiled enc = atc_encode_fn();
+    if (!enc) return set_error(-2, "cuTensorMapEncodeTiled not available (no CUDA driver?)");
+    cuuint64_t dims[4] = {64, (cuuint64_t)T, (cuuint64_t)slabs, (cuuint64_t)B};
+    cuuint64_t strides[3] = {(cuuint64_t)slabs * 64 * 2, 64 * 2, (cuuint64_t)T * slabs * 64 * 2};
+    cuuint32_t box[4] = {64, (cuuint32_t)box_rows, 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(-3, "cuTensorMapEncodeTiled (attention) failed (%d)", (int)r);
+    return 0;
+}
+
+int attention_fwd_tc_launch(const bf16* qkv, bf16* out, float* lse, int batch, int tokens, int heads, float scale,
+                            cudaStream_t stream) {
+    const int Nk = (tokens + 15) & ~15;
+    const int nt = (tokens + ATC_BM - 1) / ATC_BM;
+    CUtensorMap tmQ, tmKV;
+    int rc = make_tmap_rows64(&tmQ, qkv, batch, tokens, 3 * heads, nt * ATC_BM);
+    if (rc) return rc;
+    rc = make_tmap_rows64(&tmKV, qkv, batch, tokens, 3 * heads, Nk);
+    if (rc) return rc;
+    const size_t kv_stride = ((size_t)Nk * 128 + 1023) & ~(size_t)1023;
+    const size_t smem = 1024 + 2 * (ATC_Q_ROWS * 128 + 2 * kv_stride) + 128;
+    B200_CUDA(cudaFuncSetAttribute(attention_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int total = batch * heads;
+    const int grid = total < sm_count() ? total : sm_count();
+    attention_fwd_tc_kernel<<<grid, ATC_THREADS, smem, stream>>>(tmQ, tmKV, out, lse, total, tokens, Nk, heads,
+                                                               scale * 1.4426950408889634f, scale);
+    B200_LAUNCH_CHECK();
+    return 0;
+}
+
+int attention_bwd_tc_launch(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, bf16* dqkv, int batch,
+                            int tokens, int heads, float scale, cudaStream_t stream) {
+    const int Nk = (tokens + 15) & ~15;
+    CUtensorMap tq, td;
+    int rc = make_tmap_rows64(&tq, qkv, batch, tokens, 3 * heads, Nk);
+    if (rc) return rc;
+    rc = make_tmap_rows64(&td, dout, batch, tokens, heads, Nk);
+    if (rc) return rc;
+    const size_t tile_stride = ((size_t)Nk * 128 + 1023) & ~(size_t)1023;
+    const size_t smem = 1024 + 2 * 4 * tile_stride + ATB_TAIL_PAD + 2 * 2 * (size_t)Nk * 4 + 128;
+    B200_CHECK_ARG(smem <= 232448, "attention_bwd: %d tokens need %zu bytes of shared memory", tokens, smem);
+    B200_CUDA(cudaFuncSetAttribute(attention_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int total = batch * heads;
+    const int grid = total < sm_count() ? total : sm_count();
+    attention_bwd_tc_kernel<<<grid, ATB_THREADS, smem, stream>>>(tq, td, out, dout, lse, dqkv, total, tokens, Nk, heads,
+                                                               scale * 1.4426950408889634f, scale);
+    B200_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // namespace b200vit
