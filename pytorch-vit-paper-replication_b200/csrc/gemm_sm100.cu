@@ -43,10 +43,9 @@ constexpr int GEMM_SMEM_BYTES = STAGES * STAGE_BYTES + NUM_EPI_WARPS * EPI_STAGE
 // 2-CTA (cta_group::2) variant: a CTA pair owns a 256x256 output tile. Each CTA stages its own 128 rows of A and
 // HALF of the B tile (128 of the 256 N-rows); the pair's tensor cores read both halves, so every CTA moves
 // 32 KB per k-block instead of 48 KB (1.5x less L2->smem and smem traffic per FLOP) and the ring gets 6 stages.
-constexpr int STAGES2 = 6;
 constexpr int B2_STAGE_BYTES = (BN / 2) * BK * 2;   // 16 KB
 constexpr int STAGE2_BYTES = A_STAGE_BYTES + B2_STAGE_BYTES;
-constexpr int GEMM2_SMEM_BYTES = STAGES2 * STAGE2_BYTES + NUM_EPI_WARPS * EPI_STAGE_BYTES + 1024 + 256;
+
 
 enum GemmOp { OP_NT = 0, OP_NN = 1, OP_TN = 2 };
 enum GemmEpi {
@@ -70,6 +69,14 @@ struct GemmParams {
     DropoutParams drop;
     int row_period;
     int vec_ok;   // leading dimensions / N allow 16-byte vector access
+};
+// The ALU-heavy epilogues (GELU / dGELU, with dropout) run 16 epilogue warps (4 per scheduler, 64 columns each)
+// and give up one pipeline stage for the extra staging tiles; the others run 8 warps and a 6-deep ring.
+template <int EPI> struct Cfg2 {
+    static constexpr int EW = (EPI == EPI_BIAS_GELU || EPI == EPI_DGELU) ? 16 : 8;
+    static constexpr int STAGES = EW == 16 ? 5 : 6;
+    static constexpr int THREADS = 128 + EW * 32;
+    static constexpr int SMEM = STAGES * STAGE2_BYTES + EW * EPI_STAGE_BYTES + 1024 + 256;
 };
 
 // -------------------------------------------------------------------------------------------------
@@ -111,6 +118,27 @@ __device__ __forceinline__ void aux_prefetch(const GemmParams& p, int lane, int 
                                              uint32_t (&a)[AuxRegs<EPI>::N]) {
     if (!(AuxRegs<EPI>::F32 || AuxRegs<EPI>::B16)) return;
     if (p.aux == nullptr || col0 >= p.N) return;
+    const bool interior = p.vec_ok && col0 + 32 <= p.N && row_base + 32 <= p.M;
+    if (interior && EPI == EPI_BIAS_RES) {
+        const float* ptr = reinterpret_cast<const float*>(p.aux) + (long long)(row_base + (lane >> 3)) * p.ldaux + col0 + (lane & 7) * 4;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const uint4 q = *reinterpret_cast<const uint4*>(ptr + (long long)(it * 4) * p.ldaux);
+            a[(4 * it) % AuxRegs<EPI>::N] = q.x; a[(4 * it + 1) % AuxRegs<EPI>::N] = q.y;
+            a[(4 * it + 2) % AuxRegs<EPI>::N] = q.z; a[(4 * it + 3) % AuxRegs<EPI>::N] = q.w;
+        }
+        return;
+    }
+    if (interior && EPI == EPI_DGELU) {
+        const bf16* ptr = reinterpret_cast<const bf16*>(p.aux) + (long long)(row_base + (lane >> 2)) * p.ldaux + col0 + (lane & 3) * 8;
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const uint4 q = *reinterpret_cast<const uint4*>(ptr + (long long)(it * 8) * p.ldaux);
+            a[(4 * it) % AuxRegs<EPI>::N] = q.x; a[(4 * it + 1) % AuxRegs<EPI>::N] = q.y;
+            a[(4 * it + 2) % AuxRegs<EPI>::N] = q.z; a[(4 * it + 3) % AuxRegs<EPI>::N] = q.w;
+        }
+        return;
+    }
     if (AuxRegs<EPI>::F32) {
         const float* aux = reinterpret_cast<const float*>(p.aux);
 #pragma unroll
@@ -163,7 +191,16 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
     const bool fullw = p.vec_ok && col0 + 32 <= p.N;   // warp-uniform: every 16-byte piece of the chunk is valid
 
     // ---- cooperative movers (whole warp) -----------------------------------------------------------
+    // warp-uniform: the whole 32x32 chunk is inside the matrix and 16-byte accesses are legal -> no per-piece checks
+    const bool interior = fullw && row_base + 32 <= p.M;
     auto store_f32_tile = [&](float* base, long long ld) {
+        if (interior && EPI != EPI_PATCH) {
+            float* ptr = base + (long long)(row_base + (lane >> 3)) * ld + col0 + (lane & 7) * 4;
+#pragma unroll
+            for (int it = 0; it < 8; ++it)
+                *reinterpret_cast<uint4*>(ptr + (long long)(it * 4) * ld) = lds128(stg + stg_off_f32(it * 4 + (lane >> 3), lane & 7));
+            return;
+        }
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
             const int r = it * 4 + (lane >> 3), ch = lane & 7;
@@ -183,6 +220,17 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
         }
     };
     auto accum_f32_tile = [&](float* base, long long ld) {
+        if (interior) {
+            float* ptr = base + (long long)(row_base + (lane >> 3)) * ld + col0 + (lane & 7) * 4;
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const uint4 q = lds128(stg + stg_off_f32(it * 4 + (lane >> 3), lane & 7));
+                asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};"
+                             ::"l"(ptr + (long long)(it * 4) * ld), "f"(__uint_as_float(q.x)), "f"(__uint_as_float(q.y)),
+                               "f"(__uint_as_float(q.z)), "f"(__uint_as_float(q.w)) : "memory");
+            }
+            return;
+        }
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
             const int r = it * 4 + (lane >> 3), ch = lane & 7;
@@ -204,6 +252,13 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
         }
     };
     auto store_b16_tile = [&](bf16* base, long long ld) {
+        if (interior) {
+            bf16* ptr = base + (long long)(row_base + (lane >> 2)) * ld + col0 + (lane & 3) * 8;
+#pragma unroll
+            for (int it = 0; it < 4; ++it)
+                *reinterpret_cast<uint4*>(ptr + (long long)(it * 8) * ld) = lds128(stg + stg_off_b16(it * 8 + (lane >> 2), lane & 3));
+            return;
+        }
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
             const int r = it * 8 + (lane >> 2), ch = lane & 3;
@@ -529,15 +584,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 // The 2-CTA kernel (cluster of 2, cta_group::2 MMA, UMMA 256x256x16)
 // -------------------------------------------------------------------------------------------------
 template <bool A_MN, bool B_MN, int EPI>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Cfg2<EPI>::THREADS, 1)
 gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const GemmParams p) {
+    constexpr int STAGES2 = Cfg2<EPI>::STAGES;
+    constexpr int EW = Cfg2<EPI>::EW;
+    constexpr int CHUNKS = 8 / (EW / 4);     // 32-column chunks per epilogue warp
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t smem_a = smem_base;
     const uint32_t smem_b = smem_base + STAGES2 * A_STAGE_BYTES;
     const uint32_t smem_stage = smem_base + STAGES2 * STAGE2_BYTES;
-    const uint32_t bar_base = smem_stage + NUM_EPI_WARPS * EPI_STAGE_BYTES;
+    const uint32_t bar_base = smem_stage + EW * EPI_STAGE_BYTES;
     auto full_bar = [&](int s) { return bar_base + 8u * s; };                       // used in the leader CTA
     auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES2 + s); };          // one per CTA
     auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * STAGES2 + s); };      // one per CTA
@@ -556,7 +614,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES2; ++s) { mbar_init(full_bar(s), 2); mbar_init(empty_bar(s), 1); }
-        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 2 * NUM_EPI_WARPS); }
+        for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 2 * EW); }
         fence_barrier_init();
     }
     if (warp == 2) {
@@ -656,7 +714,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         // ===================== Epilogue (both CTAs, own 128 rows) =====================
         const int ew = warp - 4;
         const int quarter = warp & 3;
-        const int half = ew >> 2;
+        const int colgrp = ew >> 2;          // which (256 / (EW/4))-column slice of the tile
         int iter = 0;
         for (int w = cluster_id; w < total_work; w += num_clusters, ++iter) {
             int m0, n0, kb0, kb1;
@@ -666,20 +724,20 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             const int row_base = m0 + quarter * 32;
             const uint32_t stg = smem_stage + ew * EPI_STAGE_BYTES;
             uint32_t aux_next[AuxRegs<EPI>::N], aux_cur[AuxRegs<EPI>::N];
-            aux_prefetch<EPI>(p, lane, row_base, n0 + half * 128, aux_next);   // before the accumulator is even ready
+            aux_prefetch<EPI>(p, lane, row_base, n0 + colgrp * (CHUNKS * 32), aux_next);   // before the accumulator is even ready
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                const int col_in_tile = half * 128 + c * 32;
+            for (int c = 0; c < CHUNKS; ++c) {
+                const int col_in_tile = colgrp * (CHUNKS * 32) + c * 32;
                 const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + col_in_tile);
                 uint32_t r[32];
                 tmem_ld_32x32(taddr, r);
 #pragma unroll
                 for (int i = 0; i < AuxRegs<EPI>::N; ++i) aux_cur[i] = aux_next[i];
-                if (c < 3) aux_prefetch<EPI>(p, lane, row_base, n0 + col_in_tile + 32, aux_next);
+                if (c < CHUNKS - 1) aux_prefetch<EPI>(p, lane, row_base, n0 + col_in_tile + 32, aux_next);
                 tmem_ld_wait();
-                if (c == 3) {
+                if (c == CHUNKS - 1) {
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive_cluster(tempty_bar(acc), 0);    // the MMA issuer lives in CTA 0
@@ -847,12 +905,15 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
     B200_CHECK_ARG(kern != nullptr, "gemm: no kernel for op %d epi %d", op, epi);
 
     if (two_cta) {
-        B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM2_SMEM_BYTES));
+        const bool heavy = (epi == EPI_BIAS_GELU || epi == EPI_DGELU);
+        const int smem2 = heavy ? Cfg2<EPI_BIAS_GELU>::SMEM : Cfg2<EPI_BF16>::SMEM;
+        const int threads2 = heavy ? Cfg2<EPI_BIAS_GELU>::THREADS : Cfg2<EPI_BF16>::THREADS;
+        B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
         const int tiles_m2 = (M + 2 * BM - 1) / (2 * BM);
         const int total = tiles_m2 * p.tiles_n * p.splits;
         const int pairs = sm_count() / 2;
         const int grid = 2 * (total < pairs ? total : pairs);
-        kern<<<grid, GEMM_THREADS, GEMM2_SMEM_BYTES, stream>>>(tmA, tmB, p);   // cluster dims are compiled in
+        kern<<<grid, threads2, smem2, stream>>>(tmA, tmB, p);   // cluster dims are compiled in
     } else {
         B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
         const int total = p.tiles_m * p.tiles_n * p.splits;
