@@ -146,6 +146,20 @@ int b200vit_scale_by_scalar(const float* src, const float* scalar_dev, float* ds
 int b200vit_l2norm_sq(const void* const* ptrs_dev, const long long* sizes_dev, int num_tensors, long long max_size,
                       float* partials, int num_partials, float* out_sumsq, void* stream);
 
+/* Same result as b200vit_l2norm_sq, for callers that cannot provide (or allocate) the scratch buffer: a process
+ * whose device memory was handed to its own arena up front, so that cudaMalloc fails, or a loop that cannot afford
+ * the device-wide synchronisation cudaMalloc / cudaFree imply. The partial sums go to a fixed 1 MiB array that lives
+ * inside the library image on every GPU that loads it. This entry point has no counterpart in the reference.
+ *   - Limit: num_tensors * ceil(max_size / 8192) <= 262144 partial sums; larger problems return an argument error
+ *     (ViT-B/16 needs 43 928, ViT-L/16 151 552).
+ *   - It calls no cudaMalloc / cudaFree / allocating library routine.
+ *   - The first call on each device looks up the device address of the built-in array (cudaGetSymbolAddress);
+ *     make that first call before starting any stream capture.
+ *   - All calls on a device share the one array: two calls that overlap on the GPU (different streams) race on it.
+ *     Nothing has to be cleared between calls -- every slot that is read is written first in the same call. */
+int b200vit_l2norm_sq_noalloc(const void* const* ptrs_dev, const long long* sizes_dev, int num_tensors,
+                              long long max_size, float* out_sumsq, void* stream);
+
 /* One fused optimizer step over all parameters: torch.optim.Adam as configured by the reference recipe
  * (coupled L2 weight decay per param group; notebook optimizer cell, stepped at going_modular/engine.py:66),
  * or AdamW when decoupled != 0.

@@ -37,6 +37,7 @@ _SIGNATURES = {
     "b200vit_softmax_ce": [_p, _p, _p, _p, _p, _i, _i, _p],
     "b200vit_scale_by_scalar": [_p, _p, _p, _ll, _p],
     "b200vit_l2norm_sq": [_p, _p, _i, _ll, _p, _i, _p, _p],
+    "b200vit_l2norm_sq_noalloc": [_p, _p, _i, _ll, _p, _p],
     "b200vit_adam_step": [_p, _i, _ll, _p, _p, _i, _f, _f, _f, _i, _i, _p, _f, _f, _p],
 }
 
@@ -107,7 +108,8 @@ def check(rc: int, what: str) -> None:
 
 
 # CUDA kernels launched by one successful call of each entry point (memsets are not counted).
-KERNELS_PER_CALL = {"b200vit_attention_bwd": 3, "b200vit_l2norm_sq": 2, "b200vit_head_bwd": 2}
+KERNELS_PER_CALL = {"b200vit_attention_bwd": 3, "b200vit_l2norm_sq": 2, "b200vit_l2norm_sq_noalloc": 2,
+                    "b200vit_head_bwd": 2}
 launch_count = 0
 
 

@@ -18,7 +18,7 @@ __all__ = [
     "OP_NT", "OP_NN", "OP_TN", "EPI_BF16", "EPI_BIAS_GELU", "EPI_BIAS_RES", "EPI_DGELU", "EPI_ACCUM", "EPI_F32",
     "EPI_PATCH", "gemm", "cast_bf16", "im2col_patches", "class_token_rows", "embed_param_grads", "patch_grad_rows",
     "layernorm_fwd", "layernorm_bwd", "colsum_bf16", "dropout_cast", "attention_fwd", "attention_bwd", "head_fwd",
-    "head_bwd", "softmax_ce", "scale_by_scalar", "l2norm_sq", "adam_step", "stream_ptr", "split_k_for",
+    "head_bwd", "softmax_ce", "scale_by_scalar", "l2norm_sq", "l2norm_sq_noalloc", "adam_step", "stream_ptr", "split_k_for",
 ]
 
 
@@ -149,6 +149,12 @@ def scale_by_scalar(src, scalar_dev, dst) -> None:
 def l2norm_sq(ptrs_dev, sizes_dev, num_tensors, max_size, partials, out_sumsq) -> None:
     _C.call("b200vit_l2norm_sq", _ptr(ptrs_dev), _ptr(sizes_dev), num_tensors, max_size, _ptr(partials),
             partials.numel(), _ptr(out_sumsq), stream_ptr(out_sumsq.device))
+
+
+def l2norm_sq_noalloc(ptrs_dev, sizes_dev, num_tensors, max_size, out_sumsq) -> None:
+    """Gradient sum of squares without any scratch argument (built-in 1 MiB scratch; see include/b200vit.h)."""
+    _C.call("b200vit_l2norm_sq_noalloc", _ptr(ptrs_dev), _ptr(sizes_dev), num_tensors, max_size, _ptr(out_sumsq),
+            stream_ptr(out_sumsq.device))
 
 
 def adam_step(table_dev, num_tensors, max_size, lrs, wds, beta1, beta2, eps, step, decoupled, grad_sumsq, max_norm,

@@ -10,6 +10,10 @@
 #include "common.cuh"
 #include "launchers.h"
 
+#include "../../include/b200vit.h"
+
+#include <mutex>
+
 namespace b200vit {
 
 constexpr int MT_BLOCK = 256;
@@ -78,6 +82,68 @@ int l2norm_sq_launch(const float* const* ptrs_dev, const long long* sizes_dev, i
     B200_LAUNCH_CHECK();
     return 0;
 }
+
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free gradient norm.
+//
+// b200vit_l2norm_sq() above needs a scratch buffer for its per-block partial sums, and somebody has to allocate
+// it. Some hosts cannot: a serving process that gave all of HBM to its own arena at start-up (a later cudaMalloc
+// simply fails), or a training loop that must not stall -- cudaMalloc / cudaFree synchronise the whole device,
+// which would serialise the compute and communication streams of an overlapped data-parallel step.
+// For those callers the partial sums live in a fixed array inside the library image instead. The price: every
+// GPU that loads libb200vit.so carries L2NORM_STATIC_PARTIALS * 4 bytes (1 MiB) until the process exits, and
+// problems that need more partial sums than that are refused.
+//
+// NB: in host code `g_l2norm_static_scratch` is only a handle for the symbol, not a device address; the address
+// a kernel can use comes from cudaGetSymbolAddress(), queried once per device with that device current.
+// ---------------------------------------------------------------------------------------------
+constexpr int L2NORM_STATIC_PARTIALS = 262144;
+static __device__ __align__(256) float g_l2norm_static_scratch[L2NORM_STATIC_PARTIALS];
+
+static int l2norm_static_scratch(float** out) {
+    static std::mutex mu;
+    static float* per_device[64] = {nullptr};
+    int dev = -1;
+    B200_CUDA(cudaGetDevice(&dev));
+    B200_CHECK_ARG(dev >= 0 && dev < 64, "l2norm_sq_noalloc: unsupported device ordinal %d", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (per_device[dev] == nullptr) {
+        void* p = nullptr;
+        B200_CUDA(cudaGetSymbolAddress(&p, g_l2norm_static_scratch));
+        per_device[dev] = static_cast<float*>(p);
+    }
+    *out = per_device[dev];
+    return 0;
+}
+
+}  // namespace b200vit
+
+extern "C" int b200vit_l2norm_sq_noalloc(const void* const* ptrs_dev, const long long* sizes_dev, int num_tensors,
+                                         long long max_size, float* out_sumsq, void* stream) {
+    using namespace b200vit;
+    B200_CHECK_ARG(ptrs_dev && sizes_dev && out_sumsq, "l2norm_sq_noalloc: null pointer");
+    B200_CHECK_ARG(num_tensors > 0 && num_tensors <= 65535 && max_size > 0, "l2norm_sq_noalloc: bad sizes");
+    const long long chunks = (max_size + MT_CHUNK - 1) / MT_CHUNK;
+    const long long need = chunks * num_tensors;
+    B200_CHECK_ARG(need <= (long long)L2NORM_STATIC_PARTIALS,
+                   "l2norm_sq_noalloc: %d tensors of up to %lld elements need %lld partial sums but the built-in "
+                   "scratch holds %d; use b200vit_l2norm_sq with a caller-provided buffer",
+                   num_tensors, max_size, need, L2NORM_STATIC_PARTIALS);
+    float* scratch = nullptr;
+    int rc = l2norm_static_scratch(&scratch);
+    if (rc) return rc;
+    // Every (chunk, tensor) block overwrites its own slot (blocks past the end of a tensor write 0), so nothing
+    // left over from the previous call is ever read: no clearing pass is needed.
+    dim3 grid((unsigned)chunks, (unsigned)num_tensors);
+    l2norm_partial_kernel<<<grid, MT_BLOCK, 0, (cudaStream_t)stream>>>((const float* const*)ptrs_dev, sizes_dev, scratch);
+    B200_LAUNCH_CHECK();
+    l2norm_final_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(scratch, (int)need, out_sumsq);
+    B200_LAUNCH_CHECK();
+    return 0;
+}
+
+namespace b200vit {
 
 // ---------------------------------------------------------------------------------------------
 // Adam
