@@ -1,0 +1,67 @@
+"""Multi-GPU check of b200vit.dp.DataParallel on real GPUs (run with torchrun, not collected by pytest):
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tests/dp_check.py
+
+Each rank runs the tiny ViT on its shard of a global batch; after backward the (summed) bucket gradients times
+1/world must equal the gradient of the same model on the full batch computed by rank 0 alone, and after one
+FusedAdam step (grad_scale = 1/world, clip 1.0) all ranks must hold identical weights."""
+import os
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT / "pytorch-vit-paper-replication_b200"))
+sys.path.insert(0, str(ROOT / "tests"))
+
+import torch
+import torch.distributed as dist
+
+from b200vit.dp import DataParallel
+from b200vit.models.vit import ViT
+from b200vit.nn import CrossEntropyLoss
+from b200vit.optim import FusedAdam
+from common import TINY
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    torch.manual_seed(100 + rank)                      # different init per rank: the wrapper must broadcast rank 0's
+    model = ViT(**TINY).to(dev)
+    dp = DataParallel(model, bucket_mb=0.05)
+    g = torch.Generator().manual_seed(5)
+    per = 4
+    X = torch.rand(per * world, 3, 64, 64, generator=g)
+    y = torch.randint(0, 10, (per * world,), generator=g)
+    loss_fn = CrossEntropyLoss()
+    loss = loss_fn(dp(X[rank * per:(rank + 1) * per].to(dev)), y[rank * per:(rank + 1) * per].to(dev))
+    loss.backward()
+    grads = {k: p.grad.detach().clone() * dp.grad_scale for k, p in model.named_parameters()}
+
+    ref = ViT(**TINY).to(dev)
+    ref.load_state_dict(model.state_dict())
+    loss_fn(ref(X.to(dev)), y.to(dev)).backward()
+    worst = 0.0
+    for k, p in ref.named_parameters():
+        if k.endswith("in_proj_bias"):
+            continue
+        err = ((grads[k] - p.grad).norm() / (p.grad.norm() + 1e-12)).item()
+        worst = max(worst, err)
+    assert worst < 2e-2, f"rank {rank}: DP gradient differs from full-batch gradient by {worst}"   # bf16 GEMM noise
+
+    opt = FusedAdam(model.parameters(), lr=1e-3, weight_decay=0.03)
+    opt.grad_scale = dp.grad_scale
+    opt.step(max_norm=1.0)
+    flat = torch.cat([p.detach().flatten() for p in model.parameters()])
+    gathered = [torch.empty_like(flat) for _ in range(world)]
+    dist.all_gather(gathered, flat)
+    assert all(torch.equal(gathered[0], t) for t in gathered), "weights diverged across ranks after the step"
+    if rank == 0:
+        print(f"dp_check ok: world={world} buckets={len(dp.buckets)} worst grad rel err {worst:.2e}", flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
