@@ -21,16 +21,22 @@ namespace b200vit {
 using namespace ptx;
 
 constexpr int ATC_BM = 128;
-constexpr int ATC_THREADS = 320;    // warp 0: TMA producer, warp 1: TMEM alloc + MMA issue, warps 2-9: two softmax groups
+constexpr int ATC_SM_WARPS = 16;    // softmax warps: 2 query tiles x 4 TMEM lane quarters x 2 column halves
+constexpr int ATC_THREADS = 64 + ATC_SM_WARPS * 32;   // warp 0: TMA producer, warp 1: TMEM alloc + MMA issue
 constexpr int ATC_TMEM_COLS = 512;  // two 256-column slots, one per 128-query tile of the head in flight
-constexpr int ATC_O_COL = 128;      // O accumulator columns [128, 192) of a slot: dead upper half of S by then
+constexpr int ATC_O_COL = 192;      // O accumulator columns [192, 256) of a slot: clear of both packed-P ranges
 constexpr int ATC_Q_ROWS = 256;     // Q stage holds up to two 128-row tiles (rows >= T are zero-filled by TMA)
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 
 // Persistent: each CTA (one per SM) walks over (batch, head) work items. Per head the producer stages Q (all
 // rows), K and V once (2-deep smem ring); the MMA thread issues S = Q_t K^T for both query tiles into the two TMEM
-// slots; softmax group g (4 warps, thread <-> query row) owns tile g: P = exp2(...) written in place as bf16,
-// then O = P V (A operand from TMEM), then the epilogue. The two groups, the MMA thread and the producer run
-// decoupled through mbarriers, so loads, tensor work and softmax of neighbouring tiles / heads overlap.
+// slots; softmax group g (8 warps: thread <-> query row, two warps per row splitting the key columns) owns tile g:
+// P = exp2(...) written in place as bf16 (each column half packs into the front of its own range), then
+// O = P V (A operand from TMEM), then the epilogue. The two groups, the MMA thread and the producer run decoupled
+// through mbarriers, so loads, tensor work and softmax of neighbouring tiles / heads overlap.
 __global__ void __launch_bounds__(ATC_THREADS, 1)
 attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                         bf16* __restrict__ out, float* __restrict__ lse, int num_heads_total, int T, int Nk, int H,
@@ -40,7 +46,8 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
     const uint32_t kv_bytes = (uint32_t)Nk * 128u;
     const uint32_t kv_stride = (kv_bytes + 1023u) & ~1023u;
     const uint32_t stage_bytes = ATC_Q_ROWS * 128 + 2 * kv_stride;
-    const uint32_t bar_base = smem_base + 2 * stage_bytes;
+    const uint32_t xchg_base = smem_base + 2 * stage_bytes;         // float [2 groups][2 halves][128]: max, then sum
+    const uint32_t bar_base = xchg_base + 2u * 2u * 2u * 128u * 4u;
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 16u + 8u * s; };
     auto s_ready = [&](int g) { return bar_base + 32u + 8u * g; };
@@ -48,10 +55,15 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
     auto o_ready = [&](int g) { return bar_base + 64u + 8u * g; };
     auto slot_free = [&](int g) { return bar_base + 80u + 8u * g; };
     const uint32_t tmem_slot = bar_base + 96u;
-    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+    uint8_t* gen = smem_raw - smem_u32(smem_raw);
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen + tmem_slot);
+    float* sMax = reinterpret_cast<float*>(gen + xchg_base);        // [g][half][128]
+    float* sSum = sMax + 2 * 2 * 128;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nt = (T + ATC_BM - 1) / ATC_BM;          // query tiles per head: 1 or 2
+    const int split = ((Nk / 2) + 15) & ~15;           // key columns [0, split) -> half 0, [split, Nk) -> half 1
+    auto packed_col = [&](int src_col) { return src_col < split ? (src_col >> 1) : split + ((src_col - split) >> 1); };
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmQ);
@@ -60,9 +72,9 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
             mbar_init(full_bar(i), 1);
             mbar_init(empty_bar(i), 1);
             mbar_init(s_ready(i), 1);
-            mbar_init(p_ready(i), 4);
+            mbar_init(p_ready(i), 8);
             mbar_init(o_ready(i), 1);
-            mbar_init(slot_free(i), 4);
+            mbar_init(slot_free(i), 8);
         }
         fence_barrier_init();
     }
@@ -119,7 +131,7 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
                     tc_fence_after();
                     // O = P V : A = P in TMEM (bf16 pairs: 8 columns per 16 keys), B = V [Nk keys x 64] MN-major
                     for (int k = 0; k < Nk / 16; ++k)
-                        umma_bf16_ts(tmem + g * 256 + ATC_O_COL, tmem + g * 256 + k * 8,
+                        umma_bf16_ts(tmem + g * 256 + ATC_O_COL, tmem + g * 256 + packed_col(16 * k),
                                      make_smem_desc_sw128(sV + k * 2048, 1024, 0), idesc_o, k > 0 ? 1u : 0u);
                     umma_commit(o_ready(g));
                 }
@@ -129,96 +141,91 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
         __syncwarp();
     } else {
         // ===================== softmax + epilogue groups =====================
-        const int g = (warp - 2) >> 2;
-        const int quarter = warp & 3;
+        const int sw = warp - 2;
+        const int g = sw >> 3;                  // query tile / TMEM slot
+        const int half = (sw >> 2) & 1;         // key-column half
+        const int quarter = warp & 3;           // TMEM lane quarter this warp may access
         if (g < nt) {
             const uint32_t tbase = tmem + g * 256 + ((uint32_t)(quarter * 32) << 16);
-            const int r_in_head = g * ATC_BM + quarter * 32 + lane;       // query index inside the head
+            const int r_in_tile = quarter * 32 + lane;
+            const int r_in_head = g * ATC_BM + r_in_tile;       // query index inside the head
+            const int c_begin = half == 0 ? 0 : split, c_end = half == 0 ? split : Nk;
+            float* myMax = sMax + (g * 2 + half) * 128, *otherMax = sMax + (g * 2 + (half ^ 1)) * 128;
+            float* mySum = sSum + (g * 2 + half) * 128, *otherSum = sSum + (g * 2 + (half ^ 1)) * 128;
             int it = 0;
             for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
                 const uint32_t hp = it & 1;
                 const int b = w / H, h = w % H;
                 mbar_wait(s_ready(g), hp);
                 tc_fence_after();
-                // pass 1: row max over the valid keys
+                // pass 1: max over this half's valid keys
                 float mx = -INFINITY;
-                int c = 0;
-                for (; c + 32 <= Nk; c += 32) {
-                    uint32_t r[32];
-                    tmem_ld_32x32(tbase + c, r);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        if (c + i < T) mx = fmaxf(mx, __uint_as_float(r[i]));
-                }
-                if (c < Nk) {
+                for (int c = c_begin; c < c_end; c += 16) {
                     uint32_t r[16];
                     tmem_ld_32x16(tbase + c, r);
                     tmem_ld_wait();
+                    if (c + 16 <= T) {
 #pragma unroll
-                    for (int i = 0; i < 16; ++i)
-                        if (c + i < T) mx = fmaxf(mx, __uint_as_float(r[i]));
+                        for (int i = 0; i < 16; ++i) mx = fmaxf(mx, __uint_as_float(r[i]));
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) if (c + i < T) mx = fmaxf(mx, __uint_as_float(r[i]));
+                    }
                 }
-                // pass 2: P = exp2((S - max) * scale*log2e) as bf16 pairs, written over S columns already consumed
+                myMax[r_in_tile] = mx;
+                named_bar_sync(1 + g, 256);
+                mx = fmaxf(mx, otherMax[r_in_tile]);
+                // pass 2: P = exp2((S - max) * scale*log2e) as bf16 pairs, packed into the front of this half's range
                 const float mneg = -mx * scale_log2;
                 float sum = 0.f;
-                auto do16 = [&](const uint32_t* r, int c0) {
+                for (int c = c_begin; c < c_end; c += 16) {
+                    uint32_t r[16];
+                    tmem_ld_32x16(tbase + c, r);
+                    tmem_ld_wait();
+                    float p[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) p[i] = fast_ex2(fmaf(__uint_as_float(r[i]), scale_log2, mneg));
+                    if (c + 16 > T) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) if (c + i >= T) p[i] = 0.f;
+                    }
                     uint32_t pk[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
-                        const float p0 = (c0 + 2 * i < T) ? fast_ex2(fmaf(__uint_as_float(r[2 * i]), scale_log2, mneg)) : 0.f;
-                        const float p1 = (c0 + 2 * i + 1 < T) ? fast_ex2(fmaf(__uint_as_float(r[2 * i + 1]), scale_log2, mneg)) : 0.f;
-                        pk[i] = pack_bf16(p0, p1);
-                        const float2 rr = unpack_bf16(pk[i]);     // sum what the PV product will actually see
-                        sum += rr.x + rr.y;
+                        pk[i] = pack_bf16(p[2 * i], p[2 * i + 1]);
+                        sum += p[2 * i] + p[2 * i + 1];
                     }
-                    tmem_st_32x8(tbase + (c0 >> 1), pk);
-                };
-                c = 0;
-                for (; c + 32 <= Nk; c += 32) {
-                    uint32_t r[32];
-                    tmem_ld_32x32(tbase + c, r);
-                    tmem_ld_wait();
-                    do16(r, c);
-                    do16(r + 16, c + 16);
+                    tmem_st_32x8(tbase + c_begin + ((c - c_begin) >> 1), pk);
                 }
-                if (c < Nk) {
-                    uint32_t r[16];
-                    tmem_ld_32x16(tbase + c, r);
-                    tmem_ld_wait();
-                    do16(r, c);
-                }
+                mySum[r_in_tile] = sum;
                 tmem_st_wait();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(p_ready(g));
+                named_bar_sync(1 + g, 256);           // both halves' partial sums are visible (and max slots reusable)
+                sum += otherSum[r_in_tile];
                 const float inv = 1.0f / sum;
                 const bool row_ok = r_in_head < T;
-                if (row_ok) lse[(long long)w * T + r_in_head] = mx * scale + logf(sum);
-                // epilogue: O / sum -> bf16 -> out[b, row, h, :]
+                if (row_ok && half == 0) lse[(long long)w * T + r_in_head] = mx * scale + logf(sum);
+                // epilogue: this half converts 32 of the 64 output columns: O / sum -> bf16 -> out[b, row, h, :]
                 mbar_wait(o_ready(g), hp);
                 tc_fence_after();
-                bf16* dst = out + (((long long)b * T + r_in_head) * H + h) * 64;
+                uint32_t r[32];
+                tmem_ld_32x32(tbase + ATC_O_COL + half * 32, r);
+                tmem_ld_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(slot_free(g));     // all TMEM reads of this warp for this tile are done
+                if (row_ok) {
+                    bf16* dst = out + (((long long)b * T + r_in_head) * H + h) * 64 + half * 32;
 #pragma unroll
-                for (int c2 = 0; c2 < 64; c2 += 32) {
-                    uint32_t r[32];
-                    tmem_ld_32x32(tbase + ATC_O_COL + c2, r);
-                    tmem_ld_wait();
-                    if (c2 == 32) {       // all TMEM reads of this tile are done: hand the slot back
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(slot_free(g));
-                    }
-                    if (row_ok) {
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            uint4 o;
-                            o.x = pack_bf16(__uint_as_float(r[8 * i]) * inv, __uint_as_float(r[8 * i + 1]) * inv);
-                            o.y = pack_bf16(__uint_as_float(r[8 * i + 2]) * inv, __uint_as_float(r[8 * i + 3]) * inv);
-                            o.z = pack_bf16(__uint_as_float(r[8 * i + 4]) * inv, __uint_as_float(r[8 * i + 5]) * inv);
-                            o.w = pack_bf16(__uint_as_float(r[8 * i + 6]) * inv, __uint_as_float(r[8 * i + 7]) * inv);
-                            reinterpret_cast<uint4*>(dst + c2)[i] = o;
-                        }
+                    for (int i = 0; i < 4; ++i) {
+                        uint4 o;
+                        o.x = pack_bf16(__uint_as_float(r[8 * i]) * inv, __uint_as_float(r[8 * i + 1]) * inv);
+                        o.y = pack_bf16(__uint_as_float(r[8 * i + 2]) * inv, __uint_as_float(r[8 * i + 3]) * inv);
+                        o.z = pack_bf16(__uint_as_float(r[8 * i + 4]) * inv, __uint_as_float(r[8 * i + 5]) * inv);
+                        o.w = pack_bf16(__uint_as_float(r[8 * i + 6]) * inv, __uint_as_float(r[8 * i + 7]) * inv);
+                        reinterpret_cast<uint4*>(dst)[i] = o;
                     }
                 }
             }
@@ -552,7 +559,7 @@ int attention_fwd_tc_launch(const bf16* qkv, bf16* out, float* lse, int batch, i
     rc = make_tmap_rows64(&tmKV, qkv, batch, tokens, 3 * heads, Nk);
     if (rc) return rc;
     const size_t kv_stride = ((size_t)Nk * 128 + 1023) & ~(size_t)1023;
-    const size_t smem = 1024 + 2 * (ATC_Q_ROWS * 128 + 2 * kv_stride) + 128;
+    const size_t smem = 1024 + 2 * (ATC_Q_ROWS * 128 + 2 * kv_stride) + 2 * 2 * 2 * 128 * 4 + 128;
     B200_CUDA(cudaFuncSetAttribute(attention_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int total = batch * heads;
     const int grid = total < sm_count() ? total : sm_count();
