@@ -40,11 +40,11 @@ const char* b200vit_last_error(void);
  * A, B: bf16 row-major with leading dimensions lda, ldb (elements, multiples of 8; 16-byte aligned bases).
  * epilogue:
  *   0 BF16       C bf16 = acc (+ bias[n] if bias != NULL)
- *   1 BIAS_GELU  C bf16 = a = acc + bias (skipped if C == NULL) ; C2 bf16 = dropout(gelu_erf(a))
- *                                                              (models/vit.py:119-122)
+ *   1 BIAS_GELU  a = acc + bias ; C2 bf16 = dropout(gelu_erf(a)) ; C bf16 = dropout_mask/(1-p) * gelu_erf'(a), the
+ *                operand the backward epilogue 3 multiplies by (skipped if C == NULL)    (models/vit.py:119-122)
  *   2 BIAS_RES   C f32 = dropout(acc + bias) + aux_f32[m,n]  (aux NULL -> no residual)
  *                                                              (models/vit.py:123-125 and the residual adds :167-168)
- *   3 DGELU      C bf16 = acc * dropout_mask * gelu_erf'(aux_bf16[m,n])   (backward of GELU + Dropout)
+ *   3 DGELU      C bf16 = acc * aux_bf16[m,n], aux = the C output of epilogue 1      (backward of GELU + Dropout)
  *   4 ACCUM      C f32 += acc, atomically; the only epilogue that allows split_k > 1 (weight gradients)
  *   5 F32        C f32 = acc (+ bias)
  *   6 PATCH      C f32[m + m/row_period + 1, n] = dropout(acc + bias[n] + aux_f32[(m % row_period) + 1, n]):

@@ -8,7 +8,7 @@ Data layout in HBM (R = B*T token rows, D = embedding dim, M = mlp size, H heads
   LayerNorm output ............. bf16 [R, D]  (A operand of the following GEMM, kept for its weight gradient)
   packed q/k/v ................. bf16 [R, 3D] = [B, T, 3, H, 64]; attention reads it in place
   attention output ............. bf16 [R, D]  (+ f32 log-sum-exp [B, H, T])
-  fc1 pre-activation a, h ...... bf16 [R, M] each (a only when a backward pass will follow)
+  fc1 mask*gelu'(pre-act), h ... bf16 [R, M] each (the derivative only when a backward pass will follow)
   weights ...................... f32 master nn.Parameters + bf16 shadows (refreshed by FusedAdam or on demand)
 """
 from __future__ import annotations
@@ -226,8 +226,7 @@ def _mlp_backward(g, saved, drop, ln_w, w1_16, w2_16, has_residual, want_bf16_ou
     dw2 = _zeros((d, m), x2d)
     K.gemm(K.OP_TN, K.EPI_ACCUM, d, m, r, g16, d, h, m, dw2, m, split_k=K.split_k_for(d, m, r, dev))
     da = _empty((r, m), torch.bfloat16, x2d)
-    K.gemm(K.OP_NN, K.EPI_DGELU, r, m, d, g16, d, w2_16, m, da, m, aux=a, ldaux=m, dropout_p=p, seed=key1[0],
-           offset=key1[1])
+    K.gemm(K.OP_NN, K.EPI_DGELU, r, m, d, g16, d, w2_16, m, da, m, aux=a, ldaux=m)   # a = mask * gelu'(pre-activation)
     db1 = _empty((m,), torch.float32, x2d)
     K.colsum_bf16(da, m, db1, r, m)
     dw1 = _zeros((m, d), x2d)

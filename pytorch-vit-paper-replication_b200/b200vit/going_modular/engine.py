@@ -2,10 +2,10 @@
 (reference: going_modular/going_modular/engine.py:9-79, 81-130, 132-211).
 
 What differs from the reference is only *how* the same numbers are produced:
-  * metrics are accumulated on the device and read back ONCE per epoch instead of two blocking `.item()`
-    calls per batch (reference engine.py:54, 74, 121, 125) -- the returned floats are the same means of
-    per-batch means;
-  * host->device copies of the batch are issued non-blocking (pinned loaders overlap with compute);
+  * each batch's loss / accuracy goes to pinned host memory with a non-blocking copy and the host waits ONCE per
+    epoch instead of two blocking `.item()` calls per batch (reference engine.py:54, 74, 121, 125) -- the returned
+    floats are the same means of per-batch means;
+  * the host->device copy of batch i+1 is issued on a side stream while batch i computes (pinned loaders overlap);
   * with `b200vit.optim.FusedAdam`, gradient clipping at global norm 1 (engine.py:63) is folded into the
     optimizer kernel; any other torch optimizer takes the reference's clip_grad_norm_ + step() path;
   * with `b200vit.nn.CrossEntropyLoss`, the accuracy count comes out of the loss kernel.
@@ -24,6 +24,78 @@ from ..optim import FusedAdam as _FusedAdam
 MAX_GRAD_NORM = 1.0  # Table 3 of the ViT paper; reference engine.py:63
 
 
+def _device_batches(dataloader, device):
+    """Yield (X, y) on `device`, with the host->device copy of the NEXT batch already in flight on a side stream
+    while the caller computes on the current one (the reference copies synchronously inside the loop,
+    engine.py:47). Batches that already live on the device pass through untouched."""
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        for X, y in dataloader:
+            yield X.to(dev), y.to(dev)
+        return
+    copy_stream = torch.cuda.Stream(device=dev)
+    compute = torch.cuda.current_stream(dev)
+
+    def stage(batch):
+        X, y = batch
+        if X.device == dev and y.device == dev:
+            return X, y, None
+        with torch.cuda.stream(copy_stream):
+            Xd, yd = X.to(dev, non_blocking=True), y.to(dev, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+        return Xd, yd, ev
+
+    it = iter(dataloader)
+    try:
+        nxt = stage(next(it))
+    except StopIteration:
+        return
+    while nxt is not None:
+        Xd, yd, ev = nxt
+        try:
+            nxt = stage(next(it))
+        except StopIteration:
+            nxt = None
+        if ev is not None:
+            compute.wait_event(ev)
+            Xd.record_stream(compute)
+            yd.record_stream(compute)
+        yield Xd, yd
+
+
+class _EpochMetrics:
+    """Per-batch (loss, accuracy) pairs. On CUDA every batch's pair is copied to pinned host memory right away
+    with a non-blocking D2H copy (8 bytes per step) and the host waits only once, at the end of the epoch -- the
+    reference blocks on two `.item()` calls per batch instead (engine.py:54, 74)."""
+
+    def __init__(self, n: int, device):
+        self.n = n
+        self.dev = torch.device(device)
+        self.i = 0
+        if self.dev.type == "cuda":
+            self.host = torch.zeros((max(n, 1), 2), dtype=torch.float32, pin_memory=True)
+        else:
+            self.host = torch.zeros((max(n, 1), 2), dtype=torch.float32)
+
+    def add(self, loss: torch.Tensor, acc: torch.Tensor) -> None:
+        pair = torch.stack((loss.detach().to(torch.float32).reshape(()), acc.reshape(())))
+        if self.i >= self.host.shape[0]:          # loader longer than its len(): grow
+            grown = torch.zeros((2 * self.host.shape[0], 2), dtype=torch.float32, pin_memory=self.host.is_pinned())
+            if self.dev.type == "cuda":
+                torch.cuda.current_stream(self.dev).synchronize()
+            grown[:self.i] = self.host[:self.i]
+            self.host = grown
+        self.host[self.i].copy_(pair, non_blocking=True)
+        self.i += 1
+
+    def means(self) -> Tuple[float, float]:
+        if self.dev.type == "cuda":
+            torch.cuda.current_stream(self.dev).synchronize()
+        tot = self.host[:self.i].double().sum(dim=0)
+        return float(tot[0]) / self.n, float(tot[1]) / self.n
+
+
 def _batch_correct(loss_fn, logits: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
     """Number of correct top-1 predictions as a device scalar (float)."""
     if isinstance(loss_fn, _FusedCE) and loss_fn.last_correct is not None:
@@ -39,17 +111,13 @@ def train_step(model: torch.nn.Module,
                device: torch.device) -> Tuple[float, float]:
     """One epoch of training; returns (mean batch loss, mean batch accuracy)."""
     model.train()
-    loss_sum = torch.zeros((), dtype=torch.float32, device=device)
-    acc_sum = torch.zeros((), dtype=torch.float32, device=device)
+    metrics = _EpochMetrics(len(dataloader), device)
     fused_opt = isinstance(optimizer, _FusedAdam)
 
-    for batch, (X, y) in enumerate(dataloader):
-        X, y = X.to(device, non_blocking=True), y.to(device, non_blocking=True)
-
+    for batch, (X, y) in enumerate(_device_batches(dataloader, device)):
         y_pred = model(X)
         loss = loss_fn(y_pred, y)
-        loss_sum += loss.detach()
-        acc_sum += _batch_correct(loss_fn, y_pred.detach(), y) / len(y_pred)
+        metrics.add(loss, _batch_correct(loss_fn, y_pred.detach(), y) / len(y_pred))
 
         optimizer.zero_grad()
         loss.backward()
@@ -61,8 +129,7 @@ def train_step(model: torch.nn.Module,
             optimizer.step()
         lr_scheduler.step()
 
-    n = len(dataloader)
-    return loss_sum.item() / n, acc_sum.item() / n
+    return metrics.means()
 
 
 def test_step(model: torch.nn.Module,
@@ -71,17 +138,13 @@ def test_step(model: torch.nn.Module,
               device: torch.device) -> Tuple[float, float]:
     """One evaluation pass; returns (mean batch loss, mean batch accuracy)."""
     model.eval()
-    loss_sum = torch.zeros((), dtype=torch.float32, device=device)
-    acc_sum = torch.zeros((), dtype=torch.float32, device=device)
+    metrics = _EpochMetrics(len(dataloader), device)
     with torch.inference_mode():
-        for batch, (X, y) in enumerate(dataloader):
-            X, y = X.to(device, non_blocking=True), y.to(device, non_blocking=True)
+        for batch, (X, y) in enumerate(_device_batches(dataloader, device)):
             logits = model(X)
             loss = loss_fn(logits, y)
-            loss_sum += loss
-            acc_sum += _batch_correct(loss_fn, logits, y) / len(logits)
-    n = len(dataloader)
-    return loss_sum.item() / n, acc_sum.item() / n
+            metrics.add(loss, _batch_correct(loss_fn, logits, y) / len(logits))
+    return metrics.means()
 
 
 test_step.__test__ = False  # the name comes from the reference API; it is not a pytest test

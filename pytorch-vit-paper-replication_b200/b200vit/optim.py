@@ -46,6 +46,8 @@ class FusedAdam(torch.optim.Optimizer):
                     g["decoupled_weight_decay"] != g0["decoupled_weight_decay"]:
                 raise ValueError("FusedAdam: betas / eps / decoupled_weight_decay must be the same in every group")
         self._table_key = None
+        self._upload_ring = None
+        self._upload_idx = 0
         self._table_dev = None
         self._ptrs_dev = None
         self._sizes_dev = None
@@ -102,13 +104,32 @@ class FusedAdam(torch.optim.Optimizer):
             if not p.is_contiguous() or not p.grad.is_contiguous():
                 raise RuntimeError("FusedAdam expects contiguous parameters and gradients")
 
-        def upload(cbuf):
-            host = torch.frombuffer(bytearray(bytes(cbuf)), dtype=torch.uint8)
-            return host.to(dev)
-
-        self._table_dev = upload(arr)
-        self._ptrs_dev = upload(ptrs)
-        self._sizes_dev = upload(sizes)
+        # Gradients are fresh tensors every step, so the table usually changes every step. The upload must not
+        # synchronise the device (a blocking copy from pageable memory would drain the whole launch queue once per
+        # step): stage through a small ring of pinned host buffers and copy asynchronously on the current stream.
+        blob = bytes(arr) + bytes(ptrs) + bytes(sizes)
+        nbytes = len(blob)
+        ring = self._upload_ring
+        if ring is None or ring[0][0].numel() < nbytes or ring[0][1].device != dev:
+            cap = max(nbytes, 1 << 16)
+            pin = dev.type == "cuda"
+            ring = self._upload_ring = [
+                (torch.empty(cap, dtype=torch.uint8, pin_memory=pin), torch.empty(cap, dtype=torch.uint8, device=dev),
+                 [None]) for _ in range(4)]
+            self._upload_idx = 0
+        host, devbuf, ev = ring[self._upload_idx]
+        self._upload_idx = (self._upload_idx + 1) % len(ring)
+        if ev[0] is not None:
+            ev[0].synchronize()        # four optimizer steps old: never blocks in practice
+        ctypes.memmove(host.data_ptr(), blob, nbytes)
+        devbuf[:nbytes].copy_(host[:nbytes], non_blocking=True)
+        if dev.type == "cuda":
+            ev[0] = torch.cuda.Event()
+            ev[0].record()
+        o1, o2 = ctypes.sizeof(arr), ctypes.sizeof(arr) + ctypes.sizeof(ptrs)
+        self._table_dev = devbuf[:o1]
+        self._ptrs_dev = devbuf[o1:o2]
+        self._sizes_dev = devbuf[o2:nbytes]
         self._max_size = max(k[-1] for k in key)
         self._num = n
         chunks = (self._max_size + _CHUNK - 1) // _CHUNK

@@ -87,6 +87,14 @@ __device__ __forceinline__ void gelu_terms(float x, float& one_minus_pe, float& 
     e = fast_ex2(u * u * -1.4426950408889634f);
     one_minus_pe = fmaf(-poly, e, 1.0f);          // erf(|x|/sqrt2)
 }
+// h = s * gelu(x), g = s * gelu'(x) from one set of shared terms (s = dropout scale 1/(1-p), folded into constants).
+__device__ __forceinline__ void gelu_value_and_grad(float x, float s, float& h, float& g) {
+    float erf_abs, e;
+    gelu_terms(x, erf_abs, e);
+    const float hs = 0.5f * s;
+    h = hs * fmaf(fabsf(x), erf_abs, x);
+    g = fmaf(x * (0.3989422804014327f * s), e, fmaf(copysignf(hs, x), erf_abs, hs));
+}
 __device__ __forceinline__ float gelu_exact(float x) {
     float erf_abs, e;
     gelu_terms(x, erf_abs, e);
@@ -103,14 +111,16 @@ __device__ __forceinline__ float gelu_exact_grad(float x) {
 // Counter-based dropout mask. Element e of a tensor belongs to block e/8, lane e%8; a block draws 4x32 random
 // bits = eight 16-bit lanes from a 32-bit avalanche hash of (counter ^ key), where key is derived on the host
 // from (seed, offset). Any kernel (forward epilogue, backward epilogue, standalone) regenerates the same mask
-// from (seed, offset) alone, so no mask tensor is ever stored. keep <=> lane16 >= thr16, thr16 = round(p*65536).
+// from (seed, offset) alone, so no mask tensor is ever stored. keep <=> (lane16 & 0x7fff) >= thr15,
+// thr15 = round(p*32768): 15-bit lanes leave a guard bit per half-word, so a keep-mask for a packed bf16 pair
+// can be produced with five integer instructions (dropout_mask2) instead of per-element compare/select/multiply.
 // Semantics mirror nn.Dropout (models/vit.py:43,122,125): kept values are scaled by 1/(1-p).
 // (A 10-round Philox here cost more instructions than the GELU it sits next to in the fc1 epilogue.)
 // ---------------------------------------------------------------------------------------------
 struct DropoutParams {
     float p;            // drop probability; 0 disables
     float scale;        // 1/(1-p)
-    uint32_t thr16;     // drop if lane16 < thr16
+    uint32_t thr15;     // drop if (lane16 & 0x7fff) < thr15
     uint32_t key_lo;    // hash key derived from (seed, offset)
     uint32_t key_hi;
 };
@@ -132,24 +142,30 @@ __device__ __forceinline__ void dropout_mult8(const DropoutParams& d, uint64_t b
 #pragma unroll
     for (uint32_t i = 0; i < 4; ++i) {
         const uint32_t w = dropout_word(d, blk, i);
-        m[2 * i]     = ((w & 0xFFFFu) >= d.thr16) ? d.scale : 0.0f;
-        m[2 * i + 1] = ((w >> 16)     >= d.thr16) ? d.scale : 0.0f;
+        m[2 * i]     = ((w & 0x7FFFu) >= d.thr15) ? d.scale : 0.0f;
+        m[2 * i + 1] = (((w >> 16) & 0x7FFFu) >= d.thr15) ? d.scale : 0.0f;
     }
 }
 // Multiplier for a single element (used by small kernels).
 __device__ __forceinline__ float dropout_mult1(const DropoutParams& d, uint64_t elem) {
     const uint32_t lane = (uint32_t)(elem & 7);
     const uint32_t w = dropout_word(d, elem >> 3, lane >> 1);
-    const uint32_t v = (lane & 1) ? (w >> 16) : (w & 0xFFFFu);
-    return (v >= d.thr16) ? d.scale : 0.0f;
+    const uint32_t v = ((lane & 1) ? (w >> 16) : w) & 0x7FFFu;
+    return (v >= d.thr15) ? d.scale : 0.0f;
+}
+// 0xFFFF / 0x0000 half-word masks for the element pair (2i, 2i+1) drawn from random word w: AND them onto a packed
+// bf16 pair. Same keep decision as dropout_mult8 / dropout_mult1 (the scale must be applied separately).
+__device__ __forceinline__ uint32_t dropout_mask2(const DropoutParams& d, uint32_t w) {
+    const uint32_t t = ((w & 0x7FFF7FFFu) | 0x80008000u) - (d.thr15 * 0x00010001u);
+    return ((t >> 15) & 0x00010001u) * 0xFFFFu;
 }
 
 inline DropoutParams make_dropout(float p, uint64_t seed, uint64_t offset) {
     DropoutParams d;
     d.p = p;
     d.scale = (p > 0.f && p < 1.f) ? 1.0f / (1.0f - p) : (p >= 1.f ? 0.f : 1.0f);
-    double t = (double)p * 65536.0 + 0.5;
-    d.thr16 = p <= 0.f ? 0u : (t >= 65536.0 ? 65536u : (uint32_t)t);
+    double t = (double)p * 32768.0 + 0.5;
+    d.thr15 = p <= 0.f ? 0u : (t >= 32768.0 ? 32768u : (uint32_t)t);
     // splitmix64 of (seed, offset) -> 64-bit key
     uint64_t z = seed * 0x9E3779B97F4A7C15ull + offset * 0xD1B54A32D192ED03ull + 0x2545F4914F6CDD1Dull;
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;

@@ -50,9 +50,9 @@ constexpr int STAGE2_BYTES = A_STAGE_BYTES + B2_STAGE_BYTES;
 enum GemmOp { OP_NT = 0, OP_NN = 1, OP_TN = 2 };
 enum GemmEpi {
     EPI_BF16 = 0,       // C bf16 = acc (+ bias[n])
-    EPI_BIAS_GELU = 1,  // C bf16 = a = acc + bias ; C2 bf16 = dropout(gelu(a))       (fc1, vit.py:119-122)
+    EPI_BIAS_GELU = 1,  // a = acc + bias ; C2 bf16 = mask*gelu(a) ; C bf16 = mask*gelu'(a) (for backward; optional)  (fc1, vit.py:119-122)
     EPI_BIAS_RES = 2,   // C f32 = dropout(acc + bias) + aux_f32[m,n]                  (out-proj / fc2 + residual, vit.py:167-168)
-    EPI_DGELU = 3,      // C bf16 = acc * dropmask * gelu'(aux_bf16[m,n])              (backward of GELU+Dropout)
+    EPI_DGELU = 3,      // C bf16 = acc * aux_bf16[m,n], aux = mask*gelu'(a) saved by EPI_BIAS_GELU   (backward of GELU+Dropout)
     EPI_ACCUM = 4,      // C f32 += acc  (atomic; split-K weight gradients)
     EPI_F32 = 5,        // C f32 = acc (+ bias[n])
     EPI_PATCH = 6,      // C f32[m + m/P + 1, n] = dropout(acc + bias[n] + pos[m%P + 1, n])  (vit.py:53-66)
@@ -70,10 +70,10 @@ struct GemmParams {
     int row_period;
     int vec_ok;   // leading dimensions / N allow 16-byte vector access
 };
-// The ALU-heavy epilogues (GELU / dGELU, with dropout) run 16 epilogue warps (4 per scheduler, 64 columns each)
+// The ALU-heavy epilogue (GELU value + derivative, with dropout) runs 16 epilogue warps (4 per scheduler, 64 columns each)
 // and give up one pipeline stage for the extra staging tiles; the others run 8 warps and a 6-deep ring.
 template <int EPI> struct Cfg2 {
-    static constexpr int EW = (EPI == EPI_BIAS_GELU || EPI == EPI_DGELU) ? 16 : 8;
+    static constexpr int EW = (EPI == EPI_BIAS_GELU) ? 16 : 8;
     static constexpr int STAGES = EW == 16 ? 5 : 6;
     static constexpr int THREADS = 128 + EW * 32;
     static constexpr int SMEM = STAGES * STAGE2_BYTES + EW * EPI_STAGE_BYTES + 1024 + 256;
@@ -251,19 +251,19 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
             }
         }
     };
-    auto store_b16_tile = [&](bf16* base, long long ld) {
+    auto store_b16_tile = [&](bf16* base, long long ld, uint32_t soff = 0) {
         if (interior) {
             bf16* ptr = base + (long long)(row_base + (lane >> 2)) * ld + col0 + (lane & 3) * 8;
 #pragma unroll
             for (int it = 0; it < 4; ++it)
-                *reinterpret_cast<uint4*>(ptr + (long long)(it * 8) * ld) = lds128(stg + stg_off_b16(it * 8 + (lane >> 2), lane & 3));
+                *reinterpret_cast<uint4*>(ptr + (long long)(it * 8) * ld) = lds128(stg + soff + stg_off_b16(it * 8 + (lane >> 2), lane & 3));
             return;
         }
 #pragma unroll
         for (int it = 0; it < 4; ++it) {
             const int r = it * 8 + (lane >> 2), ch = lane & 3;
             const int gr = row_base + r, col = col0 + ch * 8;
-            const uint4 q = lds128(stg + stg_off_b16(r, ch));
+            const uint4 q = lds128(stg + soff + stg_off_b16(r, ch));
             if (gr < p.M && col < p.N) {
                 bf16* dst = base + epi_out_row<EPI>(p, gr) * ld + col;
                 if (fullw || (p.vec_ok && col + 8 <= p.N)) {
@@ -350,18 +350,38 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
         store_f32_tile(reinterpret_cast<float*>(p.C), p.ldc);
         __syncwarp();
     } else if (EPI == EPI_BIAS_GELU) {
-        if (p.C != nullptr) {
-            put_row_b16(v);
-            __syncwarp();
-            store_b16_tile(reinterpret_cast<bf16*>(p.C), p.ldc);
-            __syncwarp();
-        }
+        // Per group of 8 columns: h = scale*gelu(a) (the hidden activation) and gd = scale*gelu'(a) (saved for the
+        // backward epilogue), dropout keep-mask ANDed onto the packed bf16 pairs of both. A bf16 tile needs only
+        // 2 KB, so both outputs are staged side by side in the warp's 4 KB tile and stored after one warp sync.
+        const bool want_gd = p.C != nullptr;
+        const unsigned long long e0 = (unsigned long long)epi_out_row<EPI>(p, row) * (unsigned long long)p.N + (unsigned long long)col0;
+        const bool blk8 = (p.N & 7) == 0;
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = gelu_exact(v[i]);
-        apply_dropout(v);
-        put_row_b16(v);
+        for (int c = 0; c < 4; ++c) {
+            float hv[8], gv[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) gelu_value_and_grad(v[8 * c + i], p.drop.scale, hv[i], gv[i]);
+            uint32_t mk[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};
+            if (p.drop.p > 0.f) {
+                if (blk8) {
+#pragma unroll
+                    for (uint32_t j = 0; j < 4; ++j) mk[j] = dropout_mask2(p.drop, dropout_word(p.drop, (e0 >> 3) + c, j));
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        mk[j] = (dropout_mult1(p.drop, e0 + 8 * c + 2 * j) != 0.f ? 0x0000FFFFu : 0u) |
+                                (dropout_mult1(p.drop, e0 + 8 * c + 2 * j + 1) != 0.f ? 0xFFFF0000u : 0u);
+                }
+            }
+            if (want_gd)
+                sts128(stg + stg_off_b16(lane, c), pack_bf16(gv[0], gv[1]) & mk[0], pack_bf16(gv[2], gv[3]) & mk[1],
+                       pack_bf16(gv[4], gv[5]) & mk[2], pack_bf16(gv[6], gv[7]) & mk[3]);
+            sts128(stg + 2048 + stg_off_b16(lane, c), pack_bf16(hv[0], hv[1]) & mk[0], pack_bf16(hv[2], hv[3]) & mk[1],
+                   pack_bf16(hv[4], hv[5]) & mk[2], pack_bf16(hv[6], hv[7]) & mk[3]);
+        }
         __syncwarp();
-        store_b16_tile(reinterpret_cast<bf16*>(p.C2), p.ldc2);
+        if (want_gd) store_b16_tile(reinterpret_cast<bf16*>(p.C), p.ldc);
+        store_b16_tile(reinterpret_cast<bf16*>(p.C2), p.ldc2, 2048);
         __syncwarp();
     } else if (EPI == EPI_BIAS_RES || EPI == EPI_PATCH) {
         if (EPI == EPI_BIAS_RES) apply_dropout(v);
@@ -381,7 +401,6 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
         store_f32_tile(reinterpret_cast<float*>(p.C), p.ldc);
         __syncwarp();
     } else if (EPI == EPI_DGELU) {
-        apply_dropout(v);
         aux_to_stage();
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
@@ -390,8 +409,8 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const float2 f = unpack_bf16(w[j]);
-                v[8 * c + 2 * j] *= gelu_exact_grad(f.x);
-                v[8 * c + 2 * j + 1] *= gelu_exact_grad(f.y);
+                v[8 * c + 2 * j] *= f.x;
+                v[8 * c + 2 * j + 1] *= f.y;
             }
         }
         __syncwarp();
@@ -842,7 +861,7 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
     B200_CHECK_ARG((lda % 8) == 0 && (ldb % 8) == 0, "gemm: lda/ldb must be multiples of 8 elements (TMA 16B stride), got %lld %lld", lda, ldb);
     B200_CHECK_ARG(((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0, "gemm: A/B must be 16-byte aligned");
     B200_CHECK_ARG(epi != EPI_BIAS_GELU || C2 != nullptr, "gemm: GELU epilogue needs the second output");
-    B200_CHECK_ARG(epi != EPI_DGELU || aux != nullptr, "gemm: dGELU epilogue needs the pre-activation");
+    B200_CHECK_ARG(epi != EPI_DGELU || aux != nullptr, "gemm: dGELU epilogue needs the saved mask*gelu' operand");
     B200_CHECK_ARG(epi != EPI_PATCH || (aux != nullptr && row_period > 0), "gemm: patch epilogue needs pos embedding and period");
     B200_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "gemm: dropout p must be in [0,1)");
 
@@ -905,7 +924,7 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
     B200_CHECK_ARG(kern != nullptr, "gemm: no kernel for op %d epi %d", op, epi);
 
     if (two_cta) {
-        const bool heavy = (epi == EPI_BIAS_GELU || epi == EPI_DGELU);
+        const bool heavy = (epi == EPI_BIAS_GELU);
         const int smem2 = heavy ? Cfg2<EPI_BIAS_GELU>::SMEM : Cfg2<EPI_BF16>::SMEM;
         const int threads2 = heavy ? Cfg2<EPI_BIAS_GELU>::THREADS : Cfg2<EPI_BF16>::THREADS;
         B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));

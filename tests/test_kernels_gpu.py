@@ -66,21 +66,32 @@ def test_gemm_gelu_and_dgelu():
     A = _rand_bf16((M, Kd), g)
     B = _rand_bf16((N, Kd), g, 0.08)
     bias = torch.randn(N, generator=g).to(dev()) * 0.1
-    a = torch.empty((M, N), dtype=torch.bfloat16, device=dev())
+    gd = torch.empty((M, N), dtype=torch.bfloat16, device=dev())    # gelu'(a): what the backward epilogue multiplies by
     h = torch.empty((M, N), dtype=torch.bfloat16, device=dev())
-    K.gemm(K.OP_NT, K.EPI_BIAS_GELU, M, N, Kd, A, Kd, B, Kd, a, N, C2=h, ldc2=N, bias=bias)
-    a_ref = A.float() @ B.float().t() + bias
+    K.gemm(K.OP_NT, K.EPI_BIAS_GELU, M, N, Kd, A, Kd, B, Kd, gd, N, C2=h, ldc2=N, bias=bias)
+    a_ref = (A.float() @ B.float().t() + bias).requires_grad_(True)
     h_ref = torch.nn.functional.gelu(a_ref)
-    assert rel_err(a, a_ref) < 4e-3
-    assert rel_err(h, h_ref) < 5e-3
+    h_ref.sum().backward()
+    assert rel_err(h, h_ref) < 5e-3            # erf via A&S 7.1.26 (1.5e-7) + bf16 output rounding
+    assert rel_err(gd, a_ref.grad) < 5e-3
     # backward epilogue: out = (G @ W) * gelu'(a)
     G = _rand_bf16((M, Kd), g)
     W = _rand_bf16((Kd, N), g, 0.08)
     out = torch.empty((M, N), dtype=torch.bfloat16, device=dev())
-    K.gemm(K.OP_NN, K.EPI_DGELU, M, N, Kd, G, Kd, W, N, out, N, aux=a, ldaux=N)
-    x = a.float().requires_grad_(True)
-    torch.nn.functional.gelu(x).backward(G.float() @ W.float())
-    assert rel_err(out, x.grad) < 5e-3
+    K.gemm(K.OP_NN, K.EPI_DGELU, M, N, Kd, G, Kd, W, N, out, N, aux=gd, ldaux=N)
+    assert rel_err(out, (G.float() @ W.float()) * a_ref.grad) < 8e-3
+    # with dropout: hidden and saved derivative carry the SAME mask, scaled by 1/(1-p); mask == dropout_cast's
+    p = 0.25
+    gd2, h2 = torch.empty_like(gd), torch.empty_like(h)
+    K.gemm(K.OP_NT, K.EPI_BIAS_GELU, M, N, Kd, A, Kd, B, Kd, gd2, N, C2=h2, ldc2=N, bias=bias, dropout_p=p, seed=9, offset=3)
+    ones = torch.ones((M, N), dtype=torch.float32, device=dev())
+    mask = torch.empty((M, N), dtype=torch.bfloat16, device=dev())
+    K.dropout_cast(ones, mask, None, M, N, p, 9, 3)
+    keep = mask != 0
+    assert abs(keep.float().mean().item() - (1 - p)) < 0.01
+    assert torch.all(h2[~keep] == 0) and torch.all(gd2[~keep] == 0)
+    assert rel_err(h2[keep], (h_ref.detach() / (1 - p))[keep]) < 5e-3
+    assert rel_err(gd2[keep], (a_ref.grad / (1 - p))[keep]) < 5e-3
 
 
 def test_gemm_bias_res_and_dropout_consistency():
