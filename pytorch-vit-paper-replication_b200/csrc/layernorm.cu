@@ -86,7 +86,7 @@ int layernorm_fwd_launch(const float* x, long long row_stride, const float* gamm
 // NV = float4 chunks per lane (ceil(D / 128)).
 // ---------------------------------------------------------------------------------------------
 template <int NV, bool HAS_NEXT>
-__global__ void __launch_bounds__(LN_WARPS * 32, 2)
+__global__ void __launch_bounds__(LN_WARPS * 32, (NV <= 6) ? 3 : 2)
 layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__ dy_f32, const float* __restrict__ x,
                      long long row_stride, const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
                      const float* __restrict__ gamma, const float* __restrict__ gin, float* __restrict__ gout,
@@ -112,8 +112,9 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
     for (long long row = (long long)blockIdx.x * LN_WARPS + warp; row < rows; row += (long long)gridDim.x * LN_WARPS) {
         const float mean = mean_in[row], rstd = rstd_in[row];
         const float4* xr = reinterpret_cast<const float4*>(x + row * row_stride);
-        float4 xh[NV], dy[NV], res[NV];
-        // issue every global load of the row up front
+        float4 xh[NV], dy[NV];
+        // issue the x / dy loads of the row up front (the residual gradient is fetched after the row reductions:
+        // keeping it in registers too would cost the third resident block per SM)
 #pragma unroll
         for (int k = 0; k < NV; ++k) {
             const int i = lane + 32 * k;
@@ -126,7 +127,6 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
                 } else {
                     dy[k] = reinterpret_cast<const float4*>(dy_f32 + row * (long long)D)[i];
                 }
-                res[k] = gin ? reinterpret_cast<const float4*>(gin + row * gout_stride)[i] : make_float4(0, 0, 0, 0);
             }
         }
         float s1 = 0.f, s2 = 0.f;
@@ -154,11 +154,12 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
             const int i = lane + 32 * k;
             if (i < nv) {
                 const float4 g = __ldg(gamma4 + i);
+                const float4 rs = gin ? reinterpret_cast<const float4*>(gin + row * gout_stride)[i] : make_float4(0, 0, 0, 0);
                 float4 o;
-                o.x = rstd * (dy[k].x * g.x - c1 - xh[k].x * c2) + res[k].x;
-                o.y = rstd * (dy[k].y * g.y - c1 - xh[k].y * c2) + res[k].y;
-                o.z = rstd * (dy[k].z * g.z - c1 - xh[k].z * c2) + res[k].z;
-                o.w = rstd * (dy[k].w * g.w - c1 - xh[k].w * c2) + res[k].w;
+                o.x = rstd * (dy[k].x * g.x - c1 - xh[k].x * c2) + rs.x;
+                o.y = rstd * (dy[k].y * g.y - c1 - xh[k].y * c2) + rs.y;
+                o.z = rstd * (dy[k].z * g.z - c1 - xh[k].z * c2) + rs.z;
+                o.w = rstd * (dy[k].w * g.w - c1 - xh[k].w * c2) + rs.w;
                 reinterpret_cast<float4*>(gout + row * gout_stride)[i] = o;
                 if (HAS_NEXT) {
                     float v[4] = {o.x, o.y, o.z, o.w};
@@ -210,7 +211,7 @@ int layernorm_bwd_launch(const bf16* dy_bf16, const float* dy_f32, const float* 
     if (dbeta) B200_CUDA(cudaMemsetAsync(dbeta, 0, sizeof(float) * dim, stream));
     if (dbias_next) B200_CUDA(cudaMemsetAsync(dbias_next, 0, sizeof(float) * dim, stream));
     long long blocks = (rows + LN_WARPS - 1) / LN_WARPS;
-    const long long cap = (long long)sm_count() * 2;   // persistent: 2 resident blocks per SM, rows strided
+    const long long cap = (long long)sm_count() * 3;   // persistent: up to 3 resident blocks per SM, rows strided
     if (blocks > cap) blocks = cap;
     const DropoutParams drop = make_dropout(drop_p, seed, offset);
     const size_t smem = sizeof(float) * (gout_bf16 ? 3 : 2) * LN_WARPS * dim;
