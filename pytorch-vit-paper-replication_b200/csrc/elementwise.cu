@@ -171,7 +171,8 @@ int patch_grad_rows_launch(const float* gx, bf16* gy, int batch, int tokens, int
 // Column sums of a bf16 matrix (bias gradients: db[n] = sum_m dY[m, n]).
 // Block = 32 x 8 threads; thread (x, y) owns 8 consecutive columns and rows y, y+8, ... of its row slab.
 // ---------------------------------------------------------------------------------------------
-constexpr int CS_ROWS_PER_BLOCK = 512;
+constexpr int CS_ROWS_PER_BLOCK = 512;   // colsum: 64 rows per thread, loads of 4 rows issued together
+constexpr int DC_ROWS_PER_BLOCK = 128;   // dropout_cast: 16 rows per thread
 
 __global__ void colsum_bf16_kernel(const bf16* __restrict__ x, long long ld, float* __restrict__ out, long long rows,
                                    int cols) {
@@ -182,17 +183,25 @@ __global__ void colsum_bf16_kernel(const bf16* __restrict__ x, long long ld, flo
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (c0 < cols) {
         const bool vec = (c0 + 8 <= cols) && ((ld & 7) == 0) && ((((uintptr_t)x) & 15) == 0);
-        for (long long r = r0 + threadIdx.y; r < r1; r += 8) {
-            const bf16* p = x + r * ld + c0;
-            if (vec) {
-                const uint4 q = *reinterpret_cast<const uint4*>(p);
-                const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+        if (vec) {
+            for (long long r = r0 + threadIdx.y; r < r1; r += 32) {
+                uint4 q[4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const float2 f = unpack_bf16(w[j]);
-                    acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
+                for (int u = 0; u < 4; ++u)
+                    q[u] = (r + 8 * u < r1) ? *reinterpret_cast<const uint4*>(x + (r + 8 * u) * ld + c0) : make_uint4(0, 0, 0, 0);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const uint32_t w[4] = {q[u].x, q[u].y, q[u].z, q[u].w};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float2 f = unpack_bf16(w[j]);
+                        acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
+                    }
                 }
-            } else {
+            }
+        } else {
+            for (long long r = r0 + threadIdx.y; r < r1; r += 8) {
+                const bf16* p = x + r * ld + c0;
                 for (int j = 0; j < 8 && c0 + j < cols; ++j) acc[j] += __bfloat162float(p[j]);
             }
         }
@@ -230,18 +239,33 @@ __global__ void dropout_cast_kernel(const float* __restrict__ g, bf16* __restric
                                     long long rows, int cols, DropoutParams drop) {
     __shared__ float red[8][32][8 + 1];
     const int c0 = (blockIdx.x * 32 + threadIdx.x) * 8;
-    const long long r0 = (long long)blockIdx.y * CS_ROWS_PER_BLOCK;
-    const long long r1 = min(rows, r0 + CS_ROWS_PER_BLOCK);
+    const long long r0 = (long long)blockIdx.y * DC_ROWS_PER_BLOCK;
+    const long long r1 = min(rows, r0 + DC_ROWS_PER_BLOCK);
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (c0 < cols) {
         const bool vec = (c0 + 8 <= cols) && ((cols & 7) == 0) && ((((uintptr_t)g) & 15) == 0) &&
                          ((((uintptr_t)out) & 15) == 0);
-        for (long long r = r0 + threadIdx.y; r < r1; r += 8) {
+        for (long long rr = r0 + threadIdx.y; rr < r1; rr += 16) {
+          float4 la[2], lb[2];
+          if (vec) {
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const long long r = rr + 8 * u;
+                if (r < r1) {
+                    la[u] = *reinterpret_cast<const float4*>(g + (unsigned long long)r * cols + c0);
+                    lb[u] = *reinterpret_cast<const float4*>(g + (unsigned long long)r * cols + c0 + 4);
+                }
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            const long long r = rr + 8 * u;
+            if (r >= r1) continue;
             const unsigned long long e0 = (unsigned long long)r * cols + c0;
             float v[8];
             if (vec) {
-                const float4 a = *reinterpret_cast<const float4*>(g + e0);
-                const float4 b = *reinterpret_cast<const float4*>(g + e0 + 4);
+                const float4 a = la[u];
+                const float4 b = lb[u];
                 v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
                 if (drop.p > 0.f) {
                     float m[8];
@@ -267,6 +291,7 @@ __global__ void dropout_cast_kernel(const float* __restrict__ g, bf16* __restric
                     acc[j] += __bfloat162float(h);
                 }
             }
+          }
         }
     }
     if (colsum == nullptr) return;
@@ -289,7 +314,7 @@ int dropout_cast_launch(const float* g, bf16* out, float* colsum, long long rows
     B200_CHECK_ARG(g && out, "dropout_cast: null pointer");
     B200_CHECK_ARG(rows > 0 && cols > 0, "dropout_cast: bad sizes");
     if (colsum) B200_CUDA(cudaMemsetAsync(colsum, 0, sizeof(float) * cols, stream));
-    dim3 grid((cols + 255) / 256, (unsigned)((rows + CS_ROWS_PER_BLOCK - 1) / CS_ROWS_PER_BLOCK));
+    dim3 grid((cols + 255) / 256, (unsigned)((rows + DC_ROWS_PER_BLOCK - 1) / DC_ROWS_PER_BLOCK));
     dropout_cast_kernel<<<grid, dim3(32, 8), 0, stream>>>(g, out, colsum, rows, cols,
                                                          make_dropout(drop_p, seed, offset));
     B200_LAUNCH_CHECK();

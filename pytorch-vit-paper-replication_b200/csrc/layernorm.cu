@@ -12,6 +12,7 @@ constexpr int LN_WARPS = 8;
 // ---------------------------------------------------------------------------------------------
 // forward: y = (x - mean) * rstd * gamma + beta ; writes bf16 (GEMM operand) and/or fp32, plus row stats
 // ---------------------------------------------------------------------------------------------
+template <int NV>
 __global__ void __launch_bounds__(LN_WARPS * 32)
 layernorm_fwd_kernel(const float* __restrict__ x, long long row_stride, const float* __restrict__ gamma,
                      const float* __restrict__ beta, bf16* __restrict__ y_bf16, float* __restrict__ y_f32,
@@ -20,17 +21,23 @@ layernorm_fwd_kernel(const float* __restrict__ x, long long row_stride, const fl
     const int nv = D >> 2;
     for (long long row = (long long)blockIdx.x * LN_WARPS + warp; row < rows; row += (long long)gridDim.x * LN_WARPS) {
         const float4* xr = reinterpret_cast<const float4*>(x + row * row_stride);
+        float4 v[NV];                       // the whole row lives in registers: one global read
         float s = 0.f;
-        for (int i = lane; i < nv; i += 32) {
-            const float4 v = xr[i];
-            s += (v.x + v.y) + (v.z + v.w);
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            const int i = lane + 32 * k;
+            v[k] = i < nv ? xr[i] : make_float4(0, 0, 0, 0);
+            s += (v[k].x + v[k].y) + (v[k].z + v[k].w);
         }
         const float mean = warp_sum(s) / (float)D;
         float q = 0.f;
-        for (int i = lane; i < nv; i += 32) {
-            const float4 v = xr[i];
-            const float a = v.x - mean, b = v.y - mean, c = v.z - mean, d = v.w - mean;
-            q += (a * a + b * b) + (c * c + d * d);
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            const int i = lane + 32 * k;
+            if (i < nv) {
+                const float a = v[k].x - mean, b = v[k].y - mean, c = v[k].z - mean, d = v[k].w - mean;
+                q += (a * a + b * b) + (c * c + d * d);
+            }
         }
         const float var = warp_sum(q) / (float)D;
         const float rstd = rsqrtf(var + eps);
@@ -38,21 +45,24 @@ layernorm_fwd_kernel(const float* __restrict__ x, long long row_stride, const fl
             if (mean_out) mean_out[row] = mean;
             if (rstd_out) rstd_out[row] = rstd;
         }
-        for (int i = lane; i < nv; i += 32) {
-            const float4 v = xr[i];
-            const float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + i);
-            const float4 b = __ldg(reinterpret_cast<const float4*>(beta) + i);
-            float4 o;
-            o.x = (v.x - mean) * rstd * g.x + b.x;
-            o.y = (v.y - mean) * rstd * g.y + b.y;
-            o.z = (v.z - mean) * rstd * g.z + b.z;
-            o.w = (v.w - mean) * rstd * g.w + b.w;
-            if (y_f32) reinterpret_cast<float4*>(y_f32 + row * (long long)D)[i] = o;
-            if (y_bf16) {
-                uint2 p;
-                p.x = pack_bf16(o.x, o.y);
-                p.y = pack_bf16(o.z, o.w);
-                reinterpret_cast<uint2*>(y_bf16 + row * (long long)D)[i] = p;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            const int i = lane + 32 * k;
+            if (i < nv) {
+                const float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + i);
+                const float4 b = __ldg(reinterpret_cast<const float4*>(beta) + i);
+                float4 o;
+                o.x = (v[k].x - mean) * rstd * g.x + b.x;
+                o.y = (v[k].y - mean) * rstd * g.y + b.y;
+                o.z = (v[k].z - mean) * rstd * g.z + b.z;
+                o.w = (v[k].w - mean) * rstd * g.w + b.w;
+                if (y_f32) reinterpret_cast<float4*>(y_f32 + row * (long long)D)[i] = o;
+                if (y_bf16) {
+                    uint2 p;
+                    p.x = pack_bf16(o.x, o.y);
+                    p.y = pack_bf16(o.z, o.w);
+                    reinterpret_cast<uint2*>(y_bf16 + row * (long long)D)[i] = p;
+                }
             }
         }
     }
@@ -70,8 +80,17 @@ int layernorm_fwd_launch(const float* x, long long row_stride, const float* gamm
     long long blocks = (rows + LN_WARPS - 1) / LN_WARPS;
     const long long cap = (long long)sm_count() * 8;
     if (blocks > cap) blocks = cap;
-    layernorm_fwd_kernel<<<(unsigned)blocks, LN_WARPS * 32, 0, stream>>>(x, row_stride, gamma, beta, y_bf16, y_f32,
-                                                                        mean, rstd, rows, dim, eps);
+    const int nvl = (dim / 4 + 31) / 32;
+    B200_CHECK_ARG(nvl <= 16, "layernorm_fwd: dim must be <= 2048 (got %d)", dim);
+#define LN_FWD_CASE(NV) layernorm_fwd_kernel<NV><<<(unsigned)blocks, LN_WARPS * 32, 0, stream>>>( \
+        x, row_stride, gamma, beta, y_bf16, y_f32, mean, rstd, rows, dim, eps)
+    if (nvl <= 1) LN_FWD_CASE(1);
+    else if (nvl <= 2) LN_FWD_CASE(2);
+    else if (nvl <= 4) LN_FWD_CASE(4);
+    else if (nvl <= 6) LN_FWD_CASE(6);
+    else if (nvl <= 8) LN_FWD_CASE(8);
+    else LN_FWD_CASE(16);
+#undef LN_FWD_CASE
     B200_LAUNCH_CHECK();
     return 0;
 }
@@ -108,6 +127,7 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
     }
     __syncwarp();
     const float4* gamma4 = reinterpret_cast<const float4*>(gamma);
+    const bool want_cols = dgamma != nullptr || dbeta != nullptr;
 
     for (long long row = (long long)blockIdx.x * LN_WARPS + warp; row < rows; row += (long long)gridDim.x * LN_WARPS) {
         const float mean = mean_in[row], rstd = rstd_in[row];
@@ -140,11 +160,13 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
                 const float a0 = dy[k].x * g.x, a1 = dy[k].y * g.y, a2 = dy[k].z * g.z, a3 = dy[k].w * g.w;
                 s1 += (a0 + a1) + (a2 + a3);
                 s2 += (a0 * xh[k].x + a1 * xh[k].y) + (a2 * xh[k].z + a3 * xh[k].w);
-                float4 ag = acc_g[i], ab = acc_b[i];
-                ag.x += dy[k].x * xh[k].x; ag.y += dy[k].y * xh[k].y; ag.z += dy[k].z * xh[k].z; ag.w += dy[k].w * xh[k].w;
-                ab.x += dy[k].x; ab.y += dy[k].y; ab.z += dy[k].z; ab.w += dy[k].w;
-                acc_g[i] = ag;
-                acc_b[i] = ab;
+                if (want_cols) {
+                    float4 ag = acc_g[i], ab = acc_b[i];
+                    ag.x += dy[k].x * xh[k].x; ag.y += dy[k].y * xh[k].y; ag.z += dy[k].z * xh[k].z; ag.w += dy[k].w * xh[k].w;
+                    ab.x += dy[k].x; ab.y += dy[k].y; ab.z += dy[k].z; ab.w += dy[k].w;
+                    acc_g[i] = ag;
+                    acc_b[i] = ab;
+                }
             }
         }
         const float c1 = warp_sum(s1) / (float)D;

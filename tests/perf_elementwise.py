@@ -23,6 +23,8 @@ dy = torch.randn(R, D, device=dev).bfloat16(); gin = torch.randn(R, D, device=de
 g16 = torch.empty(R, D, device=dev, dtype=torch.bfloat16); dg = torch.empty(D, device=dev); db = torch.empty(D, device=dev); dbn = torch.empty(D, device=dev)
 t = timeit(lambda: K.layernorm_bwd(dy, None, x, D, mean, rstd, gam, gin, gout, D, None, dg, db, None, R, D))
 print(f"ln_bwd        {t:7.1f} us  {R*D*14/t/1e3:7.0f} GB/s")
+t = timeit(lambda: K.layernorm_bwd(dy, None, x, D, mean, rstd, gam, gin, gout, D, None, None, None, None, R, D))
+print(f"ln_bwd nocols {t:7.1f} us  {R*D*14/t/1e3:7.0f} GB/s")
 t = timeit(lambda: K.layernorm_bwd(dy, None, x, D, mean, rstd, gam, gin, gout, D, g16, dg, db, dbn, R, D))
 print(f"ln_bwd+next   {t:7.1f} us  {R*D*16/t/1e3:7.0f} GB/s")
 da = torch.randn(R, M, device=dev).bfloat16(); o = torch.empty(M, device=dev)
@@ -30,3 +32,14 @@ t = timeit(lambda: K.colsum_bf16(da, M, o, R, M))
 print(f"colsum[R,M]   {t:7.1f} us  {R*M*2/t/1e3:7.0f} GB/s")
 t = timeit(lambda: K.dropout_cast(gin, g16, db, R, D, 0.1, 1, 2))
 print(f"dropout_cast  {t:7.1f} us  {R*D*6/t/1e3:7.0f} GB/s")
+
+# calibration: what torch's own elementwise kernels reach on this box
+t = timeit(lambda: gout.copy_(gin))
+print(f"torch copy f32 {t:7.1f} us  {R*D*8/t/1e3:7.0f} GB/s")
+t = timeit(lambda: g16.copy_(gin))
+print(f"torch cast     {t:7.1f} us  {R*D*6/t/1e3:7.0f} GB/s")
+big = torch.empty(1 << 29, device=dev, dtype=torch.bfloat16); big2 = torch.empty_like(big)
+t = timeit(lambda: big2.copy_(big))
+print(f"torch copy 1GiB{t:7.1f} us  {big.numel()*4/t/1e3:7.0f} GB/s")
+t = timeit(lambda: K.cast_bf16(gin, g16))
+print(f"our cast       {t:7.1f} us  {R*D*6/t/1e3:7.0f} GB/s")
