@@ -634,6 +634,7 @@ int attention_fwd_launch(const bf16* qkv, bf16* out, float* lse, int batch, int 
     B200_CHECK_ARG(((uintptr_t)qkv % 16) == 0 && ((uintptr_t)out % 16) == 0, "attention_fwd: unaligned pointer");
     if (tokens <= AT_RESIDENT_MAX_T && attention_mode() == 0)
         return attention_fwd_tc_launch(qkv, out, lse, batch, tokens, heads, scale, stream);
+    if (attention_mode() == 0) return attention_fwd_long_launch(qkv, out, lse, batch, tokens, heads, scale, stream);
     if (tokens <= AT_RESIDENT_MAX_T) {
         const int Tp = (tokens + 15) & ~15;
         const int ntiles = Tp / 16;

@@ -846,6 +846,278 @@ attention_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
     }
 }
 
+// =============================================================================================
+// Forward for long sequences (T > 256, e.g. the 577 tokens of 384x384 images): flash-style streaming over blocks of
+// 128 keys with an online softmax. A work item is (batch, head, pair of 128-query tiles); the pair shares one
+// stream of K/V blocks (4-deep TMA ring), tile g of the pair lives in TMEM slot g:
+//     [0, 128) S block (bf16 P packed in place: key half 0 -> [0, 32), half 1 -> [64, 96)) | [192, 256) O accumulator
+// and belongs to softmax group g (8 warps: thread <-> query row, two warps per row splitting the block's keys).
+// Per block: S = Q_g K_j^T -> running max m, P = exp2((S - m) c), l = l a + rowsum(P), O = O a (tcgen05.ld/st,
+// skipped when no row of the warp raised its max) -> O += P V_j (A operand from TMEM). The MMA thread issues
+// PV(g, j) and S(g, j+1) back to back, so one group's softmax overlaps the other group's tensor work.
+// =============================================================================================
+constexpr int ATL_BN = 128;          // keys per block
+constexpr int ATL_STAGES = 4;        // K/V ring depth
+
+__global__ void __launch_bounds__(ATC_THREADS, 1)
+attention_fwd_long_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
+                          bf16* __restrict__ out, float* __restrict__ lse, int num_items, int rounds, int T, int H,
+                          float scale_log2, float scale) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    constexpr uint32_t Q_BYTES = 2 * ATC_BM * 128;               // both query tiles of the pair
+    constexpr uint32_t KV_BYTES = ATL_BN * 128;                  // one K or V block
+    const uint32_t kv_base = smem_base + 2 * Q_BYTES;
+    const uint32_t xchg_base = kv_base + ATL_STAGES * 2 * KV_BYTES;     // float [2 groups][2 halves][128]: max; then sum
+    const uint32_t bar_base = xchg_base + 2u * 2u * 2u * 128u * 4u;
+    auto q_full = [&](int s) { return bar_base + 8u * s; };
+    auto q_empty = [&](int s) { return bar_base + 16u + 8u * s; };
+    auto kv_full = [&](int s) { return bar_base + 32u + 8u * s; };
+    auto kv_empty = [&](int s) { return bar_base + 64u + 8u * s; };
+    auto s_ready = [&](int g) { return bar_base + 96u + 8u * g; };
+    auto p_ready = [&](int g) { return bar_base + 112u + 8u * g; };
+    auto o_ready = [&](int g) { return bar_base + 128u + 8u * g; };
+    auto slot_free = [&](int g) { return bar_base + 144u + 8u * g; };
+    const uint32_t tmem_slot = bar_base + 160u;
+    uint8_t* gen = smem_raw - smem_u32(smem_raw);
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen + tmem_slot);
+    float* sMax = reinterpret_cast<float*>(gen + xchg_base);
+    float* sSum = sMax + 2 * 2 * 128;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nb = (T + ATL_BN - 1) / ATL_BN;                    // key blocks per head
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmQ);
+        prefetch_tmap(&tmKV);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(q_full(i), 1);
+            mbar_init(q_empty(i), 1);
+            mbar_init(s_ready(i), 1);
+            mbar_init(p_ready(i), 8);
+            mbar_init(o_ready(i), 1);
+            mbar_init(slot_free(i), 8);
+        }
+        for (int i = 0; i < ATL_STAGES; ++i) {
+            mbar_init(kv_full(i), 1);
+            mbar_init(kv_empty(i), 1);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc<1>(tmem_slot, ATC_TMEM_COLS);
+        tmem_relinquish<1>();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int it = 0;
+            uint32_t kvn = 0;
+            for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
+                const int w = item / rounds, r = item % rounds;
+                const int b = w / H, h = w % H;
+                const int qs = it & 1;
+                mbar_wait(q_empty(qs), ((it >> 1) & 1) ^ 1u);
+                mbar_arrive_expect_tx(q_full(qs), Q_BYTES);
+                tma_load_4d(smem_base + qs * Q_BYTES, &tmQ, q_full(qs), 0, r * 2 * ATC_BM, h, b);
+                for (int j = 0; j < nb; ++j, ++kvn) {
+                    const int st = kvn % ATL_STAGES;
+                    mbar_wait(kv_empty(st), ((kvn / ATL_STAGES) & 1) ^ 1u);
+                    const uint32_t sK = kv_base + st * 2 * KV_BYTES;
+                    mbar_arrive_expect_tx(kv_full(st), 2 * KV_BYTES);
+                    tma_load_4d(sK, &tmKV, kv_full(st), 0, j * ATL_BN, H + h, b);
+                    tma_load_4d(sK + KV_BYTES, &tmKV, kv_full(st), 0, j * ATL_BN, 2 * H + h, b);
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc_o = make_idesc_bf16(ATC_BM, 64, 0, 1);
+            uint32_t n_p[2] = {0, 0}, n_free[2] = {0, 0};
+            int it = 0;
+            uint32_t kvn = 0;
+            for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
+                const int r = item % rounds;
+                const int nact = T - r * 2 * ATC_BM > ATC_BM ? 2 : 1;       // active query tiles of this pair
+                const int qs = it & 1;
+                const uint32_t sQ = smem_base + qs * Q_BYTES;
+                mbar_wait(q_full(qs), (it >> 1) & 1);
+                tc_fence_after();
+                auto keys_in = [&](int j) { return min(ATL_BN, (T - j * ATL_BN + 15) & ~15); };
+                auto issue_S = [&](int g, int j) {     // S_g = Q_g K_j^T
+                    const uint32_t sK = kv_base + ((kvn + j) % ATL_STAGES) * 2 * KV_BYTES;
+                    const uint32_t idesc_s = make_idesc_bf16(ATC_BM, keys_in(j), 0, 0);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_bf16<1>(tmem + g * 256, make_smem_desc_sw128(sQ + g * (ATC_BM * 128) + k * 32, 1024, 0),
+                                     make_smem_desc_sw128(sK + k * 32, 1024, 0), idesc_s, k > 0 ? 1u : 0u);
+                    umma_commit(s_ready(g));
+                };
+                mbar_wait(kv_full(kvn % ATL_STAGES), (kvn / ATL_STAGES) & 1);
+                tc_fence_after();
+                for (int g = 0; g < nact; ++g) {
+                    mbar_wait(slot_free(g), (n_free[g] & 1u) ^ 1u);
+                    ++n_free[g];
+                    tc_fence_after();
+                    issue_S(g, 0);
+                }
+                for (int j = 0; j < nb; ++j) {
+                    const uint32_t sV = kv_base + ((kvn + j) % ATL_STAGES) * 2 * KV_BYTES + KV_BYTES;
+                    const int ksteps = keys_in(j) / 16;
+                    for (int g = 0; g < nact; ++g) {
+                        mbar_wait(p_ready(g), n_p[g] & 1u);
+                        ++n_p[g];
+                        tc_fence_after();
+                        // O_g (+)= P V_j : A = P in TMEM (8 packed columns per 16 keys), B = V_j [keys x 64] MN-major
+                        for (int k = 0; k < ksteps; ++k)
+                            umma_bf16_ts(tmem + g * 256 + ATC_O_COL, tmem + g * 256 + (k < 4 ? 8 * k : 64 + 8 * (k - 4)),
+                                         make_smem_desc_sw128(sV + k * 2048, 1024, 0), idesc_o, (j > 0 || k > 0) ? 1u : 0u);
+                        umma_commit(o_ready(g));
+                        if (g == nact - 1) umma_commit(kv_empty((kvn + j) % ATL_STAGES));   // both tiles are done with block j
+                        if (j + 1 < nb) {
+                            if (g == 0) {
+                                mbar_wait(kv_full((kvn + j + 1) % ATL_STAGES), ((kvn + j + 1) / ATL_STAGES) & 1);
+                                tc_fence_after();
+                            }
+                            issue_S(g, j + 1);
+                        }
+                    }
+                }
+                umma_commit(q_empty(qs));
+                kvn += nb;
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===================== softmax + epilogue groups =====================
+        const int sw = warp - 2;
+        const int g = sw >> 3;
+        const int half = (sw >> 2) & 1;
+        const int quarter = warp & 3;
+        const uint32_t tbase = tmem + g * 256 + ((uint32_t)(quarter * 32) << 16);
+        const int r_in_tile = quarter * 32 + lane;
+        float* myMax = sMax + (g * 2 + half) * 128, *otherMax = sMax + (g * 2 + (half ^ 1)) * 128;
+        float* mySum = sSum + (g * 2 + half) * 128, *otherSum = sSum + (g * 2 + (half ^ 1)) * 128;
+        uint32_t n_s = 0, n_o = 0;
+        for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+            const int w = item / rounds, r = item % rounds;
+            const int b = w / H, h = w % H;
+            const int row0 = (r * 2 + g) * ATC_BM;
+            if (row0 >= T) continue;                      // this pair has a single tile
+            const int r_in_head = row0 + r_in_tile;
+            float m = -INFINITY, l = 0.f;
+            for (int j = 0; j < nb; ++j) {
+                const int nvalid = min(ATL_BN, T - j * ATL_BN);
+                const int c_begin = half * 64, c_end = min(c_begin + 64, (nvalid + 15) & ~15);
+                mbar_wait(s_ready(g), n_s & 1u);
+                ++n_s;
+                tc_fence_after();
+                float mx = -INFINITY;
+                for (int c = c_begin; c < c_end; c += 16) {
+                    uint32_t v[16];
+                    tmem_ld_32x16(tbase + c, v);
+                    tmem_ld_wait();
+                    if (c + 16 <= nvalid) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) if (c + i < nvalid) mx = fmaxf(mx, __uint_as_float(v[i]));
+                    }
+                }
+                myMax[r_in_tile] = mx;
+                named_bar_sync(1 + g, 256);
+                const float m_new = fmaxf(m, fmaxf(mx, otherMax[r_in_tile]));
+                const float alpha = fast_ex2((m - m_new) * scale_log2);
+                const float mneg = -m_new * scale_log2;
+                float sum = 0.f;
+                for (int c = c_begin; c < c_end; c += 16) {
+                    uint32_t v[16];
+                    tmem_ld_32x16(tbase + c, v);
+                    tmem_ld_wait();
+                    float p[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) p[i] = fast_ex2(fmaf(__uint_as_float(v[i]), scale_log2, mneg));
+                    if (c + 16 > nvalid) {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) if (c + i >= nvalid) p[i] = 0.f;
+                    }
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        pk[i] = pack_bf16(p[2 * i], p[2 * i + 1]);
+                        sum += p[2 * i] + p[2 * i + 1];
+                    }
+                    tmem_st_32x8(tbase + c_begin + ((c - c_begin) >> 1), pk);
+                }
+                l = fmaf(l, alpha, sum);
+                m = m_new;
+                if (j > 0) {
+                    mbar_wait(o_ready(g), n_o & 1u);          // PV of the previous block has retired: O may be rescaled
+                    ++n_o;
+                    tc_fence_after();
+                    if (__any_sync(0xffffffffu, alpha < 1.f)) {
+                        uint32_t o[32];
+                        tmem_ld_32x32(tbase + ATC_O_COL + half * 32, o);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int q8 = 0; q8 < 4; ++q8) {
+                            uint32_t t8[8];
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) t8[i] = __float_as_uint(__uint_as_float(o[8 * q8 + i]) * alpha);
+                            tmem_st_32x8(tbase + ATC_O_COL + half * 32 + 8 * q8, t8);
+                        }
+                    }
+                }
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(p_ready(g));
+            }
+            mySum[r_in_tile] = l;
+            named_bar_sync(1 + g, 256);
+            l += otherSum[r_in_tile];
+            const float inv = 1.0f / l;
+            const bool row_ok = r_in_head < T;
+            if (row_ok && half == 0) lse[(long long)w * T + r_in_head] = m * scale + logf(l);
+            mbar_wait(o_ready(g), n_o & 1u);
+            ++n_o;
+            tc_fence_after();
+            uint32_t o[32];
+            tmem_ld_32x32(tbase + ATC_O_COL + half * 32, o);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(slot_free(g));
+            if (row_ok) {
+                bf16* dst = out + (((long long)b * T + r_in_head) * H + h) * 64 + half * 32;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    uint4 q;
+                    q.x = pack_bf16(__uint_as_float(o[8 * i]) * inv, __uint_as_float(o[8 * i + 1]) * inv);
+                    q.y = pack_bf16(__uint_as_float(o[8 * i + 2]) * inv, __uint_as_float(o[8 * i + 3]) * inv);
+                    q.z = pack_bf16(__uint_as_float(o[8 * i + 4]) * inv, __uint_as_float(o[8 * i + 5]) * inv);
+                    q.w = pack_bf16(__uint_as_float(o[8 * i + 6]) * inv, __uint_as_float(o[8 * i + 7]) * inv);
+                    reinterpret_cast<uint4*>(dst)[i] = q;
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<1>(tmem, ATC_TMEM_COLS);
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 static PFN_cuTensorMapEncodeTiled atc_encode_fn() {
     static PFN_cuTensorMapEncodeTiled fn = nullptr;
@@ -892,6 +1164,26 @@ int attention_fwd_tc_launch(const bf16* qkv, bf16* out, float* lse, int batch, i
     const int grid = total < sm_count() ? total : sm_count();
     attention_fwd_tc_kernel<<<grid, ATC_THREADS, smem, stream>>>(tmQ, tmKV, out, lse, total, tokens, Nk, heads,
                                                                scale * 1.4426950408889634f, scale);
+    B200_LAUNCH_CHECK();
+    return 0;
+}
+
+int attention_fwd_long_launch(const bf16* qkv, bf16* out, float* lse, int batch, int tokens, int heads, float scale,
+                              cudaStream_t stream) {
+    const int nt = (tokens + ATC_BM - 1) / ATC_BM;
+    const int rounds = (nt + 1) / 2;
+    CUtensorMap tmQ, tmKV;
+    int rc = make_tmap_rows64(&tmQ, qkv, batch, tokens, 3 * heads, 2 * ATC_BM);
+    if (rc) return rc;
+    rc = make_tmap_rows64(&tmKV, qkv, batch, tokens, 3 * heads, ATL_BN);
+    if (rc) return rc;
+    const size_t smem = 1024 + 2 * (2 * ATC_BM * 128) + (size_t)ATL_STAGES * 2 * ATL_BN * 128 + 2 * 2 * 2 * 128 * 4 + 256;
+    B200_CUDA(cudaFuncSetAttribute(attention_fwd_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const long long items = (long long)batch * heads * rounds;
+    B200_CHECK_ARG(items < (1LL << 31), "attention_fwd: too many work items");
+    const int grid = items < sm_count() ? (int)items : sm_count();
+    attention_fwd_long_kernel<<<grid, ATC_THREADS, smem, stream>>>(tmQ, tmKV, out, lse, (int)items, rounds, tokens, heads,
+                                                                 scale * 1.4426950408889634f, scale);
     B200_LAUNCH_CHECK();
     return 0;
 }

@@ -36,6 +36,8 @@ int attention_fwd_launch(const bf16* qkv, bf16* out, float* lse, int batch, int 
                          float scale, cudaStream_t stream);
 int attention_fwd_tc_launch(const bf16* qkv, bf16* out, float* lse, int batch, int tokens, int heads, float scale,
                             cudaStream_t stream);
+int attention_fwd_long_launch(const bf16* qkv, bf16* out, float* lse, int batch, int tokens, int heads, float scale,
+                              cudaStream_t stream);
 int attention_bwd_tc_launch(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, bf16* dqkv, int batch,
                             int tokens, int heads, float scale, cudaStream_t stream);
 int attention_bwd_launch(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, float* delta,

@@ -6,7 +6,9 @@ sys.path.insert(0, str(ROOT / "pytorch-vit-paper-replication_b200"))
 import torch
 from b200vit import kernels as K
 dev = torch.device("cuda:0")
-B, T, H, hd = 256, 197, 12, 64
+# usage: perf_attn.py [B T H]   (default: the ViT-B/16 case 256 197 12; ViT-L/16-384: 64 577 16)
+B, T, H = (int(a) for a in sys.argv[1:4]) if len(sys.argv) >= 4 else (256, 197, 12)
+hd = 64
 qkv = torch.randn(B, T, 3, H, hd, device=dev).bfloat16()
 out = torch.empty(B, T, H * hd, device=dev, dtype=torch.bfloat16)
 lse = torch.empty(B, H, T, device=dev)

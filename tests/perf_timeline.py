@@ -10,13 +10,16 @@ from b200vit.models.vit import ViT
 from b200vit.nn import CrossEntropyLoss
 from b200vit.optim import FusedAdam
 
-B = 256
+# usage: perf_timeline.py [vitl]   (default: ViT-B/16 3-class B=256; vitl: ViT-L/16 at 384x384, B=64)
+VITL = len(sys.argv) > 1 and sys.argv[1] == "vitl"
+B, IMG, NC = (64, 384, 1000) if VITL else (256, 224, 3)
 dev = torch.device("cuda:0")
 torch.manual_seed(0)
-m = ViT(num_classes=3).to(dev).train()
+kw = dict(image_size=384, num_transformer_layer=24, embedding_dim=1024, num_heads=16, mlp_size=4096) if VITL else {}
+m = ViT(num_classes=NC, **kw).to(dev).train()
 opt = FusedAdam(m.parameters(), lr=1e-4)
 lf = CrossEntropyLoss()
-X = torch.rand(B, 3, 224, 224, device=dev); y = torch.randint(0, 3, (B,), device=dev)
+X = torch.rand(B, 3, IMG, IMG, device=dev); y = torch.randint(0, NC, (B,), device=dev)
 def step():
     loss = lf(m(X), y); opt.zero_grad(); loss.backward(); opt.step(max_norm=1.0)
 for _ in range(4): step()
@@ -40,5 +43,5 @@ for g in gaps[:12]:
 import collections
 agg = collections.defaultdict(float)
 for s, e, n in ks: agg[n[:60]] += (e - s)
-for n, t in sorted(agg.items(), key=lambda kv: -kv[1])[:14]:
+for n, t in sorted(agg.items(), key=lambda kv: -kv[1])[:24]:
     print(f"{t/3e3:8.3f} ms/step  {n}")
