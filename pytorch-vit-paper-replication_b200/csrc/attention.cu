@@ -675,6 +675,8 @@ int attention_bwd_launch(const bf16* qkv, const bf16* out, const bf16* dout, con
     const long long rows = (long long)batch * tokens * heads;
     attention_delta_kernel<<<(unsigned)((rows * 32 + 255) / 256), 256, 0, stream>>>(out, dout, delta, batch, tokens, heads);
     B200_LAUNCH_CHECK();
+    if (attention_mode() == 0 && tokens <= AT_LONG_MAX_T)
+        return attention_bwd_long_launch(qkv, dout, lse, delta, dqkv, batch, tokens, heads, scale, stream);
     dim3 grid(batch * heads, (tokens + AT_BLOCK - 1) / AT_BLOCK);
     const float sl2 = scale * 1.4426950408889634f;
     attention_bwd_dkdv_kernel<<<grid, AT_THREADS, 0, stream>>>(qkv, dout, lse, delta, dqkv, tokens, heads, sl2, scale);

@@ -1118,6 +1118,313 @@ attention_fwd_long_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
     }
 }
 
+// =============================================================================================
+// Backward for long sequences (T > 256). Same two item types as the short kernels -- "KV" items (rows = 128 keys:
+// S^T = K_t Q^T, dP^T = V_t dO^T -> dV_t = P^T dO, dK_t = dS^T Q) and "Q" items (rows = 128 queries: S = Q_t K^T,
+// dP = dO_t V^T -> dQ_t = dS K) -- but the other dimension is streamed in chunks of 64 columns through a 4-deep
+// TMA ring, and the gradients accumulate across the chunks in TMEM. A work item is (batch, head, type, pair of
+// row tiles); the pair shares the chunk stream, tile g of the pair owns TMEM slot g:
+//     [0, 64) acc0 chunk (packed P in place) | [64, 128) acc1 chunk (packed dS in place) | [128, 192) out0 (dV) |
+//     [192, 256) out1 (dK or dQ)
+// and math group g (8 warps: thread <-> row, two warps per row splitting the chunk's columns; each column half packs
+// into the front of its own range). The MMA thread issues the gradient MMAs of chunk c and the S/dP MMAs of chunk
+// c+1 back to back, so one group's math overlaps the other group's tensor work. delta = rowsum(dO * O) comes from
+// a small pre-pass kernel ([B, H, T] fp32, like lse); the producer warp stages each chunk's column statistics.
+// =============================================================================================
+constexpr int ATLB_W = 64;           // columns per chunk
+constexpr int ATLB_STAGES = 4;
+
+__global__ void __launch_bounds__(ATC_THREADS, 1)
+attention_bwd_long_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmXdO,
+                          const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmYdO,
+                          const float* __restrict__ lse, const float* __restrict__ delta, bf16* __restrict__ dqkv,
+                          int num_items, int rounds, int T, int H, float scale_log2, float scale) {
+    extern __shared__ uint8_t smem_raw[];
+    const int nc = (T + ATLB_W - 1) / ATLB_W;                    // column chunks per item
+    const uint32_t Tp = (uint32_t)nc * ATLB_W;
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    constexpr uint32_t X_BYTES = 2 * ATC_BM * 128;               // one operand, both row tiles of the pair
+    constexpr uint32_t Y_BYTES = ATLB_W * 128;                   // one operand chunk
+    const uint32_t ch_base = smem_base + 2 * 2 * X_BYTES;
+    const uint32_t stat_base = ch_base + ATLB_STAGES * 2 * Y_BYTES;     // per X stage: lse*log2e [Tp], delta*scale [Tp]
+    const uint32_t bar_base = stat_base + 2u * 2u * Tp * 4u;
+    auto x_full = [&](int s) { return bar_base + 8u * s; };
+    auto x_empty = [&](int s) { return bar_base + 16u + 8u * s; };
+    auto ch_full = [&](int s) { return bar_base + 32u + 8u * s; };
+    auto ch_empty = [&](int s) { return bar_base + 64u + 8u * s; };
+    auto s_ready = [&](int g) { return bar_base + 96u + 8u * g; };
+    auto p_ready = [&](int g) { return bar_base + 112u + 8u * g; };
+    auto o_ready = [&](int g) { return bar_base + 128u + 8u * g; };
+    auto slot_free = [&](int g) { return bar_base + 144u + 8u * g; };
+    const uint32_t tmem_slot = bar_base + 160u;
+    uint8_t* gen = smem_raw - smem_u32(smem_raw);
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen + tmem_slot);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int items_per_head = 2 * rounds;
+    const float LOG2E = 1.4426950408889634f;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmX);
+        prefetch_tmap(&tmXdO);
+        prefetch_tmap(&tmY);
+        prefetch_tmap(&tmYdO);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(x_full(i), 2);          // TMA transaction + the head's statistics
+            mbar_init(x_empty(i), 1);
+            mbar_init(s_ready(i), 1);
+            mbar_init(p_ready(i), 8);
+            mbar_init(o_ready(i), 1);
+            mbar_init(slot_free(i), 8);
+        }
+        for (int i = 0; i < ATLB_STAGES; ++i) {
+            mbar_init(ch_full(i), 1);
+            mbar_init(ch_empty(i), 1);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc<1>(tmem_slot, 512);
+        tmem_relinquish<1>();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        // ===================== TMA producer + column statistics =====================
+        int it = 0;
+        uint32_t chn = 0;
+        for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
+            const int w = item / items_per_head, idx = item % items_per_head;
+            const bool kv_item = idx < rounds;
+            const int r = kv_item ? idx : idx - rounds;
+            const int b = w / H, h = w % H;
+            const int xs = it & 1;
+            if (lane == 0) {
+                mbar_wait(x_empty(xs), ((it >> 1) & 1) ^ 1u);
+                const uint32_t sX = smem_base + xs * 2 * X_BYTES;
+                mbar_arrive_expect_tx(x_full(xs), 2 * X_BYTES);
+                if (kv_item) {
+                    tma_load_4d(sX, &tmX, x_full(xs), 0, r * 2 * ATC_BM, H + h, b);                  // K rows
+                    tma_load_4d(sX + X_BYTES, &tmX, x_full(xs), 0, r * 2 * ATC_BM, 2 * H + h, b);    // V rows
+                } else {
+                    tma_load_4d(sX, &tmX, x_full(xs), 0, r * 2 * ATC_BM, h, b);                      // Q rows
+                    tma_load_4d(sX + X_BYTES, &tmXdO, x_full(xs), 0, r * 2 * ATC_BM, h, b);          // dO rows
+                }
+            }
+            __syncwarp();
+            {   // the head's statistics: lse*log2e (+inf beyond T, so padded columns get P = 0) and delta*scale
+                float* sL = reinterpret_cast<float*>(gen + stat_base + (uint32_t)xs * 2u * Tp * 4u);
+                float* sD = sL + Tp;
+                for (int t = lane; t < (int)Tp; t += 32) {
+                    sL[t] = t < T ? __ldg(lse + (long long)w * T + t) * LOG2E : INFINITY;
+                    sD[t] = t < T ? __ldg(delta + (long long)w * T + t) * scale : 0.f;
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(x_full(xs));
+            }
+            for (int c = 0; c < nc; ++c, ++chn) {
+                const int st = chn % ATLB_STAGES;
+                if (lane == 0) {
+                    mbar_wait(ch_empty(st), ((chn / ATLB_STAGES) & 1) ^ 1u);
+                    const uint32_t sY = ch_base + st * 2 * Y_BYTES;
+                    mbar_arrive_expect_tx(ch_full(st), 2 * Y_BYTES);
+                    if (kv_item) {
+                        tma_load_4d(sY, &tmY, ch_full(st), 0, c * ATLB_W, h, b);                     // Q chunk
+                        tma_load_4d(sY + Y_BYTES, &tmYdO, ch_full(st), 0, c * ATLB_W, h, b);         // dO chunk
+                    } else {
+                        tma_load_4d(sY, &tmY, ch_full(st), 0, c * ATLB_W, H + h, b);                 // K chunk
+                        tma_load_4d(sY + Y_BYTES, &tmY, ch_full(st), 0, c * ATLB_W, 2 * H + h, b);   // V chunk
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            const uint32_t idesc2 = make_idesc_bf16(ATC_BM, 64, 0, 1);
+            uint32_t n_p[2] = {0, 0}, n_free[2] = {0, 0};
+            int it = 0;
+            uint32_t chn = 0;
+            for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
+                const int idx = item % items_per_head;
+                const bool kv_item = idx < rounds;
+                const int r = kv_item ? idx : idx - rounds;
+                const int nact = T - r * 2 * ATC_BM > ATC_BM ? 2 : 1;
+                const int xs = it & 1;
+                const uint32_t sX = smem_base + xs * 2 * X_BYTES, sX2 = sX + X_BYTES;
+                mbar_wait(x_full(xs), (it >> 1) & 1);
+                tc_fence_after();
+                auto width = [&](int c) { return min(ATLB_W, (T - c * ATLB_W + 15) & ~15); };
+                auto issue_1 = [&](int g, int c) {      // acc0 = X_g Y_c^T, acc1 = X2_g Y2_c^T (independent chains, interleaved)
+                    const uint32_t sY = ch_base + ((chn + c) % ATLB_STAGES) * 2 * Y_BYTES, sY2 = sY + Y_BYTES;
+                    const uint32_t idesc1 = make_idesc_bf16(ATC_BM, width(c), 0, 0);
+                    const uint32_t slot = tmem + g * 256, xo = g * (ATC_BM * 128);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        umma_bf16<1>(slot, make_smem_desc_sw128(sX + xo + k * 32, 1024, 0),
+                                     make_smem_desc_sw128(sY + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
+                        umma_bf16<1>(slot + 64, make_smem_desc_sw128(sX2 + xo + k * 32, 1024, 0),
+                                     make_smem_desc_sw128(sY2 + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
+                    }
+                    umma_commit(s_ready(g));
+                };
+                mbar_wait(ch_full(chn % ATLB_STAGES), (chn / ATLB_STAGES) & 1);
+                tc_fence_after();
+                for (int g = 0; g < nact; ++g) issue_1(g, 0);
+                for (int c = 0; c < nc; ++c) {
+                    const uint32_t sY = ch_base + ((chn + c) % ATLB_STAGES) * 2 * Y_BYTES, sY2 = sY + Y_BYTES;
+                    const int ksteps = width(c) / 16;
+                    for (int g = 0; g < nact; ++g) {
+                        const uint32_t slot = tmem + g * 256;
+                        mbar_wait(p_ready(g), n_p[g] & 1u);
+                        ++n_p[g];
+                        if (c == 0) {       // the previous item's gradients must have been read out of this slot
+                            mbar_wait(slot_free(g), (n_free[g] & 1u) ^ 1u);
+                            ++n_free[g];
+                        }
+                        tc_fence_after();
+                        for (int k = 0; k < ksteps; ++k) {
+                            const uint32_t acol = k < 2 ? 8 * k : 32 + 8 * (k - 2);
+                            const uint32_t acc = (c > 0 || k > 0) ? 1u : 0u;
+                            if (kv_item)                  // dV_t += P^T dO_c
+                                umma_bf16_ts(slot + 128, slot + acol, make_smem_desc_sw128(sY2 + k * 2048, 1024, 0), idesc2, acc);
+                            // dK_t += dS^T Q_c   or   dQ_t += dS K_c
+                            umma_bf16_ts(slot + 192, slot + 64 + acol, make_smem_desc_sw128(sY + k * 2048, 1024, 0), idesc2, acc);
+                        }
+                        if (c == nc - 1) umma_commit(o_ready(g));
+                        if (g == nact - 1) umma_commit(ch_empty((chn + c) % ATLB_STAGES));
+                        if (c + 1 < nc) {
+                            if (g == 0) {
+                                mbar_wait(ch_full((chn + c + 1) % ATLB_STAGES), ((chn + c + 1) / ATLB_STAGES) & 1);
+                                tc_fence_after();
+                            }
+                            issue_1(g, c + 1);
+                        }
+                    }
+                }
+                umma_commit(x_empty(xs));
+                chn += nc;
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===================== math + read-out groups =====================
+        const int sw = warp - 2;
+        const int g = sw >> 3;
+        const int half = (sw >> 2) & 1;
+        const int quarter = warp & 3;
+        const uint32_t slot = tmem + g * 256 + ((uint32_t)(quarter * 32) << 16);
+        const long long rs = 3LL * H * 64;
+        uint32_t n_s = 0, n_o = 0;
+        int it = 0;
+        for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++it) {
+            const int w = item / items_per_head, idx = item % items_per_head;
+            const bool kv_item = idx < rounds;
+            const int r = kv_item ? idx : idx - rounds;
+            const int b = w / H, h = w % H;
+            const int row0 = (r * 2 + g) * ATC_BM;
+            if (row0 >= T) continue;                      // this pair has a single tile
+            const int row = row0 + quarter * 32 + lane;
+            const bool row_ok = row < T;
+            const float* sL = reinterpret_cast<const float*>(gen + stat_base + (uint32_t)(it & 1) * 2u * Tp * 4u);
+            const float* sD = sL + Tp;
+            mbar_wait(x_full(it & 1), (it >> 1) & 1);                 // the head's statistics are staged
+            const float row_lse2 = row_ok ? sL[row] : 0.f, row_delta = row_ok ? sD[row] : 0.f;
+            const int cb = half * 32;
+            for (int c = 0; c < nc; ++c) {
+                const int W = min(ATLB_W, (T - c * ATLB_W + 15) & ~15);
+                const int ce = min(cb + 32, W);
+                mbar_wait(s_ready(g), n_s & 1u);
+                ++n_s;
+                tc_fence_after();
+                for (int cc = cb; cc < ce; cc += 16) {
+                    uint32_t sv[16], dp[16];
+                    tmem_ld_32x16(slot + cc, sv);
+                    tmem_ld_32x16(slot + 64 + cc, dp);
+                    float l2[16], dl[16];
+                    if (kv_item) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float4 a = reinterpret_cast<const float4*>(sL + c * ATLB_W + cc)[i];
+                            const float4 d = reinterpret_cast<const float4*>(sD + c * ATLB_W + cc)[i];
+                            l2[4 * i] = a.x; l2[4 * i + 1] = a.y; l2[4 * i + 2] = a.z; l2[4 * i + 3] = a.w;
+                            dl[4 * i] = d.x; dl[4 * i + 1] = d.y; dl[4 * i + 2] = d.z; dl[4 * i + 3] = d.w;
+                        }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) { l2[i] = row_lse2; dl[i] = row_delta; }
+                    }
+                    tmem_ld_wait();
+                    float p[16], ds[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        p[i] = fast_ex2(fmaf(__uint_as_float(sv[i]), scale_log2, -l2[i]));
+                        ds[i] = p[i] * fmaf(__uint_as_float(dp[i]), scale, -dl[i]);
+                    }
+                    if (!kv_item && c * ATLB_W + cc + 16 > T) {      // Q item: padded key columns must not contribute to dQ
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) if (c * ATLB_W + cc + i >= T) ds[i] = 0.f;
+                    }
+                    uint32_t pk[8];
+                    if (kv_item) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) pk[i] = pack_bf16(p[2 * i], p[2 * i + 1]);
+                        tmem_st_32x8(slot + cb + ((cc - cb) >> 1), pk);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) pk[i] = pack_bf16(ds[2 * i], ds[2 * i + 1]);
+                    tmem_st_32x8(slot + 64 + cb + ((cc - cb) >> 1), pk);
+                }
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(p_ready(g));
+            }
+            // read-out: this warp converts 32 of the 64 gradient columns of its rows
+            mbar_wait(o_ready(g), n_o & 1u);
+            ++n_o;
+            tc_fence_after();
+            uint32_t r1[32], r0[32];
+            tmem_ld_32x32(slot + 192 + half * 32, r1);
+            if (kv_item) tmem_ld_32x32(slot + 128 + half * 32, r0);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(slot_free(g));
+            if (row_ok) {
+                bf16* base = dqkv + ((long long)b * T + row) * rs + (long long)h * 64 + half * 32;
+                auto emit = [&](const uint32_t (&v)[32], bf16* dst) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        uint4 q;
+                        q.x = pack_bf16(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1]));
+                        q.y = pack_bf16(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3]));
+                        q.z = pack_bf16(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5]));
+                        q.w = pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7]));
+                        reinterpret_cast<uint4*>(dst)[i] = q;
+                    }
+                };
+                if (kv_item) {
+                    emit(r1, base + (long long)H * 64);        // dK
+                    emit(r0, base + 2LL * H * 64);             // dV
+                } else {
+                    emit(r1, base);                            // dQ
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<1>(tmem, 512);
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 static PFN_cuTensorMapEncodeTiled atc_encode_fn() {
     static PFN_cuTensorMapEncodeTiled fn = nullptr;
@@ -1184,6 +1491,33 @@ int attention_fwd_long_launch(const bf16* qkv, bf16* out, float* lse, int batch,
     const int grid = items < sm_count() ? (int)items : sm_count();
     attention_fwd_long_kernel<<<grid, ATC_THREADS, smem, stream>>>(tmQ, tmKV, out, lse, (int)items, rounds, tokens, heads,
                                                                  scale * 1.4426950408889634f, scale);
+    B200_LAUNCH_CHECK();
+    return 0;
+}
+
+int attention_bwd_long_launch(const bf16* qkv, const bf16* dout, const float* lse, const float* delta, bf16* dqkv,
+                              int batch, int tokens, int heads, float scale, cudaStream_t stream) {
+    const int nt = (tokens + ATC_BM - 1) / ATC_BM;
+    const int rounds = (nt + 1) / 2;
+    const int Tp = (tokens + ATLB_W - 1) / ATLB_W * ATLB_W;
+    CUtensorMap tx, txd, ty, tyd;
+    int rc = make_tmap_rows64(&tx, qkv, batch, tokens, 3 * heads, 2 * ATC_BM);
+    if (rc) return rc;
+    rc = make_tmap_rows64(&txd, dout, batch, tokens, heads, 2 * ATC_BM);
+    if (rc) return rc;
+    rc = make_tmap_rows64(&ty, qkv, batch, tokens, 3 * heads, ATLB_W);
+    if (rc) return rc;
+    rc = make_tmap_rows64(&tyd, dout, batch, tokens, heads, ATLB_W);
+    if (rc) return rc;
+    const size_t smem = 1024 + 2 * 2 * (size_t)(2 * ATC_BM * 128) + (size_t)ATLB_STAGES * 2 * ATLB_W * 128 +
+                        2 * 2 * (size_t)Tp * 4 + 256;
+    B200_CHECK_ARG(smem <= 232448, "attention_bwd: %d tokens exceed the staged-statistics limit (%d)", tokens, AT_LONG_MAX_T);
+    B200_CUDA(cudaFuncSetAttribute(attention_bwd_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const long long items = (long long)batch * heads * 2 * rounds;
+    B200_CHECK_ARG(items < (1LL << 31), "attention_bwd: too many work items");
+    const int grid = items < sm_count() ? (int)items : sm_count();
+    attention_bwd_long_kernel<<<grid, ATC_THREADS, smem, stream>>>(tx, txd, ty, tyd, lse, delta, dqkv, (int)items, rounds,
+                                                                 tokens, heads, scale * 1.4426950408889634f, scale);
     B200_LAUNCH_CHECK();
     return 0;
 }

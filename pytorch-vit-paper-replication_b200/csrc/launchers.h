@@ -38,6 +38,9 @@ int attention_fwd_tc_launch(const bf16* qkv, bf16* out, float* lse, int batch, i
                             cudaStream_t stream);
 int attention_fwd_long_launch(const bf16* qkv, bf16* out, float* lse, int batch, int tokens, int heads, float scale,
                               cudaStream_t stream);
+constexpr int AT_LONG_MAX_T = 2048;   // the long backward kernel stages lse/delta of a whole head in shared memory
+int attention_bwd_long_launch(const bf16* qkv, const bf16* dout, const float* lse, const float* delta, bf16* dqkv,
+                              int batch, int tokens, int heads, float scale, cudaStream_t stream);
 int attention_bwd_tc_launch(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, bf16* dqkv, int batch,
                             int tokens, int heads, float scale, cudaStream_t stream);
 int attention_bwd_launch(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, float* delta,
