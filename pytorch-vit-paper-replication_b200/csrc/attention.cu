@@ -226,18 +226,30 @@ attention_fwd_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, float
 // ---------------------------------------------------------------------------------------------
 __global__ void attention_delta_kernel(const bf16* __restrict__ out, const bf16* __restrict__ dout,
                                        float* __restrict__ delta, int B, int T, int H) {
-    const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
-    if (w >= (long long)B * T * H) return;
-    const int h = (int)(w % H);
-    const long long bt = w / H;
-    const int t = (int)(bt % T), b = (int)(bt / T);
-    const uint32_t o = reinterpret_cast<const uint32_t*>(out + w * AT_HD)[lane];
-    const uint32_t d = reinterpret_cast<const uint32_t*>(dout + w * AT_HD)[lane];
-    const float2 fo = unpack_bf16(o), fd = unpack_bf16(d);
-    float s = fo.x * fd.x + fo.y * fd.y;
-    s = warp_sum(s);
-    if (lane == 0) delta[((long long)b * H + h) * T + t] = s;
+    // 8 lanes per (batch, token, head) row of 64 elements: one 16-byte load per lane and operand
+    const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+    const int sub = threadIdx.x & 7;
+    const bool ok = w < (long long)B * T * H;
+    float s = 0.f;
+    if (ok) {
+        const uint4 o = __ldg(reinterpret_cast<const uint4*>(out + w * AT_HD) + sub);
+        const uint4 d = __ldg(reinterpret_cast<const uint4*>(dout + w * AT_HD) + sub);
+        const uint32_t ow[4] = {o.x, o.y, o.z, o.w}, dw[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float2 fo = unpack_bf16(ow[k]), fd = unpack_bf16(dw[k]);
+            s = fmaf(fo.x, fd.x, fmaf(fo.y, fd.y, s));
+        }
+    }
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    if (ok && sub == 0) {
+        const int h = (int)(w % H);
+        const long long bt = w / H;
+        const int t = (int)(bt % T), b = (int)(bt / T);
+        delta[((long long)b * H + h) * T + t] = s;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -673,7 +685,7 @@ int attention_bwd_launch(const bf16* qkv, const bf16* out, const bf16* dout, con
         return 0;
     }
     const long long rows = (long long)batch * tokens * heads;
-    attention_delta_kernel<<<(unsigned)((rows * 32 + 255) / 256), 256, 0, stream>>>(out, dout, delta, batch, tokens, heads);
+    attention_delta_kernel<<<(unsigned)((rows * 8 + 255) / 256), 256, 0, stream>>>(out, dout, delta, batch, tokens, heads);
     B200_LAUNCH_CHECK();
     if (attention_mode() == 0 && tokens <= AT_LONG_MAX_T)
         return attention_bwd_long_launch(qkv, dout, lse, delta, dqkv, batch, tokens, heads, scale, stream);

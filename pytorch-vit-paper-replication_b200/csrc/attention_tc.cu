@@ -1012,6 +1012,30 @@ attention_fwd_long_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
             const int row0 = (r * 2 + g) * ATC_BM;
             if (row0 >= T) continue;                      // this pair has a single tile
             const int r_in_head = row0 + r_in_tile;
+            if (row0 + quarter * 32 >= T) {
+                // all 32 rows of this warp lie beyond T: no TMEM reads, no math -- only the barrier protocol (TMEM read
+                // bandwidth and the schedulers are what bound this kernel). The P rows stay garbage, which only reaches
+                // O rows that are never stored. Kept as a separate loop so the hot path's register allocation is untouched.
+                for (int j = 0; j < nb; ++j) {
+                    mbar_wait(s_ready(g), n_s & 1u);
+                    ++n_s;
+                    myMax[r_in_tile] = -INFINITY;
+                    named_bar_sync(1 + g, 256);
+                    if (j > 0) {
+                        mbar_wait(o_ready(g), n_o & 1u);
+                        ++n_o;
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(p_ready(g));
+                }
+                mySum[r_in_tile] = 0.f;
+                named_bar_sync(1 + g, 256);
+                mbar_wait(o_ready(g), n_o & 1u);
+                ++n_o;
+                __syncwarp();
+                if (lane == 0) mbar_arrive(slot_free(g));
+                continue;
+            }
             float m = -INFINITY, l = 0.f;
             for (int j = 0; j < nb; ++j) {
                 const int nvalid = min(ATL_BN, T - j * ATL_BN);
@@ -1328,9 +1352,24 @@ attention_bwd_long_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_
             const int b = w / H, h = w % H;
             const int row0 = (r * 2 + g) * ATC_BM;
             if (row0 >= T) continue;                      // this pair has a single tile
+            if (row0 + quarter * 32 >= T) {
+                // all 32 rows of this warp lie beyond T: only the barrier protocol (see the forward kernel)
+                mbar_wait(x_full(it & 1), (it >> 1) & 1);
+                for (int c = 0; c < nc; ++c) {
+                    mbar_wait(s_ready(g), n_s & 1u);
+                    ++n_s;
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(p_ready(g));
+                }
+                mbar_wait(o_ready(g), n_o & 1u);
+                ++n_o;
+                __syncwarp();
+                if (lane == 0) mbar_arrive(slot_free(g));
+                continue;
+            }
             const int row = row0 + quarter * 32 + lane;
             const bool row_ok = row < T;
-            const float* sL = reinterpret_cast<const float*>(gen + stat_base + (uint32_t)(it & 1) * 2u * Tp * 4u);
+                        const float* sL = reinterpret_cast<const float*>(gen + stat_base + (uint32_t)(it & 1) * 2u * Tp * 4u);
             const float* sD = sL + Tp;
             mbar_wait(x_full(it & 1), (it >> 1) & 1);                 // the head's statistics are staged
             const float row_lse2 = row_ok ? sL[row] : 0.f, row_delta = row_ok ? sD[row] : 0.f;
@@ -1345,25 +1384,23 @@ attention_bwd_long_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_
                     uint32_t sv[16], dp[16];
                     tmem_ld_32x16(slot + cc, sv);
                     tmem_ld_32x16(slot + 64 + cc, dp);
-                    float l2[16], dl[16];
-                    if (kv_item) {
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            const float4 a = reinterpret_cast<const float4*>(sL + c * ATLB_W + cc)[i];
-                            const float4 d = reinterpret_cast<const float4*>(sD + c * ATLB_W + cc)[i];
-                            l2[4 * i] = a.x; l2[4 * i + 1] = a.y; l2[4 * i + 2] = a.z; l2[4 * i + 3] = a.w;
-                            dl[4 * i] = d.x; dl[4 * i + 1] = d.y; dl[4 * i + 2] = d.z; dl[4 * i + 3] = d.w;
-                        }
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) { l2[i] = row_lse2; dl[i] = row_delta; }
-                    }
                     tmem_ld_wait();
                     float p[16], ds[16];
 #pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        p[i] = fast_ex2(fmaf(__uint_as_float(sv[i]), scale_log2, -l2[i]));
-                        ds[i] = p[i] * fmaf(__uint_as_float(dp[i]), scale, -dl[i]);
+                    for (int i4 = 0; i4 < 4; ++i4) {
+                        float4 a = make_float4(row_lse2, row_lse2, row_lse2, row_lse2);
+                        float4 d = make_float4(row_delta, row_delta, row_delta, row_delta);
+                        if (kv_item) {
+                            a = reinterpret_cast<const float4*>(sL + c * ATLB_W + cc)[i4];
+                            d = reinterpret_cast<const float4*>(sD + c * ATLB_W + cc)[i4];
+                        }
+                        const float l2[4] = {a.x, a.y, a.z, a.w}, dl[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const int i = 4 * i4 + k;
+                            p[i] = fast_ex2(fmaf(__uint_as_float(sv[i]), scale_log2, -l2[k]));
+                            ds[i] = p[i] * fmaf(__uint_as_float(dp[i]), scale, -dl[k]);
+                        }
                     }
                     if (!kv_item && c * ATLB_W + cc + 16 > T) {      // Q item: padded key columns must not contribute to dQ
 #pragma unroll
