@@ -83,14 +83,20 @@ if "c4" in which:
 if "c5" in which:
     torch.manual_seed(0)
     m = vit_no_classifier.ViT().to(dev).eval()
+    from b200vit.inference import GraphedForward
+    graphed = GraphedForward(m)
     _, ffwd = train_flops_per_image(197, 768, 12, 3072, 0, 768)
     with torch.inference_mode():
         for B in (1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024):
             X = torch.rand(B, 3, 224, 224, device=dev)
             ms = timed(lambda: m(X), 3, 10 if B <= 256 else 5)
             ips = B / ms * 1e3
-            print(json.dumps({"config": "C5 headless ViT-B/16 forward", "batch": B, "ms": round(ms, 3),
-                              "images_per_s": round(ips, 1), "tflops": round(ips * ffwd / 1e12, 1)}), flush=True)
+            rec = {"config": "C5 headless ViT-B/16 forward", "batch": B, "ms": round(ms, 3),
+                   "images_per_s": round(ips, 1), "tflops": round(ips * ffwd / 1e12, 1)}
+            if B <= 64:         # launch-bound range: the same forward replayed from a CUDA graph
+                msg = timed(lambda: graphed(X), 3, 20)
+                rec.update({"graphed_ms": round(msg, 3), "graphed_images_per_s": round(B / msg * 1e3, 1)})
+            print(json.dumps(rec), flush=True)
     del m
     torch.cuda.empty_cache()
 
