@@ -78,39 +78,64 @@ def gemm_shapes_per_step(batch, image=224, patch=16, layers=12, d=768, mlp=3072)
     ]
 
 
-def measure_gemm_roofline(batch, dev, peaks):
-    """Replay every GEMM launch shape of one step (real epilogues, dropout 0.1 where the step has it) and time each
-    with CUDA events on the launching stream."""
+def make_gemm_runner(name, op, epi, M, N, Kd, dev):
+    """Operands + a closure that launches one GEMM of the training step with its real epilogue (dropout 0.1 where
+    the step has it)."""
     from b200vit import kernels as K
+    if op == K.OP_NT:
+        A = torch.randn(M, Kd, device=dev).bfloat16(); B = torch.randn(N, Kd, device=dev).bfloat16(); lda, ldb = Kd, Kd
+    elif op == K.OP_NN:
+        A = torch.randn(M, Kd, device=dev).bfloat16(); B = torch.randn(Kd, N, device=dev).bfloat16(); lda, ldb = Kd, N
+    else:
+        A = torch.randn(Kd, M, device=dev).bfloat16(); B = torch.randn(Kd, N, device=dev).bfloat16(); lda, ldb = M, N
+    f32 = epi in (K.EPI_BIAS_RES, K.EPI_ACCUM, K.EPI_PATCH)
+    rows_out = M + M // 196 + 1 if epi == K.EPI_PATCH else M
+    C = torch.zeros(rows_out, N, device=dev, dtype=torch.float32 if f32 else torch.bfloat16)
+    C2 = torch.empty(M, N, device=dev, dtype=torch.bfloat16) if epi == K.EPI_BIAS_GELU else None
+    bias = torch.randn(N, device=dev) if op == K.OP_NT else None
+    aux, ldaux, period, p = None, 0, 0, 0.0
+    if epi == K.EPI_BIAS_RES:
+        aux, ldaux = torch.randn(M, N, device=dev), N
+    if epi == K.EPI_DGELU:
+        aux, ldaux = torch.randn(M, N, device=dev).bfloat16(), N
+    if epi == K.EPI_PATCH:
+        aux, ldaux, period = torch.randn(197, N, device=dev), N, 196
+    if name in ("fc1_fwd", "fc2_fwd", "fc2_dgrad", "patch_fwd"):
+        p = 0.1
+    split = K.split_k_for(M, N, Kd, dev) if epi == K.EPI_ACCUM else 1
+
+    def run():
+        K.gemm(op, epi, M, N, Kd, A, lda, B, ldb, C, N, C2=C2, ldc2=N, bias=bias, aux=aux, ldaux=ldaux,
+               dropout_p=p, seed=1, offset=2, row_period=period, split_k=split)
+    return run
+
+
+def gemm_traffic_per_launch(batch):
+    """Count-weighted mean DRAM bytes (read + write) per GEMM launch of one step, from the committed ncu --set full
+    capture (profiles/r01_gemm_traffic.json, written by tools/summarize_ncu.py); None when the file is absent or
+    was taken at another batch size."""
+    path = ROOT / "profiles" / "r01_gemm_traffic.json"
+    if not path.exists():
+        return None, None
+    rec = json.loads(path.read_text())
+    if rec.get("batch") != batch:
+        return None, None
+    tot, n = 0.0, 0
+    for name, *_rest, count in gemm_shapes_per_step(batch):
+        if name not in rec["dram_bytes"]:
+            return None, None
+        tot += rec["dram_bytes"][name] * count
+        n += count
+    return tot / n, rec.get("source")
+
+
+def measure_gemm_roofline(batch, dev, peaks):
+    """Replay every GEMM launch shape of one step and time each with CUDA events on the launching stream."""
     total_flops = 0.0
     total_ms = 0.0
     detail = {}
     for name, op, epi, M, N, Kd, count in gemm_shapes_per_step(batch):
-        if op == K.OP_NT:
-            A = torch.randn(M, Kd, device=dev).bfloat16(); B = torch.randn(N, Kd, device=dev).bfloat16(); lda, ldb = Kd, Kd
-        elif op == K.OP_NN:
-            A = torch.randn(M, Kd, device=dev).bfloat16(); B = torch.randn(Kd, N, device=dev).bfloat16(); lda, ldb = Kd, N
-        else:
-            A = torch.randn(Kd, M, device=dev).bfloat16(); B = torch.randn(Kd, N, device=dev).bfloat16(); lda, ldb = M, N
-        f32 = epi in (K.EPI_BIAS_RES, K.EPI_ACCUM, K.EPI_PATCH)
-        rows_out = M + M // 196 + 1 if epi == K.EPI_PATCH else M
-        C = torch.zeros(rows_out, N, device=dev, dtype=torch.float32 if f32 else torch.bfloat16)
-        C2 = torch.empty(M, N, device=dev, dtype=torch.bfloat16) if epi == K.EPI_BIAS_GELU else None
-        bias = torch.randn(N, device=dev) if op == K.OP_NT else None
-        aux, ldaux, period, p = None, 0, 0, 0.0
-        if epi == K.EPI_BIAS_RES:
-            aux, ldaux = torch.randn(M, N, device=dev), N
-        if epi == K.EPI_DGELU:
-            aux, ldaux = torch.randn(M, N, device=dev).bfloat16(), N
-        if epi == K.EPI_PATCH:
-            aux, ldaux, period = torch.randn(197, N, device=dev), N, 196
-        if name in ("fc1_fwd", "fc2_fwd", "fc2_dgrad", "patch_fwd"):
-            p = 0.1
-        split = K.split_k_for(M, N, Kd, dev) if epi == K.EPI_ACCUM else 1
-
-        def run():
-            K.gemm(op, epi, M, N, Kd, A, lda, B, ldb, C, N, C2=C2, ldc2=N, bias=bias, aux=aux, ldaux=ldaux,
-                   dropout_p=p, seed=1, offset=2, row_period=period, split_k=split)
+        run = make_gemm_runner(name, op, epi, M, N, Kd, dev)
         for _ in range(2):
             run()
         torch.cuda.synchronize()
@@ -126,12 +151,17 @@ def measure_gemm_roofline(batch, dev, peaks):
         detail[name] = {"us": round(ms * 1e3, 1), "tflops": round(fl / ms / 1e9, 1), "launches_per_step": count}
         total_flops += fl * count
         total_ms += ms * count
-        del A, B, C, C2, aux
+        del run
     achieved = total_flops / total_ms / 1e9
     peak = peaks.get("bf16_tflops_sustained") or 1400.0
+    traffic, traffic_src = gemm_traffic_per_launch(batch)
+    n_launch = sum(c for *_, c in gemm_shapes_per_step(batch))
     return {
         "bound": "tensor", "achieved": round(achieved, 1), "peak": peak, "unit": "TFLOP/s",
-        "frac": round(achieved / peak, 4), "traffic": None,
+        "frac": round(achieved / peak, 4), "traffic": None if traffic is None else round(traffic),
+        "traffic_unit": "DRAM bytes (read + write) per launch, mean over the step's %d GEMM launches" % n_launch,
+        "traffic_source": traffic_src,
+        "flops_per_launch": round(total_flops / n_launch), "us_per_launch": round(total_ms / n_launch * 1e3, 2),
         "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (of measured)" if "bf16_tflops_sustained" in peaks
         else "B200_PROFILING.md fallback 1.4 PFLOP/s sustained (of fallback)",
         "kernel": "gemm_tcgen05_kernel (all %d GEMM launches of one step, FLOP-weighted)" % sum(
