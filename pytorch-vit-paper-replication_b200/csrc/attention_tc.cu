@@ -107,7 +107,7 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
         __syncwarp();
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        {       // all 32 lanes run the loop (uniform operands); one elected lane issues each tcgen05 instruction
             const uint32_t idesc_s = make_idesc_bf16(ATC_BM, Nk, 0, 0);
             const uint32_t idesc_o = make_idesc_bf16(ATC_BM, 64, 0, 1);
             int it = 0;
@@ -123,20 +123,20 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
                     // S = Q_g K^T : A = Q rows [128 g, 128 g + 128) K-major, B = K [Nk x 64] K-major
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        umma_bf16<1>(tmem + g * 256, make_smem_desc_sw128(sQ + g * (ATC_BM * 128) + k * 32, 1024, 0),
+                        umma_bf16_ss_elect(tmem + g * 256, make_smem_desc_sw128(sQ + g * (ATC_BM * 128) + k * 32, 1024, 0),
                                      make_smem_desc_sw128(sK + k * 32, 1024, 0), idesc_s, k > 0 ? 1u : 0u);
-                    umma_commit(s_ready(g));
+                    umma_commit_elect(s_ready(g));
                 }
                 for (int g = 0; g < nt; ++g) {
                     mbar_wait(p_ready(g), hp);
                     tc_fence_after();
                     // O = P V : A = P in TMEM (bf16 pairs: 8 columns per 16 keys), B = V [Nk keys x 64] MN-major
                     for (int k = 0; k < Nk / 16; ++k)
-                        umma_bf16_ts(tmem + g * 256 + ATC_O_COL, tmem + g * 256 + packed_col(16 * k),
+                        umma_bf16_ts_elect(tmem + g * 256 + ATC_O_COL, tmem + g * 256 + packed_col(16 * k),
                                      make_smem_desc_sw128(sV + k * 2048, 1024, 0), idesc_o, k > 0 ? 1u : 0u);
-                    umma_commit(o_ready(g));
+                    umma_commit_elect(o_ready(g));
                 }
-                umma_commit(empty_bar(s));      // every MMA that reads this smem stage has retired
+                umma_commit_elect(empty_bar(s));      // every MMA that reads this smem stage has retired
             }
         }
         __syncwarp();
@@ -847,6 +847,338 @@ attention_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
 }
 
 // =============================================================================================
+// Backward, single-pass variant (T <= 256). The two kernels above build the probabilities twice per head (once with
+// keys on the TMEM lanes for dK/dV, once with queries on the lanes for dQ). Here they are built ONCE, keys on the
+// lanes: per 128-key tile t and 64-query chunk c
+//     S^T = K_t Q_c^T, dP^T = V_t dO_c^T  ->  P^T, dS^T (bf16, packed in place)  ->  dV_t += P^T dO_c, dK_t += dS^T Q_c
+// and dS^T is ALSO written to shared memory as bf16, one 128-byte row of 64 queries per key: that is exactly the
+// 128B-swizzled MN-major layout of an A operand with M = queries, so after two chunks (128 queries)
+//     dQ_m += dS[128 queries x keys of tile t] K_t
+// is one more UMMA chain, A from shared memory, accumulating over the key tiles in TMEM. All exponentials, the
+// dS math and the S / dP MMAs are done once instead of twice.
+// TMEM: [0,128) chunk accumulators of group 0 (S^T | dP^T), [128,256) of group 1, [256,320) dV_t, [320,384) dK_t,
+//       [384,448) dQ rows 0-127, [448,512) dQ rows 128-255.
+// Warps: 0 = TMA + statistics, 1 = MMA issue, 2-17 = two math groups (8 warps: thread <-> key row, two warps per
+// row splitting a chunk's 64 query columns); the groups alternate chunks. The Q/K/V/dO tiles of a head are staged once
+// (single stage: 4 tiles + 2 x 32 KB of dS leave no room for a second), statistics are double-buffered.
+// =============================================================================================
+constexpr int AT3_W = 64;
+
+__global__ void __launch_bounds__(ATC_THREADS, 1)
+attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
+                         const bf16* __restrict__ out, const bf16* __restrict__ dout, const float* __restrict__ lse,
+                         bf16* __restrict__ dqkv, int num_heads_total, int T, int Nk, int H, float scale_log2,
+                         float scale) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t tile_bytes = (uint32_t)Nk * 128u;
+    const uint32_t tile_stride = (tile_bytes + 1023u) & ~1023u;
+    const uint32_t sQ = smem_base, sK = sQ + tile_stride, sV = sK + tile_stride, sdO = sV + tile_stride;
+    const uint32_t ds_base = smem_base + 4 * tile_stride + ATB_TAIL_PAD;     // 2 buffers x [2 query blocks][128 keys][128 B]
+    const uint32_t stat_base = ds_base + 2u * 32768u;                        // 2 stages x (lse2 [Nk], delta*scale [Nk])
+    const uint32_t bar_base = stat_base + 2u * 2u * Nk * 4u;
+    const uint32_t full_bar = bar_base, head_empty = bar_base + 8u;
+    auto stat_bar = [&](int s) { return bar_base + 16u + 8u * s; };
+    auto s_ready = [&](int g) { return bar_base + 32u + 8u * g; };
+    auto p_ready = [&](int g) { return bar_base + 48u + 8u * g; };
+    auto ds_free = [&](int m) { return bar_base + 64u + 8u * m; };
+    const uint32_t kv_ready = bar_base + 80u, kv_free = bar_base + 88u, dq_ready = bar_base + 96u, dq_free = bar_base + 104u;
+    const uint32_t tmem_slot = bar_base + 112u;
+    uint8_t* gen = smem_raw - smem_u32(smem_raw);
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen + tmem_slot);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nt = (T + ATC_BM - 1) / ATC_BM;           // key tiles
+    const int nc = (Nk + AT3_W - 1) / AT3_W;            // query chunks
+    const int nsteps = nt * nc;
+    const int nm = (nc + 1) / 2;                        // 128-query dQ tiles
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmQKV);
+        prefetch_tmap(&tmDO);
+        mbar_init(full_bar, 1);
+        mbar_init(head_empty, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(stat_bar(i), 1);
+            mbar_init(s_ready(i), 1);
+            mbar_init(p_ready(i), 8);
+            mbar_init(ds_free(i), 1);
+        }
+        mbar_init(kv_ready, 1);
+        mbar_init(kv_free, 16);
+        mbar_init(dq_ready, 1);
+        mbar_init(dq_free, 16);
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc<1>(tmem_slot, 512);
+        tmem_relinquish<1>();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        // ===================== TMA producer + per-token statistics =====================
+        const float LOG2E = 1.4426950408889634f;
+        const long long os = (long long)H * 64;
+        auto stats = [&](int w, int stage) {
+            const int b = w / H, h = w % H;
+            float* sLse2 = reinterpret_cast<float*>(gen + stat_base + (uint32_t)stage * 2u * Nk * 4u);
+            float* sDelta = sLse2 + Nk;
+            const bf16* gO = out + (long long)b * T * os + (long long)h * 64;
+            const bf16* gdO = dout + (long long)b * T * os + (long long)h * 64;
+            const float* L = lse + (long long)w * T;
+            for (int t = lane; t < Nk; t += 32) {
+                float d = 0.f;
+                if (t < T) {
+                    const uint4* po = reinterpret_cast<const uint4*>(gO + (long long)t * os);
+                    const uint4* pd = reinterpret_cast<const uint4*>(gdO + (long long)t * os);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const uint4 a = __ldg(po + i), c = __ldg(pd + i);
+                        const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, cw[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const float2 fa = unpack_bf16(aw[k]), fc = unpack_bf16(cw[k]);
+                            d = fmaf(fa.x, fc.x, fmaf(fa.y, fc.y, d));
+                        }
+                    }
+                }
+                sDelta[t] = d * scale;
+                sLse2[t] = t < T ? L[t] * LOG2E : INFINITY;      // +inf: padded query columns get P = 0, dS = 0
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(stat_bar(stage));
+        };
+        if ((int)blockIdx.x < num_heads_total) stats(blockIdx.x, 0);
+        int it = 0;
+        for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
+            const int b = w / H, h = w % H;
+            if (lane == 0) {
+                mbar_wait(head_empty, (it & 1) ^ 1u);
+                mbar_arrive_expect_tx(full_bar, 4 * tile_bytes);
+                tma_load_4d(sQ, &tmQKV, full_bar, 0, 0, h, b);
+                tma_load_4d(sK, &tmQKV, full_bar, 0, 0, H + h, b);
+                tma_load_4d(sV, &tmQKV, full_bar, 0, 0, 2 * H + h, b);
+                tma_load_4d(sdO, &tmDO, full_bar, 0, 0, h, b);
+            }
+            __syncwarp();
+            // statistics of the NEXT head while this one computes (its stage was last read by head it-1, which is done:
+            // head_empty has been waited on above)
+            if (w + (int)gridDim.x < num_heads_total) stats(w + gridDim.x, (it + 1) & 1);
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer: all 32 lanes run the loop, one elected lane issues =====================
+        {
+            const uint32_t idesc2 = make_idesc_bf16(ATC_BM, 64, 0, 1);      // A from TMEM, B MN-major
+            const uint32_t idesc3 = make_idesc_bf16(ATC_BM, 64, 1, 1);      // A (dS) and B (K) both MN-major
+            uint32_t n_p[2] = {0, 0};
+            uint32_t n_tiles = 0;           // key tiles whose dV/dK MMAs have started so far (all heads)
+            uint32_t S0 = 0;                // global step counter at the start of the head
+            int it = 0;
+            for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it, S0 += nsteps) {
+                mbar_wait(full_bar, it & 1);
+                tc_fence_after();
+                auto width = [&](int c) { return min(AT3_W, Nk - c * AT3_W); };
+                auto issue_1 = [&](int s) {        // S^T and dP^T of step s into the chunk accumulators of its group
+                    const int t = s / nc, c = s % nc, g = (S0 + s) & 1;
+                    const uint32_t acc = tmem + g * 128;
+                    const uint32_t xo = (uint32_t)t * (ATC_BM * 128), yo = (uint32_t)c * (AT3_W * 128);
+                    const uint32_t idesc1 = make_idesc_bf16(ATC_BM, width(c), 0, 0);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        umma_bf16_ss_elect(acc, make_smem_desc_sw128(sK + xo + k * 32, 1024, 0),
+                                     make_smem_desc_sw128(sQ + yo + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
+                        umma_bf16_ss_elect(acc + 64, make_smem_desc_sw128(sV + xo + k * 32, 1024, 0),
+                                     make_smem_desc_sw128(sdO + yo + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
+                    }
+                    umma_commit_elect(s_ready(g));
+                };
+                issue_1(0);
+                if (nsteps > 1) issue_1(1);
+                for (int s = 0; s < nsteps; ++s) {
+                    const int t = s / nc, c = s % nc, g = (S0 + s) & 1;
+                    const uint32_t acc = tmem + g * 128;
+                    mbar_wait(p_ready(g), n_p[g] & 1u);
+                    ++n_p[g];
+                    if (c == 0) {           // the previous tile's dV / dK must have been read out
+                        mbar_wait(kv_free, (n_tiles & 1u) ^ 1u);
+                        ++n_tiles;
+                    }
+                    tc_fence_after();
+                    const uint32_t yo = (uint32_t)c * (AT3_W * 128);
+                    const int ksteps = width(c) / 16;
+                    for (int k = 0; k < ksteps; ++k) {
+                        const uint32_t acol = k < 2 ? 8 * k : 32 + 8 * (k - 2);
+                        const uint32_t accf = (c > 0 || k > 0) ? 1u : 0u;
+                        umma_bf16_ts_elect(tmem + 256, acc + acol, make_smem_desc_sw128(sdO + yo + k * 2048, 1024, 0), idesc2, accf);
+                        umma_bf16_ts_elect(tmem + 320, acc + 64 + acol, make_smem_desc_sw128(sQ + yo + k * 2048, 1024, 0), idesc2, accf);
+                    }
+                    if ((c & 1) || c == nc - 1) {
+                        // both chunks of query tile m are in shared memory: dQ_m (+)= dS[m] K_t over this tile's keys
+                        const int m = c >> 1;
+                        if (t == 0 && m == 0) {         // the previous head's dQ must have been read out
+                            mbar_wait(dq_free, (it & 1) ^ 1u);
+                            tc_fence_after();
+                        }
+                        const int keys = min(ATC_BM, Nk - t * ATC_BM);
+                        const uint32_t sA = ds_base + (uint32_t)m * 32768u, sB = sK + (uint32_t)t * (ATC_BM * 128);
+                        for (int k = 0; k < keys / 16; ++k)
+                            umma_bf16_ss_elect(tmem + 384 + 64 * m, make_smem_desc_sw128(sA + k * 2048, 1024, 16384),
+                                         make_smem_desc_sw128(sB + k * 2048, 1024, 0), idesc3, (t > 0 || k > 0) ? 1u : 0u);
+                        umma_commit_elect(ds_free(m));
+                    }
+                    if (c == nc - 1) umma_commit_elect(kv_ready);
+                    if (s + 2 < nsteps) issue_1(s + 2);
+                }
+                umma_commit_elect(dq_ready);
+                umma_commit_elect(head_empty);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===================== math + read-out groups =====================
+        const int sw = warp - 2;
+        const int g = sw >> 3;
+        const int half = (sw >> 2) & 1;
+        const int quarter = warp & 3;
+        const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
+        const uint32_t acc = tmem + g * 128 + lane_sel;
+        const int r_in_tile = quarter * 32 + lane;
+        const long long rs = 3LL * H * 64;
+        const int cb = half * 32;
+        uint32_t n_s = 0, n_kv = 0;
+        uint32_t S0 = 0;
+        int it = 0;
+        for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it, S0 += nsteps) {
+            const int b = w / H, h = w % H;
+            const float* sL = reinterpret_cast<const float*>(gen + stat_base + (uint32_t)(it & 1) * 2u * Nk * 4u);
+            const float* sD = sL + Nk;
+            mbar_wait(stat_bar(it & 1), (it >> 1) & 1);
+            // dV (group 0) or dK (group 1) of key tile t: this warp converts 32 of the 64 columns of its 32 rows
+            auto read_out_kv = [&](int t) {
+                mbar_wait(kv_ready, n_kv & 1u);
+                ++n_kv;
+                tc_fence_after();
+                uint32_t v[32];
+                tmem_ld_32x32(tmem + lane_sel + 256 + 64 * g + half * 32, v);
+                tmem_ld_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(kv_free);
+                const int row = t * ATC_BM + r_in_tile;
+                if (row < T) {
+                    bf16* dst = dqkv + ((long long)b * T + row) * rs + (long long)(g == 0 ? 2 * H + h : H + h) * 64 + half * 32;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        uint4 q;
+                        q.x = pack_bf16(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1]));
+                        q.y = pack_bf16(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3]));
+                        q.z = pack_bf16(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5]));
+                        q.w = pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7]));
+                        reinterpret_cast<uint4*>(dst)[i] = q;
+                    }
+                }
+            };
+            int pending_tile = -1;          // tile whose dV/dK this group still has to read out
+            for (int s = 0; s < nsteps; ++s) {
+                const int t = s / nc, c = s % nc;
+                if (((S0 + s) & 1) != (uint32_t)g) {
+                    // the other group's step; if it is the last chunk of a tile, this group reads its half of the tile's
+                    // gradients after its own NEXT step (or at the end of the head)
+                    if (c == nc - 1) pending_tile = t;
+                    continue;
+                }
+                const int m = c >> 1, blk = c & 1;
+                const int W = min(AT3_W, Nk - c * AT3_W);
+                const int ce = min(cb + 32, W);
+                mbar_wait(s_ready(g), n_s & 1u);
+                ++n_s;
+                if (t > 0 || it > 0) {      // the dQ MMA that read this dS buffer last (previous tile / head) has retired
+                    const uint32_t uses = (uint32_t)it * nt + t;       // dQ MMAs issued on buffer m before this tile
+                    mbar_wait(ds_free(m), (uses - 1) & 1u);
+                }
+                tc_fence_after();
+                uint8_t* ds_row = gen + ds_base + (uint32_t)m * 32768u + (uint32_t)blk * 16384u + (uint32_t)r_in_tile * 128u;
+                for (int cc = cb; cc < ce; cc += 16) {
+                    uint32_t sv[16], dp[16];
+                    tmem_ld_32x16(acc + cc, sv);
+                    tmem_ld_32x16(acc + 64 + cc, dp);
+                    tmem_ld_wait();
+                    float p[16], ds[16];
+#pragma unroll
+                    for (int i4 = 0; i4 < 4; ++i4) {
+                        const float4 a = reinterpret_cast<const float4*>(sL + c * AT3_W + cc)[i4];
+                        const float4 d = reinterpret_cast<const float4*>(sD + c * AT3_W + cc)[i4];
+                        const float l2[4] = {a.x, a.y, a.z, a.w}, dl[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const int i = 4 * i4 + k;
+                            p[i] = fast_ex2(fmaf(__uint_as_float(sv[i]), scale_log2, -l2[k]));
+                            ds[i] = p[i] * fmaf(__uint_as_float(dp[i]), scale, -dl[k]);
+                        }
+                    }
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) pk[i] = pack_bf16(p[2 * i], p[2 * i + 1]);
+                    tmem_st_32x8(acc + cb + ((cc - cb) >> 1), pk);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) pk[i] = pack_bf16(ds[2 * i], ds[2 * i + 1]);
+                    tmem_st_32x8(acc + 64 + cb + ((cc - cb) >> 1), pk);
+                    // the same 16 dS values as two 16-byte pieces of this key's row of the MN-major dS tile
+                    const int j = cc >> 3;
+                    *reinterpret_cast<uint4*>(ds_row + (((j) ^ (r_in_tile & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    *reinterpret_cast<uint4*>(ds_row + (((j + 1) ^ (r_in_tile & 7)) << 4)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                }
+                fence_proxy_async_smem();       // the dS rows are read by the tensor core (async proxy)
+                tmem_st_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(p_ready(g));
+                if (pending_tile >= 0) {
+                    read_out_kv(pending_tile);
+                    pending_tile = -1;
+                }
+                if (c == nc - 1) read_out_kv(t);    // own last chunk of the tile: its MMAs follow immediately
+            }
+            if (pending_tile >= 0) read_out_kv(pending_tile);
+            // dQ: group m converts query rows [128 m, 128 m + 128)
+            mbar_wait(dq_ready, it & 1);
+            tc_fence_after();
+            uint32_t v[32];
+            if (g < nm) {
+                tmem_ld_32x32(tmem + lane_sel + 384 + 64 * g + half * 32, v);
+                tmem_ld_wait();
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(dq_free);
+            const int row = g * ATC_BM + r_in_tile;
+            if (g < nm && row < T) {
+                bf16* dst = dqkv + ((long long)b * T + row) * rs + (long long)h * 64 + half * 32;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    uint4 q;
+                    q.x = pack_bf16(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1]));
+                    q.y = pack_bf16(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3]));
+                    q.z = pack_bf16(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5]));
+                    q.w = pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7]));
+                    reinterpret_cast<uint4*>(dst)[i] = q;
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<1>(tmem, 512);
+    }
+}
+
+// =============================================================================================
 // Forward for long sequences (T > 256, e.g. the 577 tokens of 384x384 images): flash-style streaming over blocks of
 // 128 keys with an online softmax. A work item is (batch, head, pair of 128-query tiles); the pair shares one
 // stream of K/V blocks (4-deep TMA ring), tile g of the pair lives in TMEM slot g:
@@ -938,7 +1270,7 @@ attention_fwd_long_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
         __syncwarp();
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        {       // all 32 lanes run the loop (uniform operands); one elected lane issues each tcgen05 instruction
             const uint32_t idesc_o = make_idesc_bf16(ATC_BM, 64, 0, 1);
             uint32_t n_p[2] = {0, 0}, n_free[2] = {0, 0};
             int it = 0;
@@ -956,9 +1288,9 @@ attention_fwd_long_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
                     const uint32_t idesc_s = make_idesc_bf16(ATC_BM, keys_in(j), 0, 0);
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        umma_bf16<1>(tmem + g * 256, make_smem_desc_sw128(sQ + g * (ATC_BM * 128) + k * 32, 1024, 0),
+                        umma_bf16_ss_elect(tmem + g * 256, make_smem_desc_sw128(sQ + g * (ATC_BM * 128) + k * 32, 1024, 0),
                                      make_smem_desc_sw128(sK + k * 32, 1024, 0), idesc_s, k > 0 ? 1u : 0u);
-                    umma_commit(s_ready(g));
+                    umma_commit_elect(s_ready(g));
                 };
                 mbar_wait(kv_full(kvn % ATL_STAGES), (kvn / ATL_STAGES) & 1);
                 tc_fence_after();
@@ -977,10 +1309,10 @@ attention_fwd_long_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
                         tc_fence_after();
                         // O_g (+)= P V_j : A = P in TMEM (8 packed columns per 16 keys), B = V_j [keys x 64] MN-major
                         for (int k = 0; k < ksteps; ++k)
-                            umma_bf16_ts(tmem + g * 256 + ATC_O_COL, tmem + g * 256 + (k < 4 ? 8 * k : 64 + 8 * (k - 4)),
+                            umma_bf16_ts_elect(tmem + g * 256 + ATC_O_COL, tmem + g * 256 + (k < 4 ? 8 * k : 64 + 8 * (k - 4)),
                                          make_smem_desc_sw128(sV + k * 2048, 1024, 0), idesc_o, (j > 0 || k > 0) ? 1u : 0u);
-                        umma_commit(o_ready(g));
-                        if (g == nact - 1) umma_commit(kv_empty((kvn + j) % ATL_STAGES));   // both tiles are done with block j
+                        umma_commit_elect(o_ready(g));
+                        if (g == nact - 1) umma_commit_elect(kv_empty((kvn + j) % ATL_STAGES));   // both tiles are done with block j
                         if (j + 1 < nb) {
                             if (g == 0) {
                                 mbar_wait(kv_full((kvn + j + 1) % ATL_STAGES), ((kvn + j + 1) / ATL_STAGES) & 1);
@@ -990,7 +1322,7 @@ attention_fwd_long_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
                         }
                     }
                 }
-                umma_commit(q_empty(qs));
+                umma_commit_elect(q_empty(qs));
                 kvn += nb;
             }
         }
@@ -1268,7 +1600,7 @@ attention_bwd_long_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_
         __syncwarp();
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        {       // all 32 lanes run the loop (uniform operands); one elected lane issues each tcgen05 instruction
             const uint32_t idesc2 = make_idesc_bf16(ATC_BM, 64, 0, 1);
             uint32_t n_p[2] = {0, 0}, n_free[2] = {0, 0};
             int it = 0;
@@ -1289,12 +1621,12 @@ attention_bwd_long_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_
                     const uint32_t slot = tmem + g * 256, xo = g * (ATC_BM * 128);
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
-                        umma_bf16<1>(slot, make_smem_desc_sw128(sX + xo + k * 32, 1024, 0),
+                        umma_bf16_ss_elect(slot, make_smem_desc_sw128(sX + xo + k * 32, 1024, 0),
                                      make_smem_desc_sw128(sY + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
-                        umma_bf16<1>(slot + 64, make_smem_desc_sw128(sX2 + xo + k * 32, 1024, 0),
+                        umma_bf16_ss_elect(slot + 64, make_smem_desc_sw128(sX2 + xo + k * 32, 1024, 0),
                                      make_smem_desc_sw128(sY2 + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
                     }
-                    umma_commit(s_ready(g));
+                    umma_commit_elect(s_ready(g));
                 };
                 mbar_wait(ch_full(chn % ATLB_STAGES), (chn / ATLB_STAGES) & 1);
                 tc_fence_after();
@@ -1315,12 +1647,12 @@ attention_bwd_long_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_
                             const uint32_t acol = k < 2 ? 8 * k : 32 + 8 * (k - 2);
                             const uint32_t acc = (c > 0 || k > 0) ? 1u : 0u;
                             if (kv_item)                  // dV_t += P^T dO_c
-                                umma_bf16_ts(slot + 128, slot + acol, make_smem_desc_sw128(sY2 + k * 2048, 1024, 0), idesc2, acc);
+                                umma_bf16_ts_elect(slot + 128, slot + acol, make_smem_desc_sw128(sY2 + k * 2048, 1024, 0), idesc2, acc);
                             // dK_t += dS^T Q_c   or   dQ_t += dS K_c
-                            umma_bf16_ts(slot + 192, slot + 64 + acol, make_smem_desc_sw128(sY + k * 2048, 1024, 0), idesc2, acc);
+                            umma_bf16_ts_elect(slot + 192, slot + 64 + acol, make_smem_desc_sw128(sY + k * 2048, 1024, 0), idesc2, acc);
                         }
-                        if (c == nc - 1) umma_commit(o_ready(g));
-                        if (g == nact - 1) umma_commit(ch_empty((chn + c) % ATLB_STAGES));
+                        if (c == nc - 1) umma_commit_elect(o_ready(g));
+                        if (g == nact - 1) umma_commit_elect(ch_empty((chn + c) % ATLB_STAGES));
                         if (c + 1 < nc) {
                             if (g == 0) {
                                 mbar_wait(ch_full((chn + c + 1) % ATLB_STAGES), ((chn + c + 1) / ATLB_STAGES) & 1);
@@ -1330,7 +1662,7 @@ attention_bwd_long_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_
                         }
                     }
                 }
-                umma_commit(x_empty(xs));
+                umma_commit_elect(x_empty(xs));
                 chn += nc;
             }
         }
@@ -1568,16 +1900,24 @@ int attention_bwd_tc_launch(const bf16* qkv, const bf16* out, const bf16* dout, 
     rc = make_tmap_rows64(&td, dout, batch, tokens, heads, Nk);
     if (rc) return rc;
     const size_t tile_stride = ((size_t)Nk * 128 + 1023) & ~(size_t)1023;
-    const size_t smem = 1024 + 2 * 4 * tile_stride + ATB_TAIL_PAD + 2 * 2 * (size_t)Nk * 4 + 128;
-    B200_CHECK_ARG(smem <= 232448, "attention_bwd: %d tokens need %zu bytes of shared memory", tokens, smem);
-    B200_CUDA(cudaFuncSetAttribute(attention_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int total = batch * heads;
     const int grid = total < sm_count() ? total : sm_count();
-    static int variant = -1;       // B200VIT_ATTN_BWD=1 forces the unpipelined kernel (A/B measurements)
+    static int variant = -1;       // B200VIT_ATTN_BWD=1 / 2 force the two-pass kernels (A/B measurements)
     if (variant < 0) {
         const char* e = getenv("B200VIT_ATTN_BWD");
         variant = e ? atoi(e) : 0;
     }
+    if (variant == 0) {
+        const size_t smem3 = 1024 + 4 * tile_stride + ATB_TAIL_PAD + 2 * 32768 + 2 * 2 * (size_t)Nk * 4 + 128;
+        B200_CUDA(cudaFuncSetAttribute(attention_bwd_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
+        attention_bwd_tc3_kernel<<<grid, ATC_THREADS, smem3, stream>>>(tq, td, out, dout, lse, dqkv, total, tokens, Nk, heads,
+                                                                     scale * 1.4426950408889634f, scale);
+        B200_LAUNCH_CHECK();
+        return 0;
+    }
+    const size_t smem = 1024 + 2 * 4 * tile_stride + ATB_TAIL_PAD + 2 * 2 * (size_t)Nk * 4 + 128;
+    B200_CHECK_ARG(smem <= 232448, "attention_bwd: %d tokens need %zu bytes of shared memory", tokens, smem);
+    B200_CUDA(cudaFuncSetAttribute(attention_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (((Nk / 2 + 15) & ~15) <= ATP_MAX_W && variant != 1) {
         B200_CUDA(cudaFuncSetAttribute(attention_bwd_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attention_bwd_tc2_kernel<<<grid, ATP_THREADS, smem, stream>>>(tq, td, out, dout, lse, dqkv, total, tokens, Nk,

@@ -185,7 +185,8 @@ def test_layernorm_fwd_bwd(rows, D):
     assert rel_err(gout, xr.grad) < 1e-4
 
 
-@pytest.mark.parametrize("Bn,T,H", [(2, 197, 12), (1, 64, 2), (3, 50, 4), (1, 577, 16), (2, 257, 3), (1, 1000, 2), (2, 384, 5), (1, 640, 1)])
+@pytest.mark.parametrize("Bn,T,H", [(2, 197, 12), (1, 64, 2), (3, 50, 4), (2, 128, 3), (2, 129, 2), (1, 256, 2), (2, 240, 1), (7, 16, 1),
+                                    (1, 577, 16), (2, 257, 3), (1, 1000, 2), (2, 384, 5), (1, 640, 1)])
 def test_attention_fwd_bwd(Bn, T, H):
     g = torch.Generator().manual_seed(8)
     hd = 64
