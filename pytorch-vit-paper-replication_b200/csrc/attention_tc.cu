@@ -863,8 +863,9 @@ attention_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
 // (single stage: 4 tiles + 2 x 32 KB of dS leave no room for a second), statistics are double-buffered.
 // =============================================================================================
 constexpr int AT3_W = 64;
+constexpr int AT3_THREADS = ATC_THREADS + 64;     // + two statistics warps (registers are allotted per 4 warps anyway)
 
-__global__ void __launch_bounds__(ATC_THREADS, 1)
+__global__ void __launch_bounds__(AT3_THREADS, 1)
 attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                          const bf16* __restrict__ out, const bf16* __restrict__ dout, const float* __restrict__ lse,
                          bf16* __restrict__ dqkv, int num_heads_total, int T, int Nk, int H, float scale_log2,
@@ -883,7 +884,8 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
     auto p_ready = [&](int g) { return bar_base + 48u + 8u * g; };
     auto ds_free = [&](int m) { return bar_base + 64u + 8u * m; };
     const uint32_t kv_ready = bar_base + 80u, kv_free = bar_base + 88u, dq_ready = bar_base + 96u, dq_free = bar_base + 104u;
-    const uint32_t tmem_slot = bar_base + 112u;
+    auto stat_free = [&](int s) { return bar_base + 112u + 8u * s; };
+    const uint32_t tmem_slot = bar_base + 128u;
     uint8_t* gen = smem_raw - smem_u32(smem_raw);
     uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen + tmem_slot);
 
@@ -899,7 +901,8 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
         mbar_init(full_bar, 1);
         mbar_init(head_empty, 1);
         for (int i = 0; i < 2; ++i) {
-            mbar_init(stat_bar(i), 1);
+            mbar_init(stat_bar(i), 2);
+            mbar_init(stat_free(i), 1);
             mbar_init(s_ready(i), 1);
             mbar_init(p_ready(i), 8);
             mbar_init(ds_free(i), 1);
@@ -920,17 +923,39 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
     const uint32_t tmem = *tmem_slot_ptr;
 
     if (warp == 0) {
-        // ===================== TMA producer + per-token statistics =====================
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int it = 0;
+            for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
+                const int b = w / H, h = w % H;
+                mbar_wait(head_empty, (it & 1) ^ 1u);
+                mbar_arrive_expect_tx(full_bar, 4 * tile_bytes);
+                tma_load_4d(sQ, &tmQKV, full_bar, 0, 0, h, b);
+                tma_load_4d(sK, &tmQKV, full_bar, 0, 0, H + h, b);
+                tma_load_4d(sV, &tmQKV, full_bar, 0, 0, 2 * H + h, b);
+                tma_load_4d(sdO, &tmDO, full_bar, 0, 0, h, b);
+            }
+        }
+        __syncwarp();
+    } else if (warp >= 18) {
+        // ===================== per-token statistics, one head ahead (two warps, half of the tokens each) ==========
         const float LOG2E = 1.4426950408889634f;
         const long long os = (long long)H * 64;
-        auto stats = [&](int w, int stage) {
+        const int part = warp - 18;
+        const int half_rows = ((Nk / 2) + 15) & ~15;
+        const int t_begin = part == 0 ? 0 : half_rows, t_end = part == 0 ? half_rows : Nk;
+        int it = 0;
+        for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
+            const int stage = it & 1;
             const int b = w / H, h = w % H;
+            if (lane == 0) mbar_wait(stat_free(stage), ((it >> 1) & 1) ^ 1u);      // head it-2 no longer reads this stage
+            __syncwarp();
             float* sLse2 = reinterpret_cast<float*>(gen + stat_base + (uint32_t)stage * 2u * Nk * 4u);
             float* sDelta = sLse2 + Nk;
             const bf16* gO = out + (long long)b * T * os + (long long)h * 64;
             const bf16* gdO = dout + (long long)b * T * os + (long long)h * 64;
             const float* L = lse + (long long)w * T;
-            for (int t = lane; t < Nk; t += 32) {
+            for (int t = t_begin + lane; t < t_end; t += 32) {
                 float d = 0.f;
                 if (t < T) {
                     const uint4* po = reinterpret_cast<const uint4*>(gO + (long long)t * os);
@@ -951,23 +976,6 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(stat_bar(stage));
-        };
-        if ((int)blockIdx.x < num_heads_total) stats(blockIdx.x, 0);
-        int it = 0;
-        for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
-            const int b = w / H, h = w % H;
-            if (lane == 0) {
-                mbar_wait(head_empty, (it & 1) ^ 1u);
-                mbar_arrive_expect_tx(full_bar, 4 * tile_bytes);
-                tma_load_4d(sQ, &tmQKV, full_bar, 0, 0, h, b);
-                tma_load_4d(sK, &tmQKV, full_bar, 0, 0, H + h, b);
-                tma_load_4d(sV, &tmQKV, full_bar, 0, 0, 2 * H + h, b);
-                tma_load_4d(sdO, &tmDO, full_bar, 0, 0, h, b);
-            }
-            __syncwarp();
-            // statistics of the NEXT head while this one computes (its stage was last read by head it-1, which is done:
-            // head_empty has been waited on above)
-            if (w + (int)gridDim.x < num_heads_total) stats(w + gridDim.x, (it + 1) & 1);
         }
     } else if (warp == 1) {
         // ===================== MMA issuer: all 32 lanes run the loop, one elected lane issues =====================
@@ -1035,6 +1043,7 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
                 }
                 umma_commit_elect(dq_ready);
                 umma_commit_elect(head_empty);
+                umma_commit_elect(stat_free(it & 1));
             }
         }
         __syncwarp();
@@ -1910,7 +1919,7 @@ int attention_bwd_tc_launch(const bf16* qkv, const bf16* out, const bf16* dout, 
     if (variant == 0) {
         const size_t smem3 = 1024 + 4 * tile_stride + ATB_TAIL_PAD + 2 * 32768 + 2 * 2 * (size_t)Nk * 4 + 128;
         B200_CUDA(cudaFuncSetAttribute(attention_bwd_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
-        attention_bwd_tc3_kernel<<<grid, ATC_THREADS, smem3, stream>>>(tq, td, out, dout, lse, dqkv, total, tokens, Nk, heads,
+        attention_bwd_tc3_kernel<<<grid, AT3_THREADS, smem3, stream>>>(tq, td, out, dout, lse, dqkv, total, tokens, Nk, heads,
                                                                      scale * 1.4426950408889634f, scale);
         B200_LAUNCH_CHECK();
         return 0;

@@ -513,8 +513,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
         __syncwarp();
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
+        // ===================== MMA issuer: all 32 lanes run the loop, one elected lane issues =====================
+        {
             constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
             // K-major:  8-row groups 1024 B apart (SBO), one 128B atom along K (LBO unused).
             // MN-major: 8-k-row groups 1024 B apart (SBO), 64-wide MN atoms BK*128 B apart (LBO).
@@ -540,10 +540,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     for (int k = 0; k < BK / UMMA_K; ++k) {
                         const uint64_t da = make_smem_desc_sw128(sa + k * a_kstep, 1024, a_lbo);
                         const uint64_t db = make_smem_desc_sw128(sb + k * b_kstep, 1024, b_lbo);
-                        umma_bf16<1>(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        umma_bf16_ss_elect(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
                     }
-                    umma_commit(empty_bar(stage));          // frees the smem stage when the MMAs retire
-                    if (kb == kb1 - 1) umma_commit(tfull_bar(acc));  // accumulator ready
+                    umma_commit_elect(empty_bar(stage));          // frees the smem stage when the MMAs retire
+                    if (kb == kb1 - 1) umma_commit_elect(tfull_bar(acc));  // accumulator ready
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -695,8 +695,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         }
         __syncwarp();
     } else if (warp == 1) {
-        // ===================== MMA issuer (leader CTA only) =====================
-        if (lane == 0 && leader) {
+        // ===================== MMA issuer (leader CTA only): all 32 lanes run the loop, one elected lane issues ==========
+        if (leader) {
             constexpr uint32_t idesc = make_idesc_bf16(2 * BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
             constexpr uint32_t a_lbo = A_MN ? BK * 128 : 0, b_lbo = B_MN ? BK * 128 : 0;
             constexpr uint32_t a_kstep = A_MN ? UMMA_K * 128 : UMMA_K * 2;
@@ -720,10 +720,10 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                     for (int k = 0; k < BK / UMMA_K; ++k) {
                         const uint64_t da = make_smem_desc_sw128(sa + k * a_kstep, 1024, a_lbo);
                         const uint64_t db = make_smem_desc_sw128(sb + k * b_kstep, 1024, b_lbo);
-                        umma_bf16<2>(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+                        umma_bf16_ss_2sm_elect(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
                     }
-                    umma_commit_2sm(empty_bar(stage), 0x3);                      // frees the stage in BOTH CTAs
-                    if (kb == kb1 - 1) umma_commit_2sm(tfull_bar(acc), 0x3);     // accumulator ready in BOTH CTAs
+                    umma_commit_2sm_elect(empty_bar(stage), 0x3);                      // frees the stage in BOTH CTAs
+                    if (kb == kb1 - 1) umma_commit_2sm_elect(tfull_bar(acc), 0x3);     // accumulator ready in BOTH CTAs
                     if (++stage == STAGES2) { stage = 0; phase ^= 1u; }
                 }
             }
