@@ -44,7 +44,10 @@ const char* b200vit_last_error(void);
  *                operand the backward epilogue 3 multiplies by (skipped if C == NULL)    (models/vit.py:119-122)
  *   2 BIAS_RES   C f32 = dropout(acc + bias) + aux_f32[m,n]  (aux NULL -> no residual)
  *                                                              (models/vit.py:123-125 and the residual adds :167-168)
- *   3 DGELU      C bf16 = acc * aux_bf16[m,n], aux = the C output of epilogue 1      (backward of GELU + Dropout)
+ *   3 DGELU      C bf16 = acc * aux_bf16[m,n], aux = the C output of epilogue 1      (backward of GELU + Dropout);
+ *                if `bias` is non-NULL it is an OUTPUT here: the column sums of C (the bias gradient of the Linear in
+ *                front of the GELU, reference autograd of nn.Linear vit.py:119) are ADDED to bias[0..N) with fp32
+ *                atomics -- the caller zeroes it first
  *   4 ACCUM      C f32 += acc, atomically; the only epilogue that allows split_k > 1 (weight gradients)
  *   5 F32        C f32 = acc (+ bias)
  *   6 PATCH      C f32[m + m/row_period + 1, n] = dropout(acc + bias[n] + aux_f32[(m % row_period) + 1, n]):

@@ -226,9 +226,9 @@ def _mlp_backward(g, saved, drop, ln_w, w1_16, w2_16, has_residual, want_bf16_ou
     dw2 = _zeros((d, m), x2d)
     K.gemm(K.OP_TN, K.EPI_ACCUM, d, m, r, g16, d, h, m, dw2, m, split_k=K.split_k_for(d, m, r, dev))
     da = _empty((r, m), torch.bfloat16, x2d)
-    K.gemm(K.OP_NN, K.EPI_DGELU, r, m, d, g16, d, w2_16, m, da, m, aux=a, ldaux=m)   # a = mask * gelu'(pre-activation)
-    db1 = _empty((m,), torch.float32, x2d)
-    K.colsum_bf16(da, m, db1, r, m)
+    db1 = _zeros((m,), x2d)
+    # a = mask * gelu'(pre-activation); the epilogue also accumulates the fc1 bias gradient (column sums of da) into db1
+    K.gemm(K.OP_NN, K.EPI_DGELU, r, m, d, g16, d, w2_16, m, da, m, bias=db1, aux=a, ldaux=m)
     dw1 = _zeros((m, d), x2d)
     K.gemm(K.OP_TN, K.EPI_ACCUM, m, d, r, da, m, ln, d, dw1, d, split_k=K.split_k_for(m, d, r, dev))
     dln = g16  # reuse: g16 is dead after the two GEMMs above (same shape / dtype)

@@ -107,6 +107,23 @@ __device__ __forceinline__ float gelu_exact_grad(float x) {
     return fmaf(x * 0.3989422804014327f, e, cdf);  // cdf + x pdf
 }
 
+// Column sums of a 32 x 32 block held one ROW per lane (v[j] = element (row = lane, column = j)): returns, in lane
+// j, the sum over the 32 rows of column j. Butterfly transpose-reduce: at every stage a lane keeps one half of its
+// columns and sends the other half to its partner (31 shuffles in total); v is destroyed.
+__device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        const bool upper = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < off; ++i) {
+            const float send = upper ? v[i] : v[i + off];
+            const float keep = upper ? v[i + off] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+    }
+    return v[0];
+}
+
 // ---------------------------------------------------------------------------------------------
 // Counter-based dropout mask. Element e of a tensor belongs to block e/8, lane e%8; a block draws 4x32 random
 // bits = eight 16-bit lanes from a 32-bit avalanche hash of (counter ^ key), where key is derived on the host

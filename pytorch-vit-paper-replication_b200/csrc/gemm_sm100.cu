@@ -418,6 +418,17 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
         __syncwarp();
         store_b16_tile(reinterpret_cast<bf16*>(p.C), p.ldc);
         __syncwarp();
+        if (p.bias != nullptr) {
+            // optional fused bias gradient of the layer in front of the GELU: column sums of this tile's rows are
+            // added to bias[] (an OUTPUT for this epilogue; the caller zeroes it), sparing a separate pass over C
+            if (row >= p.M) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = 0.f;
+            }
+            const float cs = warp_colsum32(v, lane);
+            if (col0 + lane < p.N)
+                asm volatile("red.global.add.f32 [%0], %1;" ::"l"(const_cast<float*>(p.bias) + col0 + lane), "f"(cs) : "memory");
+        }
     } else if (EPI == EPI_ACCUM) {
         put_row_f32(v);
         __syncwarp();

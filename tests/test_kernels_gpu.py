@@ -80,6 +80,12 @@ def test_gemm_gelu_and_dgelu():
     out = torch.empty((M, N), dtype=torch.bfloat16, device=dev())
     K.gemm(K.OP_NN, K.EPI_DGELU, M, N, Kd, G, Kd, W, N, out, N, aux=gd, ldaux=N)
     assert rel_err(out, (G.float() @ W.float()) * a_ref.grad) < 8e-3
+    # ... and, optionally, the column sums of the same product (the fc1 bias gradient) accumulated into `bias`
+    out2 = torch.empty_like(out)
+    colsum = torch.full((N,), 1.0, dtype=torch.float32, device=dev())       # accumulates on top of what is there
+    K.gemm(K.OP_NN, K.EPI_DGELU, M, N, Kd, G, Kd, W, N, out2, N, bias=colsum, aux=gd, ldaux=N)
+    assert torch.equal(out2, out)
+    assert rel_err(colsum - 1.0, ((G.float() @ W.float()) * gd.float()).sum(0)) < 2e-3
     # with dropout: hidden and saved derivative carry the SAME mask, scaled by 1/(1-p); mask == dropout_cast's
     p = 0.25
     gd2, h2 = torch.empty_like(gd), torch.empty_like(h)
