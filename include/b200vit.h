@@ -124,6 +124,14 @@ int b200vit_attention_bwd(const void* qkv_bf16, const void* out_bf16, const void
                           float* delta, void* dqkv_bf16, int batch, int tokens, int heads, int head_dim, float scale,
                           void* stream);
 
+/* Same, and additionally dbias f32 [3 * H * 64] = column sums of dqkv over all B*T rows: the gradient of
+ * nn.MultiheadAttention.in_proj_bias (models/vit.py:86-90; torch adds the packed bias in F.linear, so its gradient
+ * is the row sum of the packed projection's gradient). dbias is overwritten. For tokens <= 256 the sums come out of
+ * the backward kernel itself (no second pass over dqkv); longer sequences run a column-sum pass afterwards. */
+int b200vit_attention_bwd_bias(const void* qkv_bf16, const void* out_bf16, const void* dout_bf16, const float* lse,
+                               float* delta, void* dqkv_bf16, float* dbias, int batch, int tokens, int heads,
+                               int head_dim, float scale, void* stream);
+
 /* Classifier head on the normalised class-token rows: logits[B, C] = xn[B, D] . w[C, D]^T + b
  * (nn.Linear(D, num_classes), models/vit.py:219-222, 235); fp32 on the master weights. */
 int b200vit_head_fwd(const float* xn, const float* w, const float* b, float* logits, int batch, int dim, int classes,

@@ -32,6 +32,7 @@ _SIGNATURES = {
     "b200vit_dropout_cast": [_p, _p, _p, _ll, _i, _f, _ull, _ull, _p],
     "b200vit_attention_fwd": [_p, _p, _p, _i, _i, _i, _i, _f, _p],
     "b200vit_attention_bwd": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _f, _p],
+    "b200vit_attention_bwd_bias": [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _f, _p],
     "b200vit_head_fwd": [_p, _p, _p, _p, _i, _i, _i, _p],
     "b200vit_head_bwd": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _p],
     "b200vit_softmax_ce": [_p, _p, _p, _p, _p, _i, _i, _p],
@@ -108,7 +109,7 @@ def check(rc: int, what: str) -> None:
 
 
 # CUDA kernels launched by one successful call of each entry point (memsets are not counted).
-KERNELS_PER_CALL = {"b200vit_attention_bwd": 3, "b200vit_l2norm_sq": 2, "b200vit_l2norm_sq_noalloc": 2,
+KERNELS_PER_CALL = {"b200vit_l2norm_sq": 2, "b200vit_l2norm_sq_noalloc": 2,
                     "b200vit_head_bwd": 2}
 launch_count = 0
 

@@ -180,9 +180,8 @@ def _msa_backward(g, saved, bn, t, heads, ln_w, w_in16, w_out16, has_residual, g
     K.gemm(K.OP_NN, K.EPI_BF16, r, d, d, g16, d, w_out16, d, do, d)
     delta = _empty((bn, heads, t), torch.float32, x2d)
     dqkv = _empty((r, 3 * d), torch.bfloat16, x2d)
-    K.attention_bwd(qkv, o, do, lse, delta, dqkv, bn, t, heads, HEAD_DIM, 1.0 / math.sqrt(HEAD_DIM))
-    db_in = _empty((3 * d,), torch.float32, x2d)
-    K.colsum_bf16(dqkv, 3 * d, db_in, r, 3 * d)
+    db_in = _empty((3 * d,), torch.float32, x2d)       # in_proj_bias gradient: column sums of dqkv, from the same kernel
+    K.attention_bwd(qkv, o, do, lse, delta, dqkv, bn, t, heads, HEAD_DIM, 1.0 / math.sqrt(HEAD_DIM), dbias=db_in)
     dw_in = _zeros((3 * d, d), x2d)
     K.gemm(K.OP_TN, K.EPI_ACCUM, 3 * d, d, r, dqkv, 3 * d, ln, d, dw_in, d, split_k=K.split_k_for(3 * d, d, r, dev))
     dln = _empty((r, d), torch.bfloat16, x2d)

@@ -123,9 +123,14 @@ def attention_fwd(qkv, out, lse, batch, tokens, heads, head_dim, scale) -> None:
             stream_ptr(qkv.device))
 
 
-def attention_bwd(qkv, out, dout, lse, delta, dqkv, batch, tokens, heads, head_dim, scale) -> None:
-    _C.call("b200vit_attention_bwd", _ptr(qkv), _ptr(out), _ptr(dout), _ptr(lse), _ptr(delta), _ptr(dqkv), batch,
-            tokens, heads, head_dim, float(scale), stream_ptr(qkv.device))
+def attention_bwd(qkv, out, dout, lse, delta, dqkv, batch, tokens, heads, head_dim, scale, dbias=None) -> None:
+    """dbias (optional, f32 [3 * heads * head_dim]) receives the column sums of dqkv (the in_proj_bias gradient)."""
+    if dbias is None:
+        _C.call("b200vit_attention_bwd", _ptr(qkv), _ptr(out), _ptr(dout), _ptr(lse), _ptr(delta), _ptr(dqkv), batch,
+                tokens, heads, head_dim, float(scale), stream_ptr(qkv.device))
+    else:
+        _C.call("b200vit_attention_bwd_bias", _ptr(qkv), _ptr(out), _ptr(dout), _ptr(lse), _ptr(delta), _ptr(dqkv),
+                _ptr(dbias), batch, tokens, heads, head_dim, float(scale), stream_ptr(qkv.device))
 
 
 def head_fwd(xn, w, b, logits, batch, dim, classes) -> None:

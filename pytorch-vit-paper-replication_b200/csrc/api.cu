@@ -76,8 +76,14 @@ int b200vit_attention_fwd(const void* qkv, void* out, float* lse, int batch, int
 
 int b200vit_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
                           void* dqkv, int batch, int tokens, int heads, int head_dim, float scale, void* stream) {
-    return attention_bwd_launch((const bf16*)qkv, (const bf16*)out, (const bf16*)dout, lse, delta, (bf16*)dqkv, batch,
-                                tokens, heads, head_dim, scale, (cudaStream_t)stream);
+    return attention_bwd_launch((const bf16*)qkv, (const bf16*)out, (const bf16*)dout, lse, delta, (bf16*)dqkv, nullptr,
+                                batch, tokens, heads, head_dim, scale, (cudaStream_t)stream);
+}
+int b200vit_attention_bwd_bias(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                               void* dqkv, float* dbias, int batch, int tokens, int heads, int head_dim, float scale,
+                               void* stream) {
+    return attention_bwd_launch((const bf16*)qkv, (const bf16*)out, (const bf16*)dout, lse, delta, (bf16*)dqkv, dbias,
+                                batch, tokens, heads, head_dim, scale, (cudaStream_t)stream);
 }
 
 int b200vit_head_fwd(const float* xn, const float* w, const float* b, float* logits, int batch, int dim, int classes,

@@ -667,13 +667,13 @@ int attention_fwd_launch(const bf16* qkv, bf16* out, float* lse, int batch, int 
 }
 
 int attention_bwd_launch(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, float* delta,
-                         bf16* dqkv, int batch, int tokens, int heads, int head_dim, float scale,
+                         bf16* dqkv, float* dbias, int batch, int tokens, int heads, int head_dim, float scale,
                          cudaStream_t stream) {
     B200_CHECK_ARG(qkv && out && dout && lse && delta && dqkv, "attention_bwd: null pointer");
     B200_CHECK_ARG(head_dim == AT_HD, "attention_bwd: head_dim must be 64 (got %d)", head_dim);
     B200_CHECK_ARG(batch > 0 && tokens > 0 && heads > 0, "attention_bwd: bad sizes");
     if (tokens <= AT_RESIDENT_MAX_T && attention_mode() == 0)
-        return attention_bwd_tc_launch(qkv, out, dout, lse, dqkv, batch, tokens, heads, scale, stream);
+        return attention_bwd_tc_launch(qkv, out, dout, lse, dqkv, dbias, batch, tokens, heads, scale, stream);
     if (tokens <= AT_RESIDENT_MAX_T) {
         // delta is computed inside the fused kernel (kept in shared memory); the scratch buffer is not touched
         const int Tp = (tokens + 15) & ~15;
@@ -682,20 +682,23 @@ int attention_bwd_launch(const bf16* qkv, const bf16* out, const bf16* dout, con
         attention_bwd_resident_kernel<<<batch * heads, 128, smem, stream>>>(
             qkv, out, dout, lse, dqkv, tokens, Tp, heads, scale * 1.4426950408889634f, scale);
         B200_LAUNCH_CHECK();
-        return 0;
+        return dbias ? colsum_bf16_launch(dqkv, 3LL * heads * AT_HD, dbias, (long long)batch * tokens, 3 * heads * AT_HD, stream) : 0;
     }
     const long long rows = (long long)batch * tokens * heads;
     attention_delta_kernel<<<(unsigned)((rows * 8 + 255) / 256), 256, 0, stream>>>(out, dout, delta, batch, tokens, heads);
     B200_LAUNCH_CHECK();
-    if (attention_mode() == 0 && tokens <= AT_LONG_MAX_T)
-        return attention_bwd_long_launch(qkv, dout, lse, delta, dqkv, batch, tokens, heads, scale, stream);
+    if (attention_mode() == 0 && tokens <= AT_LONG_MAX_T) {
+        const int rc = attention_bwd_long_launch(qkv, dout, lse, delta, dqkv, batch, tokens, heads, scale, stream);
+        if (rc || !dbias) return rc;
+        return colsum_bf16_launch(dqkv, 3LL * heads * AT_HD, dbias, (long long)batch * tokens, 3 * heads * AT_HD, stream);
+    }
     dim3 grid(batch * heads, (tokens + AT_BLOCK - 1) / AT_BLOCK);
     const float sl2 = scale * 1.4426950408889634f;
     attention_bwd_dkdv_kernel<<<grid, AT_THREADS, 0, stream>>>(qkv, dout, lse, delta, dqkv, tokens, heads, sl2, scale);
     B200_LAUNCH_CHECK();
     attention_bwd_dq_kernel<<<grid, AT_THREADS, 0, stream>>>(qkv, dout, lse, delta, dqkv, tokens, heads, sl2, scale);
     B200_LAUNCH_CHECK();
-    return 0;
+    return dbias ? colsum_bf16_launch(dqkv, 3LL * heads * AT_HD, dbias, (long long)batch * tokens, 3 * heads * AT_HD, stream) : 0;
 }
 
 }  // namespace b200vit

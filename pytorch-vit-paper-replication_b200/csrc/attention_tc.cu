@@ -868,8 +868,8 @@ constexpr int AT3_THREADS = ATC_THREADS + 64;     // + two statistics warps (reg
 __global__ void __launch_bounds__(AT3_THREADS, 1)
 attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
                          const bf16* __restrict__ out, const bf16* __restrict__ dout, const float* __restrict__ lse,
-                         bf16* __restrict__ dqkv, int num_heads_total, int T, int Nk, int H, float scale_log2,
-                         float scale) {
+                         bf16* __restrict__ dqkv, float* __restrict__ dbias, int num_heads_total, int T, int Nk, int H,
+                         float scale_log2, float scale) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t tile_bytes = (uint32_t)Nk * 128u;
@@ -886,6 +886,10 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
     const uint32_t kv_ready = bar_base + 80u, kv_free = bar_base + 88u, dq_ready = bar_base + 96u, dq_free = bar_base + 104u;
     auto stat_free = [&](int s) { return bar_base + 112u + 8u * s; };
     const uint32_t tmem_slot = bar_base + 128u;
+    // optional fused in-projection bias gradient: per-CTA column sums of dQ | dK | dV, [3][H][64] fp32, flushed at the end
+    float* sBias = reinterpret_cast<float*>(smem_raw - smem_u32(smem_raw) + bar_base + 256u);
+    if (dbias != nullptr)
+        for (int k = threadIdx.x; k < 3 * H * 64; k += blockDim.x) sBias[k] = 0.f;
     uint8_t* gen = smem_raw - smem_u32(smem_raw);
     uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen + tmem_slot);
 
@@ -1090,6 +1094,13 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
                         reinterpret_cast<uint4*>(dst)[i] = q;
                     }
                 }
+                if (dbias != nullptr) {         // column sums over this warp's valid rows -> lane j holds column j
+                    float f[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) f[i] = row < T ? __uint_as_float(v[i]) : 0.f;
+                    const float cs = warp_colsum32(f, lane);
+                    atomicAdd(sBias + ((g == 0 ? 2 : 1) * H + h) * 64 + half * 32 + lane, cs);
+                }
             };
             int pending_tile = -1;          // tile whose dV/dK this group still has to read out
             for (int s = 0; s < nsteps; ++s) {
@@ -1177,6 +1188,13 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
                     reinterpret_cast<uint4*>(dst)[i] = q;
                 }
             }
+            if (dbias != nullptr && g < nm) {
+                float f[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) f[i] = row < T ? __uint_as_float(v[i]) : 0.f;
+                const float cs = warp_colsum32(f, lane);
+                atomicAdd(sBias + h * 64 + half * 32 + lane, cs);
+            }
         }
     }
     tc_fence_before();
@@ -1185,6 +1203,8 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
         tc_fence_after();
         tmem_dealloc<1>(tmem, 512);
     }
+    if (dbias != nullptr)
+        for (int k = threadIdx.x; k < 3 * H * 64; k += blockDim.x) atomicAdd(dbias + k, sBias[k]);
 }
 
 // =============================================================================================
@@ -1900,8 +1920,8 @@ int attention_bwd_long_launch(const bf16* qkv, const bf16* dout, const float* ls
     return 0;
 }
 
-int attention_bwd_tc_launch(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, bf16* dqkv, int batch,
-                            int tokens, int heads, float scale, cudaStream_t stream) {
+int attention_bwd_tc_launch(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, bf16* dqkv, float* dbias,
+                            int batch, int tokens, int heads, float scale, cudaStream_t stream) {
     const int Nk = (tokens + 15) & ~15;
     CUtensorMap tq, td;
     int rc = make_tmap_rows64(&tq, qkv, batch, tokens, 3 * heads, Nk);
@@ -1917,13 +1937,23 @@ int attention_bwd_tc_launch(const bf16* qkv, const bf16* out, const bf16* dout, 
         variant = e ? atoi(e) : 0;
     }
     if (variant == 0) {
-        const size_t smem3 = 1024 + 4 * tile_stride + ATB_TAIL_PAD + 2 * 32768 + 2 * 2 * (size_t)Nk * 4 + 128;
-        B200_CUDA(cudaFuncSetAttribute(attention_bwd_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
-        attention_bwd_tc3_kernel<<<grid, AT3_THREADS, smem3, stream>>>(tq, td, out, dout, lse, dqkv, total, tokens, Nk, heads,
-                                                                     scale * 1.4426950408889634f, scale);
-        B200_LAUNCH_CHECK();
-        return 0;
+        const size_t smem3 = 1024 + 4 * tile_stride + ATB_TAIL_PAD + 2 * 32768 + 2 * 2 * (size_t)Nk * 4 + 256 +
+                             (dbias ? (size_t)3 * heads * 64 * 4 : 0);
+        if (smem3 <= 232448) {
+            if (dbias) B200_CUDA(cudaMemsetAsync(dbias, 0, sizeof(float) * 3 * heads * 64, stream));
+            B200_CUDA(cudaFuncSetAttribute(attention_bwd_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
+            attention_bwd_tc3_kernel<<<grid, AT3_THREADS, smem3, stream>>>(tq, td, out, dout, lse, dqkv, dbias, total, tokens, Nk,
+                                                                         heads, scale * 1.4426950408889634f, scale);
+            B200_LAUNCH_CHECK();
+            return 0;
+        }
     }
+    // the two-pass kernels below do not produce the bias gradient themselves
+    struct BiasAfter {
+        const bf16* dqkv; float* dbias; long long rows; int cols; cudaStream_t stream;
+        int run() const { return dbias ? colsum_bf16_launch(dqkv, cols, dbias, rows, cols, stream) : 0; }
+    } bias_after{dqkv, dbias, (long long)batch * tokens, 3 * heads * 64, stream};
+    {
     const size_t smem = 1024 + 2 * 4 * tile_stride + ATB_TAIL_PAD + 2 * 2 * (size_t)Nk * 4 + 128;
     B200_CHECK_ARG(smem <= 232448, "attention_bwd: %d tokens need %zu bytes of shared memory", tokens, smem);
     B200_CUDA(cudaFuncSetAttribute(attention_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -1932,12 +1962,13 @@ int attention_bwd_tc_launch(const bf16* qkv, const bf16* out, const bf16* dout, 
         attention_bwd_tc2_kernel<<<grid, ATP_THREADS, smem, stream>>>(tq, td, out, dout, lse, dqkv, total, tokens, Nk,
                                                                     heads, scale * 1.4426950408889634f, scale);
         B200_LAUNCH_CHECK();
-        return 0;
+        return bias_after.run();
     }
     attention_bwd_tc_kernel<<<grid, ATB_THREADS, smem, stream>>>(tq, td, out, dout, lse, dqkv, total, tokens, Nk, heads,
                                                                scale * 1.4426950408889634f, scale);
     B200_LAUNCH_CHECK();
-    return 0;
+    return bias_after.run();
+    }
 }
 
 }  // namespace b200vit

@@ -41,10 +41,10 @@ int attention_fwd_long_launch(const bf16* qkv, bf16* out, float* lse, int batch,
 constexpr int AT_LONG_MAX_T = 2048;   // the long backward kernel stages lse/delta of a whole head in shared memory
 int attention_bwd_long_launch(const bf16* qkv, const bf16* dout, const float* lse, const float* delta, bf16* dqkv,
                               int batch, int tokens, int heads, float scale, cudaStream_t stream);
-int attention_bwd_tc_launch(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, bf16* dqkv, int batch,
-                            int tokens, int heads, float scale, cudaStream_t stream);
+int attention_bwd_tc_launch(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, bf16* dqkv, float* dbias,
+                            int batch, int tokens, int heads, float scale, cudaStream_t stream);
 int attention_bwd_launch(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, float* delta,
-                         bf16* dqkv, int batch, int tokens, int heads, int head_dim, float scale,
+                         bf16* dqkv, float* dbias, int batch, int tokens, int heads, int head_dim, float scale,
                          cudaStream_t stream);
 
 int head_fwd_launch(const float* xn, const float* w, const float* b, float* logits, int batch, int dim, int classes,

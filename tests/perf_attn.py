@@ -26,5 +26,7 @@ def timeit(f, n=10):
     return e0.elapsed_time(e1) / n * 1e3
 f = timeit(lambda: K.attention_fwd(qkv, out, lse, B, T, H, hd, sc))
 b = timeit(lambda: K.attention_bwd(qkv, out, dout, lse, delta, dqkv, B, T, H, hd, sc))
+dbias = torch.empty(3 * H * hd, device=dev)
+bb = timeit(lambda: K.attention_bwd(qkv, out, dout, lse, delta, dqkv, B, T, H, hd, sc, dbias=dbias))
 fl = 4 * B * H * T * T * hd
-print(f"attention fwd {f:.1f} us ({fl/f/1e6:.0f} TFLOP/s)  bwd {b:.1f} us ({2.5*fl/b/1e6:.0f} TFLOP/s algorithmic)")
+print(f"attention fwd {f:.1f} us ({fl/f/1e6:.0f} TFLOP/s)  bwd {b:.1f} us ({2.5*fl/b/1e6:.0f} TFLOP/s algorithmic)  bwd+bias-grad {bb:.1f} us")

@@ -210,7 +210,12 @@ def test_attention_fwd_bwd(Bn, T, H):
     dout = _rand_bf16((Bn, T, H * hd), g, 1.0)
     delta = torch.empty((Bn, H, T), dtype=torch.float32, device=dev())
     dqkv = torch.empty_like(qkv)
-    K.attention_bwd(qkv, out, dout, lse, delta, dqkv, Bn, T, H, hd, scale)
+    dbias = torch.full((3 * H * hd,), 7.0, dtype=torch.float32, device=dev())      # must be overwritten
+    K.attention_bwd(qkv, out, dout, lse, delta, dqkv, Bn, T, H, hd, scale, dbias=dbias)
+    assert rel_err(dbias, dqkv.float().reshape(Bn * T, -1).sum(0)) < 3e-3           # in_proj_bias gradient
+    dqkv_plain = torch.empty_like(dqkv)
+    K.attention_bwd(qkv, out, dout, lse, delta, dqkv_plain, Bn, T, H, hd, scale)
+    assert torch.equal(dqkv_plain, dqkv)
     ref.backward(dout.float().reshape(Bn, T, H, hd).permute(0, 2, 1, 3))
     for i, t in enumerate((q, k, v)):
         got = dqkv[:, :, i].float().permute(0, 2, 1, 3)
