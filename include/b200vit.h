@@ -132,6 +132,20 @@ int b200vit_attention_bwd_bias(const void* qkv_bf16, const void* out_bf16, const
                                float* delta, void* dqkv_bf16, float* dbias, int batch, int tokens, int heads,
                                int head_dim, float scale, void* stream);
 
+/* Attention with dropout on the probabilities: nn.MultiheadAttention(dropout=attn_dropout) in training mode
+ * (models/vit.py:86-90; torch drops softmax(S) before the PV product and scales the kept entries by 1/(1-p)).
+ * Element (b, h, q, k) of the probability tensor uses index ((b*H + h)*T + q)*T + k of the (seed, offset) mask, so
+ * the backward call regenerates the forward's mask from the same triple. dropout_p == 0 forwards to the entry points
+ * above; dropout_p > 0 runs the mma.sync kernels (the reference default is 0, the tcgen05 kernels carry no mask code).
+ * dbias may be NULL. */
+int b200vit_attention_fwd_dropout(const void* qkv_bf16, void* out_bf16, float* lse, int batch, int tokens, int heads,
+                                  int head_dim, float scale, float dropout_p, unsigned long long seed,
+                                  unsigned long long offset, void* stream);
+int b200vit_attention_bwd_dropout(const void* qkv_bf16, const void* out_bf16, const void* dout_bf16, const float* lse,
+                                  float* delta, void* dqkv_bf16, float* dbias, int batch, int tokens, int heads,
+                                  int head_dim, float scale, float dropout_p, unsigned long long seed,
+                                  unsigned long long offset, void* stream);
+
 /* Classifier head on the normalised class-token rows: logits[B, C] = xn[B, D] . w[C, D]^T + b
  * (nn.Linear(D, num_classes), models/vit.py:219-222, 235); fp32 on the master weights. */
 int b200vit_head_fwd(const float* xn, const float* w, const float* b, float* logits, int batch, int dim, int classes,

@@ -33,6 +33,8 @@ _SIGNATURES = {
     "b200vit_attention_fwd": [_p, _p, _p, _i, _i, _i, _i, _f, _p],
     "b200vit_attention_bwd": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _f, _p],
     "b200vit_attention_bwd_bias": [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _f, _p],
+    "b200vit_attention_fwd_dropout": [_p, _p, _p, _i, _i, _i, _i, _f, _f, _ull, _ull, _p],
+    "b200vit_attention_bwd_dropout": [_p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _f, _f, _ull, _ull, _p],
     "b200vit_head_fwd": [_p, _p, _p, _p, _i, _i, _i, _p],
     "b200vit_head_bwd": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _p],
     "b200vit_softmax_ce": [_p, _p, _p, _p, _p, _i, _i, _p],

@@ -148,7 +148,7 @@ class PatchEmbedFn(torch.autograd.Function):
 # ---------------------------------------------------------------------------------------------------------
 # MSA / MLP halves of an encoder block (reference models/vit.py:92-98, 128-131, 166-169)
 # ---------------------------------------------------------------------------------------------------------
-def _msa_forward(x2d, bn, t, heads, ln_w, ln_b, w_in16, b_in, w_out16, b_out, residual):
+def _msa_forward(x2d, bn, t, heads, ln_w, ln_b, w_in16, b_in, w_out16, b_out, residual, attn_p=0.0):
     r, d = x2d.shape
     if d != heads * HEAD_DIM:
         raise NotImplementedError(f"b200vit attention kernels need head_dim == 64 (embedding_dim {d}, heads {heads})")
@@ -160,13 +160,15 @@ def _msa_forward(x2d, bn, t, heads, ln_w, ln_b, w_in16, b_in, w_out16, b_out, re
     K.gemm(K.OP_NT, K.EPI_BF16, r, 3 * d, d, ln, d, w_in16, d, qkv, 3 * d, bias=b_in)
     o = _empty((r, d), torch.bfloat16, x2d)
     lse = _empty((bn, heads, t), torch.float32, x2d)
-    K.attention_fwd(qkv, o, lse, bn, t, heads, HEAD_DIM, 1.0 / math.sqrt(HEAD_DIM))
+    akey = next_dropout_key() if attn_p > 0 else (0, 0)      # dropout on the attention probabilities (vit.py:86-90)
+    K.attention_fwd(qkv, o, lse, bn, t, heads, HEAD_DIM, 1.0 / math.sqrt(HEAD_DIM), attn_p, akey[0], akey[1])
     y = _empty((r, d), torch.float32, x2d)
     K.gemm(K.OP_NT, K.EPI_BIAS_RES, r, d, d, o, d, w_out16, d, y, d, bias=b_out, aux=residual, ldaux=d)
-    return y, (x2d, mean, rstd, ln, qkv, o, lse)
+    return y, (x2d, mean, rstd, ln, qkv, o, lse), (attn_p, akey)
 
 
-def _msa_backward(g, saved, bn, t, heads, ln_w, w_in16, w_out16, has_residual, g16=None, db_out=None):
+def _msa_backward(g, saved, bn, t, heads, ln_w, w_in16, w_out16, has_residual, g16=None, db_out=None,
+                  adrop=(0.0, (0, 0))):
     x2d, mean, rstd, ln, qkv, o, lse = saved
     r, d = x2d.shape
     dev = x2d.device
@@ -181,7 +183,8 @@ def _msa_backward(g, saved, bn, t, heads, ln_w, w_in16, w_out16, has_residual, g
     delta = _empty((bn, heads, t), torch.float32, x2d)
     dqkv = _empty((r, 3 * d), torch.bfloat16, x2d)
     db_in = _empty((3 * d,), torch.float32, x2d)       # in_proj_bias gradient: column sums of dqkv, from the same kernel
-    K.attention_bwd(qkv, o, do, lse, delta, dqkv, bn, t, heads, HEAD_DIM, 1.0 / math.sqrt(HEAD_DIM), dbias=db_in)
+    K.attention_bwd(qkv, o, do, lse, delta, dqkv, bn, t, heads, HEAD_DIM, 1.0 / math.sqrt(HEAD_DIM), dbias=db_in,
+                    dropout_p=adrop[0], seed=adrop[1][0], offset=adrop[1][1])
     dw_in = _zeros((3 * d, d), x2d)
     K.gemm(K.OP_TN, K.EPI_ACCUM, 3 * d, d, r, dqkv, 3 * d, ln, d, dw_in, d, split_k=K.split_k_for(3 * d, d, r, dev))
     dln = _empty((r, d), torch.bfloat16, x2d)
@@ -246,13 +249,16 @@ class MSAFn(torch.autograd.Function):
     """MultiHeadSelfAttentionBlock.forward (models/vit.py:92-98): LN -> self-attention, no residual."""
 
     @staticmethod
-    def forward(ctx, x, ln_w, ln_b, w_in, b_in, w_out, b_out, w_in16, w_out16, heads: int):
+    def forward(ctx, x, ln_w, ln_b, w_in, b_in, w_out, b_out, w_in16, w_out16, heads: int, attn_p: float = 0.0,
+                training: bool = False):
         _require_cuda(x, "MultiHeadSelfAttentionBlock")
         x = _f32c(x)
         bn, t, d = x.shape
-        y, saved = _msa_forward(x.view(bn * t, d), bn, t, heads, ln_w, ln_b, w_in16, b_in, w_out16, b_out, None)
+        y, saved, adrop = _msa_forward(x.view(bn * t, d), bn, t, heads, ln_w, ln_b, w_in16, b_in, w_out16, b_out, None,
+                                       float(attn_p) if training else 0.0)
         ctx.save_for_backward(ln_w, w_in16, w_out16, *saved)
         ctx.meta = (bn, t, heads)
+        ctx.adrop = adrop
         return y.view(bn, t, d)
 
     @staticmethod
@@ -261,8 +267,9 @@ class MSAFn(torch.autograd.Function):
         bn, t, heads = ctx.meta
         d = g.shape[-1]
         gx, (dgam, dbet, dw_in, db_in, dw_out, db_out) = _msa_backward(
-            _f32c(g).view(bn * t, d), tuple(saved), bn, t, heads, ln_w, w_in16, w_out16, has_residual=False)
-        return gx.view(bn, t, d), dgam, dbet, dw_in, db_in, dw_out, db_out, None, None, None
+            _f32c(g).view(bn * t, d), tuple(saved), bn, t, heads, ln_w, w_in16, w_out16, has_residual=False,
+            adrop=ctx.adrop)
+        return gx.view(bn, t, d), dgam, dbet, dw_in, db_in, dw_out, db_out, None, None, None, None, None
 
 
 class MLPFn(torch.autograd.Function):
@@ -299,19 +306,21 @@ class EncoderBlockFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, a_ln_w, a_ln_b, w_in, b_in, w_out, b_out, m_ln_w, m_ln_b, w1, b1, w2, b2,
-                w_in16, w_out16, w1_16, w2_16, heads: int, p: float, training: bool):
+                w_in16, w_out16, w1_16, w2_16, heads: int, p: float, training: bool, attn_p: float = 0.0):
         _require_cuda(x, "TransformerEncoderBlock")
         x = _f32c(x)
         bn, t, d = x.shape
         x2d = x.view(bn * t, d)
         needs_bwd = any(ctx.needs_input_grad)
-        x1, s_msa = _msa_forward(x2d, bn, t, heads, a_ln_w, a_ln_b, w_in16, b_in, w_out16, b_out, x2d)
+        x1, s_msa, adrop = _msa_forward(x2d, bn, t, heads, a_ln_w, a_ln_b, w_in16, b_in, w_out16, b_out, x2d,
+                                        float(attn_p) if training else 0.0)
         x2, s_mlp, drop = _mlp_forward(x1, m_ln_w, m_ln_b, w1_16, b1, w2_16, b2, float(p) if training else 0.0, x1,
                                        keep_preact=needs_bwd)
         if needs_bwd:
             ctx.save_for_backward(a_ln_w, m_ln_w, w_in16, w_out16, w1_16, w2_16, *s_msa, *s_mlp)
         ctx.meta = (bn, t, heads, len(s_msa))
         ctx.drop = drop
+        ctx.adrop = adrop
         return x2.view(bn, t, d)
 
     @staticmethod
@@ -324,9 +333,10 @@ class EncoderBlockFn(torch.autograd.Function):
         g1, (m_dgam, m_dbet, dw1, db1, dw2, db2), g1_16, db_out = _mlp_backward(
             g2, s_mlp, ctx.drop, m_ln_w, w1_16, w2_16, has_residual=True, want_bf16_out=True)
         g0, (a_dgam, a_dbet, dw_in, db_in, dw_out, db_out) = _msa_backward(
-            g1, s_msa, bn, t, heads, a_ln_w, w_in16, w_out16, has_residual=True, g16=g1_16, db_out=db_out)
+            g1, s_msa, bn, t, heads, a_ln_w, w_in16, w_out16, has_residual=True, g16=g1_16, db_out=db_out,
+            adrop=ctx.adrop)
         return (g0.view(bn, t, d), a_dgam, a_dbet, dw_in, db_in, dw_out, db_out, m_dgam, m_dbet, dw1, db1, dw2, db2,
-                None, None, None, None, None, None, None)
+                None, None, None, None, None, None, None, None)
 
 
 # ---------------------------------------------------------------------------------------------------------

@@ -118,14 +118,25 @@ def dropout_cast(g, out_bf16, colsum, rows, cols, p, seed, offset) -> None:
             int(offset), stream_ptr(g.device))
 
 
-def attention_fwd(qkv, out, lse, batch, tokens, heads, head_dim, scale) -> None:
-    _C.call("b200vit_attention_fwd", _ptr(qkv), _ptr(out), _ptr(lse), batch, tokens, heads, head_dim, float(scale),
-            stream_ptr(qkv.device))
+def attention_fwd(qkv, out, lse, batch, tokens, heads, head_dim, scale, dropout_p=0.0, seed=0, offset=0) -> None:
+    """dropout_p > 0: dropout on the attention probabilities (mask = function of (seed, offset))."""
+    if dropout_p > 0:
+        _C.call("b200vit_attention_fwd_dropout", _ptr(qkv), _ptr(out), _ptr(lse), batch, tokens, heads, head_dim,
+                float(scale), float(dropout_p), int(seed), int(offset), stream_ptr(qkv.device))
+    else:
+        _C.call("b200vit_attention_fwd", _ptr(qkv), _ptr(out), _ptr(lse), batch, tokens, heads, head_dim, float(scale),
+                stream_ptr(qkv.device))
 
 
-def attention_bwd(qkv, out, dout, lse, delta, dqkv, batch, tokens, heads, head_dim, scale, dbias=None) -> None:
-    """dbias (optional, f32 [3 * heads * head_dim]) receives the column sums of dqkv (the in_proj_bias gradient)."""
-    if dbias is None:
+def attention_bwd(qkv, out, dout, lse, delta, dqkv, batch, tokens, heads, head_dim, scale, dbias=None, dropout_p=0.0,
+                  seed=0, offset=0) -> None:
+    """dbias (optional, f32 [3 * heads * head_dim]) receives the column sums of dqkv (the in_proj_bias gradient).
+    dropout_p / seed / offset: the triple given to the forward call."""
+    if dropout_p > 0:
+        _C.call("b200vit_attention_bwd_dropout", _ptr(qkv), _ptr(out), _ptr(dout), _ptr(lse), _ptr(delta), _ptr(dqkv),
+                _ptr(dbias), batch, tokens, heads, head_dim, float(scale), float(dropout_p), int(seed), int(offset),
+                stream_ptr(qkv.device))
+    elif dbias is None:
         _C.call("b200vit_attention_bwd", _ptr(qkv), _ptr(out), _ptr(dout), _ptr(lse), _ptr(delta), _ptr(dqkv), batch,
                 tokens, heads, head_dim, float(scale), stream_ptr(qkv.device))
     else:

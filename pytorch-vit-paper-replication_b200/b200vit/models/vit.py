@@ -66,18 +66,12 @@ class MultiHeadSelfAttentionBlock(nn.Module):
         self.multi_head_attention = nn.MultiheadAttention(embed_dim=embedding_dim, num_heads=num_heads,
                                                           dropout=attn_dropout, batch_first=True)
 
-    def _check(self):
-        mha = self.multi_head_attention
-        if self.training and mha.dropout > 0:
-            raise NotImplementedError("attn_dropout > 0 in training mode is not implemented by the fused attention "
-                                      "kernel yet (the reference default is 0)")
-        return mha
-
     def forward(self, x: torch.Tensor):
-        mha = self._check()
+        mha = self.multi_head_attention
+        # mha.dropout > 0 (attn_dropout): dropout on the attention probabilities in training mode, as torch does
         return F_.MSAFn.apply(x, self.layer_norm.weight, self.layer_norm.bias, mha.in_proj_weight, mha.in_proj_bias,
                               mha.out_proj.weight, mha.out_proj.bias, F_.bf16_shadow(mha.in_proj_weight),
-                              F_.bf16_shadow(mha.out_proj.weight), mha.num_heads)
+                              F_.bf16_shadow(mha.out_proj.weight), mha.num_heads, mha.dropout, self.training)
 
 
 class MLPBlock(nn.Module):
@@ -120,13 +114,14 @@ class TransformerEncoderBlock(nn.Module):
 
     def forward(self, x: torch.Tensor):
         msa, mlp = self.msa_block, self.mlp_block
-        mha = msa._check()
+        mha = msa.multi_head_attention
         fc1, fc2 = mlp.mlp[0], mlp.mlp[3]
         return F_.EncoderBlockFn.apply(
             x, msa.layer_norm.weight, msa.layer_norm.bias, mha.in_proj_weight, mha.in_proj_bias,
             mha.out_proj.weight, mha.out_proj.bias, mlp.layer_norm.weight, mlp.layer_norm.bias, fc1.weight, fc1.bias,
             fc2.weight, fc2.bias, F_.bf16_shadow(mha.in_proj_weight), F_.bf16_shadow(mha.out_proj.weight),
-            F_.bf16_shadow(fc1.weight), F_.bf16_shadow(fc2.weight), mha.num_heads, mlp.mlp[2].p, self.training)
+            F_.bf16_shadow(fc1.weight), F_.bf16_shadow(fc2.weight), mha.num_heads, mlp.mlp[2].p, self.training,
+            mha.dropout)
 
 
 class ViT(nn.Module):

@@ -79,6 +79,19 @@ int b200vit_attention_bwd(const void* qkv, const void* out, const void* dout, co
     return attention_bwd_launch((const bf16*)qkv, (const bf16*)out, (const bf16*)dout, lse, delta, (bf16*)dqkv, nullptr,
                                 batch, tokens, heads, head_dim, scale, (cudaStream_t)stream);
 }
+int b200vit_attention_fwd_dropout(const void* qkv, void* out, float* lse, int batch, int tokens, int heads, int head_dim,
+                                  float scale, float dropout_p, unsigned long long seed, unsigned long long offset,
+                                  void* stream) {
+    return attention_fwd_dropout_launch((const bf16*)qkv, (bf16*)out, lse, batch, tokens, heads, head_dim, scale,
+                                        dropout_p, seed, offset, (cudaStream_t)stream);
+}
+int b200vit_attention_bwd_dropout(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                                  void* dqkv, float* dbias, int batch, int tokens, int heads, int head_dim, float scale,
+                                  float dropout_p, unsigned long long seed, unsigned long long offset, void* stream) {
+    return attention_bwd_dropout_launch((const bf16*)qkv, (const bf16*)out, (const bf16*)dout, lse, delta, (bf16*)dqkv,
+                                        dbias, batch, tokens, heads, head_dim, scale, dropout_p, seed, offset,
+                                        (cudaStream_t)stream);
+}
 int b200vit_attention_bwd_bias(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
                                void* dqkv, float* dbias, int batch, int tokens, int heads, int head_dim, float scale,
                                void* stream) {

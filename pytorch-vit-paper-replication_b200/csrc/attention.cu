@@ -137,9 +137,13 @@ __device__ __forceinline__ void store_acc_bf16(const float (&c)[8][4], bf16* g, 
 // ---------------------------------------------------------------------------------------------
 // forward
 // ---------------------------------------------------------------------------------------------
+// DROP: dropout on the attention probabilities (nn.MultiheadAttention(dropout=p), models/vit.py:86-90, applied by
+// torch to softmax(S) before the PV product). Element (b, h, q, k) of the probability tensor has index
+// ((b*H + h)*T + q)*T + k in the counter-hash mask of common.cuh, so forward and backward regenerate the same mask.
+template <bool DROP>
 __global__ void __launch_bounds__(AT_THREADS)
 attention_fwd_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, float* __restrict__ lse, int T, int H,
-                     float scale_log2, float scale) {
+                     float scale_log2, float scale, DropoutParams drop) {
     __shared__ __align__(128) uint8_t sQ[AT_TILE_BYTES];
     __shared__ __align__(128) uint8_t sK[AT_TILE_BYTES];
     __shared__ __align__(128) uint8_t sV[AT_TILE_BYTES];
@@ -203,6 +207,18 @@ attention_fwd_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, float
         l1 = l1 * c1 + rs1;
 #pragma unroll
         for (int nt = 0; nt < 8; ++nt) { o[nt][0] *= c0; o[nt][1] *= c0; o[nt][2] *= c1; o[nt][3] *= c1; }
+        if (DROP) {     // the row sums above use the un-dropped probabilities; only the PV product sees the mask
+            const unsigned long long e_lo = ((unsigned long long)bh * T + (q0 + warp * 16 + (lane >> 2))) * T;
+            const unsigned long long e_hi = e_lo + 8ull * T;
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt) {
+                const int key = k0 + nt * 8 + 2 * tq;
+                s[nt][0] *= dropout_mult1(drop, e_lo + key);
+                s[nt][1] *= dropout_mult1(drop, e_lo + key + 1);
+                s[nt][2] *= dropout_mult1(drop, e_hi + key);
+                s[nt][3] *= dropout_mult1(drop, e_hi + key + 1);
+            }
+        }
         mma_p_b(o, s, sV, lane);
     }
     l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
@@ -255,10 +271,11 @@ __global__ void attention_delta_kernel(const bf16* __restrict__ out, const bf16*
 // ---------------------------------------------------------------------------------------------
 // backward pass 1: dK, dV for one 64-key block; loops over the query blocks
 // ---------------------------------------------------------------------------------------------
+template <bool DROP>
 __global__ void __launch_bounds__(AT_THREADS)
 attention_bwd_dkdv_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ dout, const float* __restrict__ lse,
                           const float* __restrict__ delta, bf16* __restrict__ dqkv, int T, int H, float scale_log2,
-                          float scale) {
+                          float scale, DropoutParams drop) {
     __shared__ __align__(128) uint8_t sK[AT_TILE_BYTES];
     __shared__ __align__(128) uint8_t sV[AT_TILE_BYTES];
     __shared__ __align__(128) uint8_t sQ[AT_TILE_BYTES];
@@ -319,11 +336,20 @@ attention_bwd_dkdv_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__
             const float p1 = exp2f(st[nt][1] * scale_log2 - ls1);
             const float p2 = exp2f(st[nt][2] * scale_log2 - ls0);
             const float p3 = exp2f(st[nt][3] * scale_log2 - ls1);
-            st[nt][0] = p0; st[nt][1] = p1; st[nt][2] = p2; st[nt][3] = p3;
-            dpt[nt][0] = p0 * (dpt[nt][0] - d0) * scale;
-            dpt[nt][1] = p1 * (dpt[nt][1] - d1) * scale;
-            dpt[nt][2] = p2 * (dpt[nt][2] - d0) * scale;
-            dpt[nt][3] = p3 * (dpt[nt][3] - d1) * scale;
+            float m0 = 1.f, m1 = 1.f, m2 = 1.f, m3 = 1.f;     // dropout multipliers of (query q / q+1, key lo / hi)
+            if (DROP) {
+                const int key_lo = k0 + warp * 16 + (lane >> 2);
+                const unsigned long long e0 = ((unsigned long long)bh * T + (q0 + q)) * T, e1 = e0 + T;
+                m0 = dropout_mult1(drop, e0 + key_lo);
+                m1 = dropout_mult1(drop, e1 + key_lo);
+                m2 = dropout_mult1(drop, e0 + key_lo + 8);
+                m3 = dropout_mult1(drop, e1 + key_lo + 8);
+            }
+            st[nt][0] = p0 * m0; st[nt][1] = p1 * m1; st[nt][2] = p2 * m2; st[nt][3] = p3 * m3;   // dropped P -> dV
+            dpt[nt][0] = p0 * (dpt[nt][0] * m0 - d0) * scale;
+            dpt[nt][1] = p1 * (dpt[nt][1] * m1 - d1) * scale;
+            dpt[nt][2] = p2 * (dpt[nt][2] * m2 - d0) * scale;
+            dpt[nt][3] = p3 * (dpt[nt][3] * m3 - d1) * scale;
         }
         mma_p_b(dv, st, sdO, lane);    // dV += P^T dO
         mma_p_b(dk, dpt, sQ, lane);    // dK += dS^T Q
@@ -337,10 +363,11 @@ attention_bwd_dkdv_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__
 // ---------------------------------------------------------------------------------------------
 // backward pass 2: dQ for one 64-query block; loops over the key blocks
 // ---------------------------------------------------------------------------------------------
+template <bool DROP>
 __global__ void __launch_bounds__(AT_THREADS)
 attention_bwd_dq_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ dout, const float* __restrict__ lse,
                         const float* __restrict__ delta, bf16* __restrict__ dqkv, int T, int H, float scale_log2,
-                        float scale) {
+                        float scale, DropoutParams drop) {
     __shared__ __align__(128) uint8_t sQ[AT_TILE_BYTES];
     __shared__ __align__(128) uint8_t sdO[AT_TILE_BYTES];
     __shared__ __align__(128) uint8_t sK[AT_TILE_BYTES];
@@ -392,6 +419,13 @@ attention_bwd_dq_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ d
             const float p1 = v1 ? exp2f(s[nt][1] * scale_log2 - ls0) : 0.f;
             const float p2 = v0 ? exp2f(s[nt][2] * scale_log2 - ls1) : 0.f;
             const float p3 = v1 ? exp2f(s[nt][3] * scale_log2 - ls1) : 0.f;
+            if (DROP) {
+                const unsigned long long e_lo = ((unsigned long long)bh * T + r_lo) * T, e_hi = e_lo + 8ull * T;
+                dp[nt][0] *= dropout_mult1(drop, e_lo + key);
+                dp[nt][1] *= dropout_mult1(drop, e_lo + key + 1);
+                dp[nt][2] *= dropout_mult1(drop, e_hi + key);
+                dp[nt][3] *= dropout_mult1(drop, e_hi + key + 1);
+            }
             dp[nt][0] = p0 * (dp[nt][0] - dl0) * scale;
             dp[nt][1] = p1 * (dp[nt][1] - dl0) * scale;
             dp[nt][2] = p2 * (dp[nt][2] - dl1) * scale;
@@ -660,8 +694,8 @@ int attention_fwd_launch(const bf16* qkv, bf16* out, float* lse, int batch, int 
         return 0;
     }
     dim3 grid(batch * heads, (tokens + AT_BLOCK - 1) / AT_BLOCK);
-    attention_fwd_kernel<<<grid, AT_THREADS, 0, stream>>>(qkv, out, lse, tokens, heads, scale * 1.4426950408889634f,
-                                                         scale);
+    attention_fwd_kernel<false><<<grid, AT_THREADS, 0, stream>>>(qkv, out, lse, tokens, heads, scale * 1.4426950408889634f,
+                                                                scale, DropoutParams{});
     B200_LAUNCH_CHECK();
     return 0;
 }
@@ -694,9 +728,48 @@ int attention_bwd_launch(const bf16* qkv, const bf16* out, const bf16* dout, con
     }
     dim3 grid(batch * heads, (tokens + AT_BLOCK - 1) / AT_BLOCK);
     const float sl2 = scale * 1.4426950408889634f;
-    attention_bwd_dkdv_kernel<<<grid, AT_THREADS, 0, stream>>>(qkv, dout, lse, delta, dqkv, tokens, heads, sl2, scale);
+    attention_bwd_dkdv_kernel<false><<<grid, AT_THREADS, 0, stream>>>(qkv, dout, lse, delta, dqkv, tokens, heads, sl2, scale, DropoutParams{});
     B200_LAUNCH_CHECK();
-    attention_bwd_dq_kernel<<<grid, AT_THREADS, 0, stream>>>(qkv, dout, lse, delta, dqkv, tokens, heads, sl2, scale);
+    attention_bwd_dq_kernel<false><<<grid, AT_THREADS, 0, stream>>>(qkv, dout, lse, delta, dqkv, tokens, heads, sl2, scale, DropoutParams{});
+    B200_LAUNCH_CHECK();
+    return dbias ? colsum_bf16_launch(dqkv, 3LL * heads * AT_HD, dbias, (long long)batch * tokens, 3 * heads * AT_HD, stream) : 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// attention-probability dropout (attn_dropout > 0; the reference default is 0): the FA2-style kernels with the mask
+// ---------------------------------------------------------------------------------------------
+int attention_fwd_dropout_launch(const bf16* qkv, bf16* out, float* lse, int batch, int tokens, int heads, int head_dim,
+                                 float scale, float p, unsigned long long seed, unsigned long long offset,
+                                 cudaStream_t stream) {
+    if (!(p > 0.f)) return attention_fwd_launch(qkv, out, lse, batch, tokens, heads, head_dim, scale, stream);
+    B200_CHECK_ARG(qkv && out && lse, "attention_fwd: null pointer");
+    B200_CHECK_ARG(head_dim == AT_HD, "attention_fwd: head_dim must be 64 (got %d)", head_dim);
+    B200_CHECK_ARG(batch > 0 && tokens > 0 && heads > 0 && p < 1.f, "attention_fwd: bad sizes / dropout probability");
+    B200_CHECK_ARG(((uintptr_t)qkv % 16) == 0 && ((uintptr_t)out % 16) == 0, "attention_fwd: unaligned pointer");
+    dim3 grid(batch * heads, (tokens + AT_BLOCK - 1) / AT_BLOCK);
+    attention_fwd_kernel<true><<<grid, AT_THREADS, 0, stream>>>(qkv, out, lse, tokens, heads, scale * 1.4426950408889634f,
+                                                               scale, make_dropout(p, seed, offset));
+    B200_LAUNCH_CHECK();
+    return 0;
+}
+
+int attention_bwd_dropout_launch(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, float* delta,
+                                 bf16* dqkv, float* dbias, int batch, int tokens, int heads, int head_dim, float scale,
+                                 float p, unsigned long long seed, unsigned long long offset, cudaStream_t stream) {
+    if (!(p > 0.f))
+        return attention_bwd_launch(qkv, out, dout, lse, delta, dqkv, dbias, batch, tokens, heads, head_dim, scale, stream);
+    B200_CHECK_ARG(qkv && out && dout && lse && delta && dqkv, "attention_bwd: null pointer");
+    B200_CHECK_ARG(head_dim == AT_HD, "attention_bwd: head_dim must be 64 (got %d)", head_dim);
+    B200_CHECK_ARG(batch > 0 && tokens > 0 && heads > 0 && p < 1.f, "attention_bwd: bad sizes / dropout probability");
+    const long long rows = (long long)batch * tokens * heads;
+    attention_delta_kernel<<<(unsigned)((rows * 8 + 255) / 256), 256, 0, stream>>>(out, dout, delta, batch, tokens, heads);
+    B200_LAUNCH_CHECK();
+    dim3 grid(batch * heads, (tokens + AT_BLOCK - 1) / AT_BLOCK);
+    const float sl2 = scale * 1.4426950408889634f;
+    const DropoutParams drop = make_dropout(p, seed, offset);
+    attention_bwd_dkdv_kernel<true><<<grid, AT_THREADS, 0, stream>>>(qkv, dout, lse, delta, dqkv, tokens, heads, sl2, scale, drop);
+    B200_LAUNCH_CHECK();
+    attention_bwd_dq_kernel<true><<<grid, AT_THREADS, 0, stream>>>(qkv, dout, lse, delta, dqkv, tokens, heads, sl2, scale, drop);
     B200_LAUNCH_CHECK();
     return dbias ? colsum_bf16_launch(dqkv, 3LL * heads * AT_HD, dbias, (long long)batch * tokens, 3 * heads * AT_HD, stream) : 0;
 }

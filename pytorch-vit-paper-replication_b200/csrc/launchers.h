@@ -46,6 +46,12 @@ int attention_bwd_tc_launch(const bf16* qkv, const bf16* out, const bf16* dout, 
 int attention_bwd_launch(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, float* delta,
                          bf16* dqkv, float* dbias, int batch, int tokens, int heads, int head_dim, float scale,
                          cudaStream_t stream);
+int attention_fwd_dropout_launch(const bf16* qkv, bf16* out, float* lse, int batch, int tokens, int heads, int head_dim,
+                                 float scale, float p, unsigned long long seed, unsigned long long offset,
+                                 cudaStream_t stream);
+int attention_bwd_dropout_launch(const bf16* qkv, const bf16* out, const bf16* dout, const float* lse, float* delta,
+                                 bf16* dqkv, float* dbias, int batch, int tokens, int heads, int head_dim, float scale,
+                                 float p, unsigned long long seed, unsigned long long offset, cudaStream_t stream);
 
 int head_fwd_launch(const float* xn, const float* w, const float* b, float* logits, int batch, int dim, int classes,
                     cudaStream_t stream);

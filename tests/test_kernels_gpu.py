@@ -222,6 +222,43 @@ def test_attention_fwd_bwd(Bn, T, H):
         assert rel_err(got, t.grad) < 2e-2, f"d{'qkv'[i]}"
 
 
+@pytest.mark.parametrize("Bn,T,H,p", [(2, 197, 3, 0.1), (1, 70, 2, 0.5), (1, 300, 2, 0.2)])
+def test_attention_probability_dropout(Bn, T, H, p):
+    """nn.MultiheadAttention(dropout=p) semantics: softmax(S) is dropped (kept entries / (1-p)) before the PV product.
+    The mask is regenerated here from the same (seed, offset) through dropout_cast on a [B*H*T, T] tensor of ones."""
+    g = torch.Generator().manual_seed(12)
+    hd = 64
+    seed, offset = 77, 5
+    qkv = _rand_bf16((Bn, T, 3, H, hd), g, 1.0)
+    out = torch.empty((Bn, T, H * hd), dtype=torch.bfloat16, device=dev())
+    lse = torch.empty((Bn, H, T), dtype=torch.float32, device=dev())
+    scale = 1.0 / math.sqrt(hd)
+    K.attention_fwd(qkv, out, lse, Bn, T, H, hd, scale, p, seed, offset)
+    ones = torch.ones((Bn * H * T, T), dtype=torch.float32, device=dev())
+    mask = torch.empty((Bn * H * T, T), dtype=torch.bfloat16, device=dev())
+    K.dropout_cast(ones, mask, None, Bn * H * T, T, p, seed, offset)
+    mask = mask.float().reshape(Bn, H, T, T)                      # 0 or 1/(1-p)
+    assert abs((mask != 0).float().mean().item() - (1 - p)) < 0.01
+    q, k, v = [qkv[:, :, i].float().permute(0, 2, 1, 3).detach().requires_grad_(True) for i in range(3)]
+    s = (q @ k.transpose(-1, -2)) * scale
+    ref = (torch.softmax(s, -1) * mask) @ v
+    assert rel_err(out, ref.permute(0, 2, 1, 3).reshape(Bn, T, H * hd)) < 1e-2
+    assert rel_err(lse, torch.logsumexp(s, -1)) < 1e-4            # the log-sum-exp is of the un-dropped scores
+    dout = _rand_bf16((Bn, T, H * hd), g, 1.0)
+    delta = torch.empty((Bn, H, T), dtype=torch.float32, device=dev())
+    dqkv = torch.empty_like(qkv)
+    dbias = torch.empty(3 * H * hd, dtype=torch.float32, device=dev())
+    K.attention_bwd(qkv, out, dout, lse, delta, dqkv, Bn, T, H, hd, scale, dbias=dbias, dropout_p=p, seed=seed, offset=offset)
+    ref.backward(dout.float().reshape(Bn, T, H, hd).permute(0, 2, 1, 3))
+    for i, t in enumerate((q, k, v)):
+        assert rel_err(dqkv[:, :, i].float().permute(0, 2, 1, 3), t.grad) < 2e-2, f"d{'qkv'[i]}"
+    assert rel_err(dbias, dqkv.float().reshape(Bn * T, -1).sum(0)) < 3e-3
+    # another (seed, offset) gives another mask
+    out2 = torch.empty_like(out)
+    K.attention_fwd(qkv, out2, lse, Bn, T, H, hd, scale, p, seed, offset + 1)
+    assert rel_err(out2, out) > 0.05
+
+
 @pytest.mark.parametrize("Bn,C", [(32, 3), (256, 1000), (7, 10)])
 def test_head_and_ce(Bn, C):
     g = torch.Generator().manual_seed(9)

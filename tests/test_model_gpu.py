@@ -221,3 +221,31 @@ def test_vit_b16_logits_vs_oracle():
     ref = O.vit_forward(X, sd, O.ViTConfig(num_classes=3, mlp_dropout=0.0, embedding_dropout=0.0))
     out = m.to(dev()).train()(X.to(dev()))
     assert rel_err(out, ref) < BF16_TOL
+
+
+def test_attn_dropout_is_honoured(tiny):
+    """attn_dropout > 0 (reference ctor argument, models/vit.py:79,180): dropout on the attention probabilities in
+    training mode only; eval ignores it. (Mask-exact parity is tested at kernel level; the CPU generator's mask cannot
+    be reproduced on a GPU.)"""
+    sd = sub(tiny, "sd0/")
+    X = torch.from_numpy(tiny["X"]).to(dev())
+    y = torch.from_numpy(tiny["y"]).to(dev())
+    m0 = build_tiny(sd).eval()
+    m1 = build_tiny(sd, attn_dropout=0.3)
+    with torch.no_grad():
+        base = m0(X)
+        assert torch.equal(m1.eval()(X), base)                 # eval: no dropout
+    m1.train()
+    torch.manual_seed(1)
+    a = m1(X)
+    b = m1(X)
+    assert rel_err(a, base) > 1e-3 and rel_err(a, b) > 1e-4    # train: dropped, fresh mask per call
+    assert rel_err(a, base) < 0.5
+    loss = torch.nn.functional.cross_entropy(a, y)
+    loss.backward()
+    for n, p in m1.named_parameters():
+        assert p.grad is not None and torch.isfinite(p.grad).all(), n
+    # the mean over many masks approaches the un-dropped forward of the attention output (unbiased estimator)
+    with torch.no_grad():
+        acc = sum(m1(X) for _ in range(64)) / 64
+    assert rel_err(acc, base) < rel_err(a, base)
