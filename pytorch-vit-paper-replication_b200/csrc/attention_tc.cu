@@ -886,6 +886,8 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
     const uint32_t kv_ready = bar_base + 80u, kv_free = bar_base + 88u, dq_ready = bar_base + 96u, dq_free = bar_base + 104u;
     auto stat_free = [&](int s) { return bar_base + 112u + 8u * s; };
     const uint32_t tmem_slot = bar_base + 128u;
+    const uint32_t kv_started = bar_base + 144u;
+    auto ds_half = [&](int m) { return bar_base + 152u + 8u * m; };
     // optional fused in-projection bias gradient: per-CTA column sums of dQ | dK | dV, [3][H][64] fp32, flushed at the end
     float* sBias = reinterpret_cast<float*>(smem_raw - smem_u32(smem_raw) + bar_base + 256u);
     if (dbias != nullptr)
@@ -903,17 +905,19 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
         prefetch_tmap(&tmQKV);
         prefetch_tmap(&tmDO);
         mbar_init(full_bar, 1);
-        mbar_init(head_empty, 1);
+        mbar_init(head_empty, 2);       // "2": one commit per MMA-issuing warp
         for (int i = 0; i < 2; ++i) {
             mbar_init(stat_bar(i), 2);
-            mbar_init(stat_free(i), 1);
+            mbar_init(stat_free(i), 2);
             mbar_init(s_ready(i), 1);
             mbar_init(p_ready(i), 8);
             mbar_init(ds_free(i), 1);
+            mbar_init(ds_half(i), 8);
         }
-        mbar_init(kv_ready, 1);
+        mbar_init(kv_ready, 2);
         mbar_init(kv_free, 16);
-        mbar_init(dq_ready, 1);
+        mbar_init(kv_started, 1);
+        mbar_init(dq_ready, 2);
         mbar_init(dq_free, 16);
         fence_barrier_init();
     }
@@ -926,19 +930,98 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
     tc_fence_after();
     const uint32_t tmem = *tmem_slot_ptr;
 
-    if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
-            int it = 0;
-            for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
+    if (warp < 2) {
+        // ===================== two MMA issuers: warp 1 serves math group 0, warp 0 serves group 1 and issues the TMA loads ======
+        // One thread can only issue ~1 small UMMA per 100 cycles, and a head is ~140 of them: with a single issuer that is
+        // half of the head's time. All 32 lanes run the loop (uniform operands); one elected lane issues each instruction.
+        // Cross-issuer ordering: tcgen05.commit only tracks the MMAs of its own thread, so barriers that mean "all MMAs of
+        // the tile / head are done" (kv_ready, dq_ready, head_empty, stat_free) take one commit from EACH issuer; the
+        // issuer of a tile's first chunk (accumulate = 0 into dV/dK) signals kv_started, the other one waits for it;
+        // the dQ MMA waits until the other group's half of the dS tile is in shared memory (ds_half).
+        const int my_g = warp == 1 ? 0 : 1;
+        const uint32_t idesc2 = make_idesc_bf16(ATC_BM, 64, 0, 1);      // A from TMEM, B MN-major
+        const uint32_t idesc3 = make_idesc_bf16(ATC_BM, 64, 1, 1);      // A (dS) and B (K) both MN-major
+        const uint32_t acc = tmem + my_g * 128;
+        uint32_t n_p = 0;
+        uint32_t S0 = 0;                // global step counter at the start of the head
+        int it = 0;
+        for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it, S0 += nsteps) {
+            if (warp == 0) {
                 const int b = w / H, h = w % H;
                 mbar_wait(head_empty, (it & 1) ^ 1u);
-                mbar_arrive_expect_tx(full_bar, 4 * tile_bytes);
-                tma_load_4d(sQ, &tmQKV, full_bar, 0, 0, h, b);
-                tma_load_4d(sK, &tmQKV, full_bar, 0, 0, H + h, b);
-                tma_load_4d(sV, &tmQKV, full_bar, 0, 0, 2 * H + h, b);
-                tma_load_4d(sdO, &tmDO, full_bar, 0, 0, h, b);
+                if (lane == 0) {
+                    mbar_arrive_expect_tx(full_bar, 4 * tile_bytes);
+                    tma_load_4d(sQ, &tmQKV, full_bar, 0, 0, h, b);
+                    tma_load_4d(sK, &tmQKV, full_bar, 0, 0, H + h, b);
+                    tma_load_4d(sV, &tmQKV, full_bar, 0, 0, 2 * H + h, b);
+                    tma_load_4d(sdO, &tmDO, full_bar, 0, 0, h, b);
+                }
+                __syncwarp();
             }
+            mbar_wait(full_bar, it & 1);
+            tc_fence_after();
+            auto width = [&](int c) { return min(AT3_W, Nk - c * AT3_W); };
+            auto issue_1 = [&](int s) {        // S^T and dP^T of (my) step s into my group's chunk accumulators
+                const int t = s / nc, c = s % nc;
+                const uint32_t xo = (uint32_t)t * (ATC_BM * 128), yo = (uint32_t)c * (AT3_W * 128);
+                const uint32_t idesc1 = make_idesc_bf16(ATC_BM, width(c), 0, 0);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    umma_bf16_ss_elect(acc, make_smem_desc_sw128(sK + xo + k * 32, 1024, 0),
+                                       make_smem_desc_sw128(sQ + yo + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
+                    umma_bf16_ss_elect(acc + 64, make_smem_desc_sw128(sV + xo + k * 32, 1024, 0),
+                                       make_smem_desc_sw128(sdO + yo + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
+                }
+                umma_commit_elect(s_ready(my_g));
+            };
+            const int s_first = ((S0 & 1u) == (uint32_t)my_g) ? 0 : 1;
+            if (s_first < nsteps) issue_1(s_first);
+            bool dq_waited = false;
+            for (int t = 0; t < nt; ++t) {
+                const uint32_t tile_idx = (uint32_t)it * nt + t;        // key tiles so far, all heads
+                bool first_mine = true;
+                for (int c = 0; c < nc; ++c) {
+                    const int s = t * nc + c;
+                    if (((S0 + s) & 1u) != (uint32_t)my_g) continue;
+                    mbar_wait(p_ready(my_g), n_p & 1u);
+                    ++n_p;
+                    if (c == 0) mbar_wait(kv_free, (tile_idx & 1u) ^ 1u);       // the previous tile's dV / dK have been read out
+                    else if (first_mine) mbar_wait(kv_started, tile_idx & 1u);  // ... and this tile's were zero-initialised
+                    first_mine = false;
+                    tc_fence_after();
+                    const uint32_t yo = (uint32_t)c * (AT3_W * 128);
+                    const int ksteps = width(c) / 16;
+                    for (int k = 0; k < ksteps; ++k) {
+                        const uint32_t acol = k < 2 ? 8 * k : 32 + 8 * (k - 2);
+                        const uint32_t accf = (c > 0 || k > 0) ? 1u : 0u;
+                        umma_bf16_ts_elect(tmem + 256, acc + acol, make_smem_desc_sw128(sdO + yo + k * 2048, 1024, 0), idesc2, accf);
+                        umma_bf16_ts_elect(tmem + 320, acc + 64 + acol, make_smem_desc_sw128(sQ + yo + k * 2048, 1024, 0), idesc2, accf);
+                    }
+                    if (c == 0 && nc > 1 && lane == 0) mbar_arrive(kv_started);
+                    if (c + 2 >= nc) umma_commit_elect(kv_ready);               // my last chunk of this tile
+                    if ((c & 1) || c == nc - 1) {
+                        // both chunks of query tile m are in shared memory: dQ_m (+)= dS[m] K_t over this tile's keys
+                        const int m = c >> 1;
+                        if (c & 1) mbar_wait(ds_half(m), tile_idx & 1u);        // the other group's chunk 2m
+                        if (t == 0 && !dq_waited) {                             // the previous head's dQ has been read out
+                            mbar_wait(dq_free, (it & 1) ^ 1u);
+                            dq_waited = true;
+                        }
+                        tc_fence_after();
+                        const int keys = min(ATC_BM, Nk - t * ATC_BM);
+                        const uint32_t sA = ds_base + (uint32_t)m * 32768u, sB = sK + (uint32_t)t * (ATC_BM * 128);
+                        for (int k = 0; k < keys / 16; ++k)
+                            umma_bf16_ss_elect(tmem + 384 + 64 * m, make_smem_desc_sw128(sA + k * 2048, 1024, 16384),
+                                               make_smem_desc_sw128(sB + k * 2048, 1024, 0), idesc3, (t > 0 || k > 0) ? 1u : 0u);
+                        umma_commit_elect(ds_free(m));
+                    }
+                    if (s + 2 < nsteps) issue_1(s + 2);
+                }
+                if (first_mine) umma_commit_elect(kv_ready);    // no chunk of this tile was mine (single-chunk tiles)
+            }
+            umma_commit_elect(dq_ready);
+            umma_commit_elect(head_empty);
+            umma_commit_elect(stat_free(it & 1));
         }
         __syncwarp();
     } else if (warp >= 18) {
@@ -981,76 +1064,6 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
             __syncwarp();
             if (lane == 0) mbar_arrive(stat_bar(stage));
         }
-    } else if (warp == 1) {
-        // ===================== MMA issuer: all 32 lanes run the loop, one elected lane issues =====================
-        {
-            const uint32_t idesc2 = make_idesc_bf16(ATC_BM, 64, 0, 1);      // A from TMEM, B MN-major
-            const uint32_t idesc3 = make_idesc_bf16(ATC_BM, 64, 1, 1);      // A (dS) and B (K) both MN-major
-            uint32_t n_p[2] = {0, 0};
-            uint32_t n_tiles = 0;           // key tiles whose dV/dK MMAs have started so far (all heads)
-            uint32_t S0 = 0;                // global step counter at the start of the head
-            int it = 0;
-            for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it, S0 += nsteps) {
-                mbar_wait(full_bar, it & 1);
-                tc_fence_after();
-                auto width = [&](int c) { return min(AT3_W, Nk - c * AT3_W); };
-                auto issue_1 = [&](int s) {        // S^T and dP^T of step s into the chunk accumulators of its group
-                    const int t = s / nc, c = s % nc, g = (S0 + s) & 1;
-                    const uint32_t acc = tmem + g * 128;
-                    const uint32_t xo = (uint32_t)t * (ATC_BM * 128), yo = (uint32_t)c * (AT3_W * 128);
-                    const uint32_t idesc1 = make_idesc_bf16(ATC_BM, width(c), 0, 0);
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        umma_bf16_ss_elect(acc, make_smem_desc_sw128(sK + xo + k * 32, 1024, 0),
-                                     make_smem_desc_sw128(sQ + yo + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
-                        umma_bf16_ss_elect(acc + 64, make_smem_desc_sw128(sV + xo + k * 32, 1024, 0),
-                                     make_smem_desc_sw128(sdO + yo + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
-                    }
-                    umma_commit_elect(s_ready(g));
-                };
-                issue_1(0);
-                if (nsteps > 1) issue_1(1);
-                for (int s = 0; s < nsteps; ++s) {
-                    const int t = s / nc, c = s % nc, g = (S0 + s) & 1;
-                    const uint32_t acc = tmem + g * 128;
-                    mbar_wait(p_ready(g), n_p[g] & 1u);
-                    ++n_p[g];
-                    if (c == 0) {           // the previous tile's dV / dK must have been read out
-                        mbar_wait(kv_free, (n_tiles & 1u) ^ 1u);
-                        ++n_tiles;
-                    }
-                    tc_fence_after();
-                    const uint32_t yo = (uint32_t)c * (AT3_W * 128);
-                    const int ksteps = width(c) / 16;
-                    for (int k = 0; k < ksteps; ++k) {
-                        const uint32_t acol = k < 2 ? 8 * k : 32 + 8 * (k - 2);
-                        const uint32_t accf = (c > 0 || k > 0) ? 1u : 0u;
-                        umma_bf16_ts_elect(tmem + 256, acc + acol, make_smem_desc_sw128(sdO + yo + k * 2048, 1024, 0), idesc2, accf);
-                        umma_bf16_ts_elect(tmem + 320, acc + 64 + acol, make_smem_desc_sw128(sQ + yo + k * 2048, 1024, 0), idesc2, accf);
-                    }
-                    if ((c & 1) || c == nc - 1) {
-                        // both chunks of query tile m are in shared memory: dQ_m (+)= dS[m] K_t over this tile's keys
-                        const int m = c >> 1;
-                        if (t == 0 && m == 0) {         // the previous head's dQ must have been read out
-                            mbar_wait(dq_free, (it & 1) ^ 1u);
-                            tc_fence_after();
-                        }
-                        const int keys = min(ATC_BM, Nk - t * ATC_BM);
-                        const uint32_t sA = ds_base + (uint32_t)m * 32768u, sB = sK + (uint32_t)t * (ATC_BM * 128);
-                        for (int k = 0; k < keys / 16; ++k)
-                            umma_bf16_ss_elect(tmem + 384 + 64 * m, make_smem_desc_sw128(sA + k * 2048, 1024, 16384),
-                                         make_smem_desc_sw128(sB + k * 2048, 1024, 0), idesc3, (t > 0 || k > 0) ? 1u : 0u);
-                        umma_commit_elect(ds_free(m));
-                    }
-                    if (c == nc - 1) umma_commit_elect(kv_ready);
-                    if (s + 2 < nsteps) issue_1(s + 2);
-                }
-                umma_commit_elect(dq_ready);
-                umma_commit_elect(head_empty);
-                umma_commit_elect(stat_free(it & 1));
-            }
-        }
-        __syncwarp();
     } else {
         // ===================== math + read-out groups =====================
         const int sw = warp - 2;
@@ -1156,7 +1169,10 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
                 tmem_st_wait();
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(p_ready(g));
+                if (lane == 0) {
+                    mbar_arrive(p_ready(g));
+                    if (!(c & 1) && c + 1 < nc) mbar_arrive(ds_half(m));     // first half of dS tile m is in shared memory
+                }
                 if (pending_tile >= 0) {
                     read_out_kv(pending_tile);
                     pending_tile = -1;
