@@ -101,6 +101,27 @@ def _zeros(shape, like: torch.Tensor) -> torch.Tensor:
     return torch.zeros(shape, dtype=torch.float32, device=like.device)
 
 
+class _ZeroArena:
+    """One zero-filled fp32 allocation carved into the accumulate-into buffers of a backward node (split-K weight
+    gradients, atomically accumulated bias gradients): one fill launch instead of one per buffer. Each piece starts
+    on a 256-byte boundary."""
+
+    def __init__(self, like: torch.Tensor, shapes):
+        self._views = []
+        offs, total = [], 0
+        for shp in shapes:
+            n = 1
+            for v in shp:
+                n *= int(v)
+            offs.append((total, n, shp))
+            total += (n + 63) // 64 * 64
+        flat = torch.zeros(total, dtype=torch.float32, device=like.device)
+        self._views = [flat[o:o + n].view(shp) for o, n, shp in offs]
+
+    def take(self) -> torch.Tensor:
+        return self._views.pop(0)
+
+
 # ---------------------------------------------------------------------------------------------------------
 # Patch embedding  (reference PatchEmbedding.forward, models/vit.py:45-67)
 # ---------------------------------------------------------------------------------------------------------
@@ -168,7 +189,7 @@ def _msa_forward(x2d, bn, t, heads, ln_w, ln_b, w_in16, b_in, w_out16, b_out, re
 
 
 def _msa_backward(g, saved, bn, t, heads, ln_w, w_in16, w_out16, has_residual, g16=None, db_out=None,
-                  adrop=(0.0, (0, 0))):
+                  adrop=(0.0, (0, 0)), arena=None):
     x2d, mean, rstd, ln, qkv, o, lse = saved
     r, d = x2d.shape
     dev = x2d.device
@@ -176,7 +197,9 @@ def _msa_backward(g, saved, bn, t, heads, ln_w, w_in16, w_out16, has_residual, g
         g16 = _empty((r, d), torch.bfloat16, x2d)
         db_out = _empty((d,), torch.float32, x2d)
         K.dropout_cast(g, g16, db_out, r, d, 0.0, 0, 0)
-    dw_out = _zeros((d, d), x2d)
+    if arena is None:
+        arena = _ZeroArena(x2d, [(d, d), (3 * d, d)])
+    dw_out = arena.take()
     K.gemm(K.OP_TN, K.EPI_ACCUM, d, d, r, g16, d, o, d, dw_out, d, split_k=K.split_k_for(d, d, r, dev))
     do = _empty((r, d), torch.bfloat16, x2d)
     K.gemm(K.OP_NN, K.EPI_BF16, r, d, d, g16, d, w_out16, d, do, d)
@@ -185,7 +208,7 @@ def _msa_backward(g, saved, bn, t, heads, ln_w, w_in16, w_out16, has_residual, g
     db_in = _empty((3 * d,), torch.float32, x2d)       # in_proj_bias gradient: column sums of dqkv, from the same kernel
     K.attention_bwd(qkv, o, do, lse, delta, dqkv, bn, t, heads, HEAD_DIM, 1.0 / math.sqrt(HEAD_DIM), dbias=db_in,
                     dropout_p=adrop[0], seed=adrop[1][0], offset=adrop[1][1])
-    dw_in = _zeros((3 * d, d), x2d)
+    dw_in = arena.take()
     K.gemm(K.OP_TN, K.EPI_ACCUM, 3 * d, d, r, dqkv, 3 * d, ln, d, dw_in, d, split_k=K.split_k_for(3 * d, d, r, dev))
     dln = _empty((r, d), torch.bfloat16, x2d)
     K.gemm(K.OP_NN, K.EPI_BF16, r, d, 3 * d, dqkv, 3 * d, w_in16, d, dln, d)
@@ -216,7 +239,7 @@ def _mlp_forward(x2d, ln_w, ln_b, w1_16, b1, w2_16, b2, p, residual, keep_preact
     return y, (x2d, mean, rstd, ln, a, h), (p, key1, key2)
 
 
-def _mlp_backward(g, saved, drop, ln_w, w1_16, w2_16, has_residual, want_bf16_out):
+def _mlp_backward(g, saved, drop, ln_w, w1_16, w2_16, has_residual, want_bf16_out, arena=None):
     x2d, mean, rstd, ln, a, h = saved
     p, key1, key2 = drop
     r, d = x2d.shape
@@ -225,13 +248,15 @@ def _mlp_backward(g, saved, drop, ln_w, w1_16, w2_16, has_residual, want_bf16_ou
     g16 = _empty((r, d), torch.bfloat16, x2d)
     db2 = _empty((d,), torch.float32, x2d)
     K.dropout_cast(g, g16, db2, r, d, p, key2[0], key2[1])
-    dw2 = _zeros((d, m), x2d)
+    if arena is None:
+        arena = _ZeroArena(x2d, [(d, m), (m,), (m, d)])
+    dw2 = arena.take()
     K.gemm(K.OP_TN, K.EPI_ACCUM, d, m, r, g16, d, h, m, dw2, m, split_k=K.split_k_for(d, m, r, dev))
     da = _empty((r, m), torch.bfloat16, x2d)
-    db1 = _zeros((m,), x2d)
+    db1 = arena.take()
     # a = mask * gelu'(pre-activation); the epilogue also accumulates the fc1 bias gradient (column sums of da) into db1
     K.gemm(K.OP_NN, K.EPI_DGELU, r, m, d, g16, d, w2_16, m, da, m, bias=db1, aux=a, ldaux=m)
-    dw1 = _zeros((m, d), x2d)
+    dw1 = arena.take()
     K.gemm(K.OP_TN, K.EPI_ACCUM, m, d, r, da, m, ln, d, dw1, d, split_k=K.split_k_for(m, d, r, dev))
     dln = g16  # reuse: g16 is dead after the two GEMMs above (same shape / dtype)
     K.gemm(K.OP_NN, K.EPI_BF16, r, d, m, da, m, w1_16, d, dln, d)
@@ -330,11 +355,13 @@ class EncoderBlockFn(torch.autograd.Function):
         s_msa, s_mlp = tuple(rest[:n_msa]), tuple(rest[n_msa:])
         d = g.shape[-1]
         g2 = _f32c(g).view(bn * t, d)
+        m = w1_16.shape[0]
+        arena = _ZeroArena(g2, [(d, m), (m,), (m, d), (d, d), (3 * d, d)])     # in the order the helpers take them
         g1, (m_dgam, m_dbet, dw1, db1, dw2, db2), g1_16, db_out = _mlp_backward(
-            g2, s_mlp, ctx.drop, m_ln_w, w1_16, w2_16, has_residual=True, want_bf16_out=True)
+            g2, s_mlp, ctx.drop, m_ln_w, w1_16, w2_16, has_residual=True, want_bf16_out=True, arena=arena)
         g0, (a_dgam, a_dbet, dw_in, db_in, dw_out, db_out) = _msa_backward(
             g1, s_msa, bn, t, heads, a_ln_w, w_in16, w_out16, has_residual=True, g16=g1_16, db_out=db_out,
-            adrop=ctx.adrop)
+            adrop=ctx.adrop, arena=arena)
         return (g0.view(bn, t, d), a_dgam, a_dbet, dw_in, db_in, dw_out, db_out, m_dgam, m_dbet, dw1, db1, dw2, db2,
                 None, None, None, None, None, None, None, None)
 
