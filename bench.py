@@ -322,7 +322,7 @@ def main():
     opt = FusedAdam([{"params": decay, "weight_decay": 0.03}, {"params": no_decay, "weight_decay": 0.0}], lr=1e-3)
     if world > 1:
         opt.grad_scale = net.grad_scale
-    total = 2 * (W + K_steps) + 8
+    total = 3 * (W + K_steps) + 12
     warm_n = int(0.05 * total)
     sched = torch.optim.lr_scheduler.SequentialLR(opt, schedulers=[
         torch.optim.lr_scheduler.LinearLR(opt, start_factor=1e-6, end_factor=1.0, total_iters=max(1, warm_n)),
@@ -380,6 +380,17 @@ def main():
     h2d = B * 3 * 224 * 224 * 4 + B * 8
     d2h = 8
 
+    # the same with uint8 host images (the reference's ToDtype(float32, scale=True) moved onto the device): informational
+    host_u8 = [((x * 255).to(torch.uint8).pin_memory(), y) for x, y in host]
+    engine.train_step(net, [host_u8[i % n_pool] for i in range(2)], loss_fn, opt, sched, dev)
+    barrier()
+    e0.record()
+    engine.train_step(net, [host_u8[i % n_pool] for i in range(K_steps)], loss_fn, opt, sched, dev)
+    e1.record()
+    barrier()
+    ms_u8 = max_over_ranks(e0.elapsed_time(e1))
+    del host_u8
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -411,6 +422,8 @@ def main():
                 "vs_measured_sustained": round(tflops / world / peaks["bf16_tflops_sustained"], 4) if "bf16_tflops_sustained" in peaks else None},
         "e2e": {"value": round(e2e_value, 1), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": round(ms_e2e / K_steps, 3)},
+        "e2e_uint8_images": {"value": round(world * B * K_steps / (ms_u8 / 1e3), 1), "unit": UNIT,
+                             "h2d_bytes_per_step": B * 3 * 224 * 224 + B * 8, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": roof,

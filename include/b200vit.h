@@ -71,6 +71,12 @@ int b200vit_cast_f32_to_bf16(const float* src, void* dst_bf16, long long n, void
 int b200vit_im2col_patches(const float* image, void* patches_bf16, int batch, int channels, int height, int width,
                            int patch, void* stream);
 
+/* The same for uint8 images [B, C, H, W], converted to [0, 1] floats on the fly (value / 255): the reference's
+ * ToImage + ToDtype(torch.float32, scale=True) transform (08_pytorch_paper_replicating_self.ipynb:253-265) moved to
+ * the device, so a batch crosses PCIe as 1 byte per value instead of 4. */
+int b200vit_im2col_patches_u8(const unsigned char* image_u8, void* patches_bf16, int batch, int channels, int height,
+                              int width, int patch, void* stream);
+
 /* x[b, 0, :] = dropout(class_token + pos[0]) for every b; x is the f32 [B, T, D] embedded sequence whose patch
  * rows the PATCH GEMM epilogue writes.  Replaces expand + torch.cat + add + Dropout for the class row
  * (models/vit.py:50, 59, 63, 66). */

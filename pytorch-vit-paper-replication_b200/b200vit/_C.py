@@ -23,6 +23,7 @@ _SIGNATURES = {
     "b200vit_gemm": [_i, _i, _i, _i, _i, _p, _ll, _p, _ll, _p, _ll, _p, _ll, _p, _p, _ll, _f, _ull, _ull, _i, _i, _p],
     "b200vit_cast_f32_to_bf16": [_p, _p, _ll, _p],
     "b200vit_im2col_patches": [_p, _p, _i, _i, _i, _i, _i, _p],
+    "b200vit_im2col_patches_u8": [_p, _p, _i, _i, _i, _i, _i, _p],
     "b200vit_class_token_rows": [_p, _p, _p, _i, _i, _i, _f, _ull, _ull, _p],
     "b200vit_embed_param_grads": [_p, _p, _p, _p, _i, _i, _i, _f, _ull, _ull, _p],
     "b200vit_patch_grad_rows": [_p, _p, _i, _i, _i, _f, _ull, _ull, _p],

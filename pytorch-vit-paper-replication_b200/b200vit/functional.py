@@ -129,7 +129,9 @@ class PatchEmbedFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, img, w, b, cls, pos, w16, patch: int, p_drop: float, training: bool):
         _require_cuda(img, "PatchEmbedding")
-        img = _f32c(img)
+        # uint8 images are accepted as they are (converted to [0, 1] inside the im2col kernel: the reference's
+        # ToDtype(float32, scale=True) on the device, a 4x smaller host->device copy); anything else becomes fp32
+        img = img.contiguous() if img.dtype == torch.uint8 else _f32c(img)
         bn, c, h, wd = img.shape
         d = w.shape[0]
         np_ = (h // patch) * (wd // patch)

@@ -74,10 +74,13 @@ def cast_bf16(src: torch.Tensor, dst: Optional[torch.Tensor] = None) -> torch.Te
 
 
 def im2col_patches(image: torch.Tensor, patch: int) -> torch.Tensor:
-    _chk(image, torch.float32, "image")
+    """image: float32 [B, C, H, W], or uint8 [B, C, H, W] (scaled by 1/255 on the fly)."""
+    u8 = image.dtype == torch.uint8
+    _chk(image, torch.uint8 if u8 else torch.float32, "image")
     b, c, h, w = image.shape
     out = torch.empty((b * (h // patch) * (w // patch), c * patch * patch), dtype=torch.bfloat16, device=image.device)
-    _C.call("b200vit_im2col_patches", _ptr(image), _ptr(out), b, c, h, w, patch, stream_ptr(image.device))
+    _C.call("b200vit_im2col_patches_u8" if u8 else "b200vit_im2col_patches", _ptr(image), _ptr(out), b, c, h, w, patch,
+            stream_ptr(image.device))
     return out
 
 

@@ -25,6 +25,10 @@ int b200vit_im2col_patches(const float* image, void* patches, int batch, int cha
                            int patch, void* stream) {
     return im2col_launch(image, (bf16*)patches, batch, channels, height, width, patch, (cudaStream_t)stream);
 }
+int b200vit_im2col_patches_u8(const unsigned char* image, void* patches, int batch, int channels, int height, int width,
+                              int patch, void* stream) {
+    return im2col_u8_launch(image, (bf16*)patches, batch, channels, height, width, patch, (cudaStream_t)stream);
+}
 
 int b200vit_class_token_rows(const float* class_token, const float* pos, float* x, int batch, int tokens, int dim,
                              float dropout_p, unsigned long long seed, unsigned long long offset, void* stream) {

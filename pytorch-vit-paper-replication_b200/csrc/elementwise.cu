@@ -65,6 +65,56 @@ __global__ void im2col_kernel(const float* __restrict__ img, bf16* __restrict__ 
     *reinterpret_cast<uint4*>(out + row * K + k) = o;
 }
 
+// Same re-index for uint8 images (NCHW), scaled to [0, 1] on the fly: the torchvision pipeline of the reference
+// (ToImage + ToDtype(float32, scale=True), 08_..._self.ipynb:253-265) applied on the device, so the host->device copy
+// moves 1 byte per pixel-channel instead of 4. value = u8 / 255 (exactly what ToDtype(scale=True) computes).
+__global__ void im2col_u8_kernel(const uint8_t* __restrict__ img, bf16* __restrict__ out, int B, int C, int H, int W,
+                                 int P, long long total8) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= total8) return;
+    const int Wp = W / P, Hp = H / P;
+    const int K = C * P * P;
+    const int k8 = K / 8;
+    const long long row = t / k8;
+    const int k = (int)(t % k8) * 8;
+    const int c = k / (P * P);
+    const int i = (k % (P * P)) / P;
+    const int j = k % P;
+    const int b = (int)(row / (Hp * Wp));
+    const int pp = (int)(row % (Hp * Wp));
+    const int py = pp / Wp, px = pp % Wp;
+    const uint8_t* src = img + (((long long)b * C + c) * H + (py * P + i)) * W + px * P + j;
+    const uint2 q = *reinterpret_cast<const uint2*>(src);
+    const float s = 1.0f / 255.0f;
+    float f[8];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        f[e] = (float)((q.x >> (8 * e)) & 0xFFu) * s;
+        f[4 + e] = (float)((q.y >> (8 * e)) & 0xFFu) * s;
+    }
+    uint4 o;
+    o.x = pack_bf16(f[0], f[1]); o.y = pack_bf16(f[2], f[3]);
+    o.z = pack_bf16(f[4], f[5]); o.w = pack_bf16(f[6], f[7]);
+    *reinterpret_cast<uint4*>(out + row * K + k) = o;
+}
+
+int im2col_u8_launch(const uint8_t* image, bf16* patches, int batch, int channels, int height, int width, int patch,
+                     cudaStream_t stream) {
+    B200_CHECK_ARG(image && patches, "im2col: null pointer");
+    B200_CHECK_ARG(batch > 0 && channels > 0 && patch > 0, "im2col: bad sizes");
+    B200_CHECK_ARG(height % patch == 0 && width % patch == 0, "im2col: image %dx%d not divisible by patch %d", height,
+                   width, patch);
+    B200_CHECK_ARG(patch % 8 == 0 && width % 8 == 0, "im2col: patch must be a multiple of 8 (got %d)", patch);
+    B200_CHECK_ARG(((uintptr_t)image % 8) == 0 && ((uintptr_t)patches % 16) == 0, "im2col: unaligned pointer");
+    const long long rows = (long long)batch * (height / patch) * (width / patch);
+    const long long total8 = rows * (channels * patch * patch / 8);
+    const int block = 256;
+    im2col_u8_kernel<<<(unsigned)((total8 + block - 1) / block), block, 0, stream>>>(image, patches, batch, channels,
+                                                                                    height, width, patch, total8);
+    B200_LAUNCH_CHECK();
+    return 0;
+}
+
 int im2col_launch(const float* image, bf16* patches, int batch, int channels, int height, int width, int patch,
                   cudaStream_t stream) {
     B200_CHECK_ARG(image && patches, "im2col: null pointer");

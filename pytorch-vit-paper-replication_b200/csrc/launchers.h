@@ -12,6 +12,8 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
 int cast_f32_bf16_launch(const float* src, bf16* dst, long long n, cudaStream_t stream);
 int im2col_launch(const float* image, bf16* patches, int batch, int channels, int height, int width, int patch,
                   cudaStream_t stream);
+int im2col_u8_launch(const uint8_t* image, bf16* patches, int batch, int channels, int height, int width, int patch,
+                     cudaStream_t stream);
 int cls_rows_launch(const float* cls, const float* pos, float* x, int batch, int tokens, int dim, float drop_p,
                     unsigned long long seed, unsigned long long offset, cudaStream_t stream);
 int embed_grads_launch(const float* gx, float* g_cls, float* g_pos, float* g_bias, int batch, int tokens, int dim,

@@ -249,3 +249,20 @@ def test_attn_dropout_is_honoured(tiny):
     with torch.no_grad():
         acc = sum(m1(X) for _ in range(64)) / 64
     assert rel_err(acc, base) < rel_err(a, base)
+
+
+def test_uint8_images_equal_scaled_float_images(tiny):
+    """uint8 input: the device-side /255 of the im2col kernel equals ToDtype(float32, scale=True)."""
+    sd = sub(tiny, "sd0/")
+    m = build_tiny(sd).eval()
+    g = torch.Generator().manual_seed(4)
+    xu8 = torch.randint(0, 256, (3, 3, TINY["image_size"], TINY["image_size"]), dtype=torch.uint8, generator=g)
+    with torch.no_grad():
+        a = m(xu8.to(dev()))
+        b = m((xu8.float() / 255.0).to(dev()))
+    assert torch.equal(a, b)
+    # and it trains: gradients flow to the patch-embedding weights
+    m.train()
+    loss = m(xu8.to(dev())).square().mean()
+    loss.backward()
+    assert torch.isfinite(m.patch_embedding_block.patch_and_flatten[0].weight.grad).all()
