@@ -56,6 +56,7 @@ class FusedAdam(torch.optim.Optimizer):
         self._max_size = 0
         self._num = 0
         self.grad_scale = 1.0
+        self._shared_step = None
 
     # -- tensor tables -------------------------------------------------------------------------------
     def _active(self):
@@ -72,7 +73,14 @@ class FusedAdam(torch.optim.Optimizer):
     def _ensure_state(self, p):
         st = self.state[p]
         if len(st) == 0:
-            st["step"] = torch.tensor(0.0, dtype=torch.float32)
+            # parameters whose state is created before the first step share ONE step tensor (advanced once per step
+            # instead of once per parameter); a parameter that joins later gets its own, as in torch.optim.Adam
+            if self._shared_step is None:
+                self._shared_step = torch.tensor(0.0, dtype=torch.float32)
+            if float(self._shared_step) == 0.0:
+                st["step"] = self._shared_step
+            else:
+                st["step"] = torch.tensor(0.0, dtype=torch.float32)
             st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
             st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
         return st
@@ -170,9 +178,18 @@ class FusedAdam(torch.optim.Optimizer):
         K.adam_step(self._table_dev, self._num, self._max_size, [g["lr"] for g in self.param_groups],
                     [g["weight_decay"] for g in self.param_groups], g0["betas"][0], g0["betas"][1], g0["eps"], step,
                     g0["decoupled_weight_decay"], sumsq, max_norm if max_norm else 0.0, self.grad_scale)
+        shared = self._shared_step
+        shared_bumped = False
         for _, p in items:
-            self.state[p]["step"] += 1
-            torch.autograd.graph.increment_version(p)   # the kernel wrote p behind autograd's back
+            st_step = self.state[p]["step"]
+            if st_step is shared:
+                if not shared_bumped:
+                    shared += 1
+                    shared_bumped = True
+            else:
+                st_step += 1
+        torch.autograd.graph.increment_version([p for _, p in items])   # the kernel wrote p behind autograd's back
+        for _, p in items:
             sh = F_.shadow_entry(p)
             if sh is not None:
                 sh.version = p._version                 # ... and refreshed its bf16 shadow in the same pass
