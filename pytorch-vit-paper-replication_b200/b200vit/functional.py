@@ -171,6 +171,36 @@ class PatchEmbedFn(torch.autograd.Function):
 # ---------------------------------------------------------------------------------------------------------
 # MSA / MLP halves of an encoder block (reference models/vit.py:92-98, 128-131, 166-169)
 # ---------------------------------------------------------------------------------------------------------
+# ---------------------------------------------------------------------------------------------------------
+# Cross-block hand-over in the backward pass. The gradient leaving encoder block i+1 (fp32 residual-stream gradient,
+# written by the LayerNorm backward of its attention half) is consumed by block i's MLP backward, which first needs
+# bf16(dropout_mask_i * g) and its column sums (fc2 backward operands; the Dropout of models/vit.py:125). The
+# LayerNorm backward kernel can emit both in the pass that writes g, sparing a 3-pass elementwise kernel per layer.
+# The two blocks are separate autograd nodes, so the hand-over is keyed by the storage address of g:
+#   forward : block i records (address of its output, its fc2-dropout p and key); block i+1, whose input is that
+#             very tensor, picks the triple up;
+#   backward: block i+1 emits the extra outputs with block i's mask and files them under g's address; block i looks
+#             its incoming gradient up and falls back to the stand-alone kernel if anything does not match (another
+#             consumer, a hook that modified g, a different mask).
+# ---------------------------------------------------------------------------------------------------------
+_LAST_BLOCK_OUT = None      # (data_ptr of the block's output, p, (seed, offset))
+_GRAD_SIDE: dict = {}       # data_ptr of g -> (g16, colsum, p, (seed, offset), version of g)
+
+
+def _note_block_output(y: torch.Tensor, p: float, key) -> None:
+    global _LAST_BLOCK_OUT
+    _LAST_BLOCK_OUT = (y.data_ptr(), float(p), tuple(key))
+
+
+def _producer_dropout(x: torch.Tensor):
+    """(p, key) of the encoder block that produced x, if x is that block's output tensor; else None."""
+    global _LAST_BLOCK_OUT
+    rec, _LAST_BLOCK_OUT = _LAST_BLOCK_OUT, None        # one consumer per record; a stale address must not match later
+    if rec is not None and rec[0] == x.data_ptr():
+        return rec[1], rec[2]
+    return None
+
+
 def _msa_forward(x2d, bn, t, heads, ln_w, ln_b, w_in16, b_in, w_out16, b_out, residual, attn_p=0.0):
     r, d = x2d.shape
     if d != heads * HEAD_DIM:
@@ -191,7 +221,7 @@ def _msa_forward(x2d, bn, t, heads, ln_w, ln_b, w_in16, b_in, w_out16, b_out, re
 
 
 def _msa_backward(g, saved, bn, t, heads, ln_w, w_in16, w_out16, has_residual, g16=None, db_out=None,
-                  adrop=(0.0, (0, 0)), arena=None):
+                  adrop=(0.0, (0, 0)), arena=None, consumer_drop=None):
     x2d, mean, rstd, ln, qkv, o, lse = saved
     r, d = x2d.shape
     dev = x2d.device
@@ -217,8 +247,19 @@ def _msa_backward(g, saved, bn, t, heads, ln_w, w_in16, w_out16, has_residual, g
     gx = _empty((r, d), torch.float32, x2d)
     dgamma = _empty((d,), torch.float32, x2d)
     dbeta = _empty((d,), torch.float32, x2d)
-    K.layernorm_bwd(dln, None, x2d, d, mean, rstd, ln_w, g if has_residual else None, gx, d, None, dgamma, dbeta,
-                    None, r, d)
+    if consumer_drop is None:
+        K.layernorm_bwd(dln, None, x2d, d, mean, rstd, ln_w, g if has_residual else None, gx, d, None, dgamma, dbeta,
+                        None, r, d)
+    else:
+        # also emit what the previous block's MLP backward needs first: bf16(mask * gx) with ITS fc2-dropout mask
+        cp, ckey = consumer_drop
+        gx16 = _empty((r, d), torch.bfloat16, x2d)
+        dbn = _empty((d,), torch.float32, x2d)
+        K.layernorm_bwd(dln, None, x2d, d, mean, rstd, ln_w, g if has_residual else None, gx, d, gx16, dgamma, dbeta,
+                        dbn, r, d, cp, ckey[0], ckey[1])
+        if len(_GRAD_SIDE) > 64:        # never consumed (a graph that was not run to the end): do not grow
+            _GRAD_SIDE.clear()
+        _GRAD_SIDE[gx.data_ptr()] = (gx16, dbn, cp, ckey, gx._version)
     return gx, (dgamma, dbeta, dw_in, db_in, dw_out, db_out)
 
 
@@ -247,9 +288,14 @@ def _mlp_backward(g, saved, drop, ln_w, w1_16, w2_16, has_residual, want_bf16_ou
     r, d = x2d.shape
     m = w1_16.shape[0]
     dev = x2d.device
-    g16 = _empty((r, d), torch.bfloat16, x2d)
-    db2 = _empty((d,), torch.float32, x2d)
-    K.dropout_cast(g, g16, db2, r, d, p, key2[0], key2[1])
+    side = _GRAD_SIDE.pop(g.data_ptr(), None)
+    if side is not None and side[2] == p and side[3] == tuple(key2) and side[4] == g._version and \
+            side[0].shape == (r, d):
+        g16, db2 = side[0], side[1]     # produced by the next block's LayerNorm backward together with g
+    else:
+        g16 = _empty((r, d), torch.bfloat16, x2d)
+        db2 = _empty((d,), torch.float32, x2d)
+        K.dropout_cast(g, g16, db2, r, d, p, key2[0], key2[1])
     if arena is None:
         arena = _ZeroArena(x2d, [(d, m), (m,), (m, d)])
     dw2 = arena.take()
@@ -339,6 +385,7 @@ class EncoderBlockFn(torch.autograd.Function):
         bn, t, d = x.shape
         x2d = x.view(bn * t, d)
         needs_bwd = any(ctx.needs_input_grad)
+        ctx.consumer_drop = _producer_dropout(x) if needs_bwd else None      # see "cross-block hand-over" above
         x1, s_msa, adrop = _msa_forward(x2d, bn, t, heads, a_ln_w, a_ln_b, w_in16, b_in, w_out16, b_out, x2d,
                                         float(attn_p) if training else 0.0)
         x2, s_mlp, drop = _mlp_forward(x1, m_ln_w, m_ln_b, w1_16, b1, w2_16, b2, float(p) if training else 0.0, x1,
@@ -348,7 +395,10 @@ class EncoderBlockFn(torch.autograd.Function):
         ctx.meta = (bn, t, heads, len(s_msa))
         ctx.drop = drop
         ctx.adrop = adrop
-        return x2.view(bn, t, d)
+        out = x2.view(bn, t, d)
+        if needs_bwd:
+            _note_block_output(out, drop[0], drop[2])
+        return out
 
     @staticmethod
     def backward(ctx, g):
@@ -363,7 +413,7 @@ class EncoderBlockFn(torch.autograd.Function):
             g2, s_mlp, ctx.drop, m_ln_w, w1_16, w2_16, has_residual=True, want_bf16_out=True, arena=arena)
         g0, (a_dgam, a_dbet, dw_in, db_in, dw_out, db_out) = _msa_backward(
             g1, s_msa, bn, t, heads, a_ln_w, w_in16, w_out16, has_residual=True, g16=g1_16, db_out=db_out,
-            adrop=ctx.adrop, arena=arena)
+            adrop=ctx.adrop, arena=arena, consumer_drop=ctx.consumer_drop)
         return (g0.view(bn, t, d), a_dgam, a_dbet, dw_in, db_in, dw_out, db_out, m_dgam, m_dbet, dw1, db1, dw2, db2,
                 None, None, None, None, None, None, None, None)
 
