@@ -186,9 +186,15 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
                 if (HAS_NEXT) {
                     float v[4] = {o.x, o.y, o.z, o.w};
                     if (drop.p > 0.f) {
+                        // elements e0 .. e0+3 (e0 % 4 == 0) sit in two consecutive 32-bit words of one mask block:
+                        // two hashes per float4 instead of one per element (same decisions as dropout_mult1)
                         const unsigned long long e0 = (unsigned long long)row * D + 4ull * i;
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) v[j] *= dropout_mult1(drop, e0 + j);
+                        const uint32_t j0 = (uint32_t)(e0 & 7) >> 1;
+                        const uint32_t w0 = dropout_word(drop, e0 >> 3, j0), w1 = dropout_word(drop, e0 >> 3, j0 + 1);
+                        v[0] *= ((w0 & 0x7FFFu) >= drop.thr15) ? drop.scale : 0.f;
+                        v[1] *= (((w0 >> 16) & 0x7FFFu) >= drop.thr15) ? drop.scale : 0.f;
+                        v[2] *= ((w1 & 0x7FFFu) >= drop.thr15) ? drop.scale : 0.f;
+                        v[3] *= (((w1 >> 16) & 0x7FFFu) >= drop.thr15) ? drop.scale : 0.f;
                     }
                     uint2 pk;
                     pk.x = pack_bf16(v[0], v[1]);
