@@ -206,13 +206,45 @@ __global__ void patch_grad_rows_kernel(const float* __restrict__ gx, bf16* __res
     gy[i] = __float2bfloat16(v);
 }
 
+// 8 elements per thread (D % 8 == 0, 16-byte aligned pointers): two float4 loads, one mask block, one 16-byte store
+__global__ void patch_grad_rows_vec8_kernel(const float* __restrict__ gx, bf16* __restrict__ gy, int B, int T, int D,
+                                            DropoutParams drop, long long total8) {
+    const long long i8 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i8 >= total8) return;
+    const int d8 = D >> 3;
+    const int d = (int)(i8 % d8) * 8;
+    const long long r = i8 / d8;
+    const int b = (int)(r / (T - 1));
+    const int t = (int)(r % (T - 1)) + 1;
+    const unsigned long long e = ((unsigned long long)b * T + t) * D + d;
+    const float4 a = *reinterpret_cast<const float4*>(gx + e);
+    const float4 c = *reinterpret_cast<const float4*>(gx + e + 4);
+    float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+    if (drop.p > 0.f) {
+        float m[8];
+        dropout_mult8(drop, e >> 3, m);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] *= m[j];
+    }
+    uint4 o;
+    o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]);
+    o.z = pack_bf16(v[4], v[5]); o.w = pack_bf16(v[6], v[7]);
+    *reinterpret_cast<uint4*>(gy + r * D + d) = o;
+}
+
 int patch_grad_rows_launch(const float* gx, bf16* gy, int batch, int tokens, int dim, float drop_p,
                            unsigned long long seed, unsigned long long offset, cudaStream_t stream) {
     B200_CHECK_ARG(gx && gy, "patch_grad_rows: null pointer");
     B200_CHECK_ARG(batch > 0 && tokens > 1 && dim > 0, "patch_grad_rows: bad sizes");
     const long long total = (long long)batch * (tokens - 1) * dim;
-    patch_grad_rows_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(gx, gy, batch, tokens, dim,
-                                                                               make_dropout(drop_p, seed, offset), total);
+    const DropoutParams drop = make_dropout(drop_p, seed, offset);
+    if ((dim & 7) == 0 && (((uintptr_t)gx) & 15) == 0 && (((uintptr_t)gy) & 15) == 0) {
+        const long long total8 = total / 8;
+        patch_grad_rows_vec8_kernel<<<(unsigned)((total8 + 255) / 256), 256, 0, stream>>>(gx, gy, batch, tokens, dim, drop,
+                                                                                         total8);
+    } else {
+        patch_grad_rows_kernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(gx, gy, batch, tokens, dim, drop, total);
+    }
     B200_LAUNCH_CHECK();
     return 0;
 }

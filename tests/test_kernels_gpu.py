@@ -309,3 +309,9 @@ def test_colsum_and_embed_grads():
     gy = torch.empty((Bn * (T - 1), D), dtype=torch.bfloat16, device=dev())
     K.patch_grad_rows(gx, gy, Bn, T, D, 0.0, 0, 0)
     assert torch.equal(gy.float(), gx[:, 1:].reshape(-1, D).to(torch.bfloat16).float())
+    # with the embedding dropout's mask: same mask as dropout_cast draws over the whole [B*T, D] tensor
+    p = 0.3
+    K.patch_grad_rows(gx, gy, Bn, T, D, p, 21, 4)
+    full = torch.empty((Bn * T, D), dtype=torch.bfloat16, device=dev())
+    K.dropout_cast(gx.reshape(Bn * T, D).contiguous(), full, None, Bn * T, D, p, 21, 4)
+    assert torch.equal(gy, full.reshape(Bn, T, D)[:, 1:].reshape(-1, D))
