@@ -349,13 +349,15 @@ class MLPFn(torch.autograd.Function):
     """MLPBlock.forward (models/vit.py:128-131): LN -> Linear -> GELU -> Dropout -> Linear -> Dropout."""
 
     @staticmethod
-    def forward(ctx, x, ln_w, ln_b, w1, b1, w2, b2, w1_16, w2_16, p: float, training: bool):
+    def forward(ctx, x, ln_w, ln_b, w1, b1, w2, b2, w1_16, w2_16, p: float, training: bool, grad_mode: bool = True):
+        # grad_mode: torch.is_grad_enabled() as seen by the CALLER (inside forward it is always False, and
+        # needs_input_grad stays True under no_grad / inference_mode): without it, inference would save activations
         _require_cuda(x, "MLPBlock")
         x = _f32c(x)
         shape = x.shape
         d = shape[-1]
         x2d = x.view(-1, d)
-        needs_bwd = any(ctx.needs_input_grad)
+        needs_bwd = bool(grad_mode) and any(ctx.needs_input_grad)
         y, saved, drop = _mlp_forward(x2d, ln_w, ln_b, w1_16, b1, w2_16, b2, float(p) if training else 0.0, None,
                                       keep_preact=needs_bwd)
         if needs_bwd:
@@ -370,7 +372,7 @@ class MLPFn(torch.autograd.Function):
         d = shape[-1]
         gx, (dgam, dbet, dw1, db1, dw2, db2), _, _ = _mlp_backward(
             _f32c(g).view(-1, d), tuple(saved), ctx.drop, ln_w, w1_16, w2_16, has_residual=False, want_bf16_out=False)
-        return gx.view(shape), dgam, dbet, dw1, db1, dw2, db2, None, None, None, None
+        return gx.view(shape), dgam, dbet, dw1, db1, dw2, db2, None, None, None, None, None
 
 
 class EncoderBlockFn(torch.autograd.Function):
@@ -379,12 +381,13 @@ class EncoderBlockFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, a_ln_w, a_ln_b, w_in, b_in, w_out, b_out, m_ln_w, m_ln_b, w1, b1, w2, b2,
-                w_in16, w_out16, w1_16, w2_16, heads: int, p: float, training: bool, attn_p: float = 0.0):
+                w_in16, w_out16, w1_16, w2_16, heads: int, p: float, training: bool, attn_p: float = 0.0,
+                grad_mode: bool = True):
         _require_cuda(x, "TransformerEncoderBlock")
         x = _f32c(x)
         bn, t, d = x.shape
         x2d = x.view(bn * t, d)
-        needs_bwd = any(ctx.needs_input_grad)
+        needs_bwd = bool(grad_mode) and any(ctx.needs_input_grad)
         ctx.consumer_drop = _producer_dropout(x) if needs_bwd else None      # see "cross-block hand-over" above
         x1, s_msa, adrop = _msa_forward(x2d, bn, t, heads, a_ln_w, a_ln_b, w_in16, b_in, w_out16, b_out, x2d,
                                         float(attn_p) if training else 0.0)
@@ -415,7 +418,7 @@ class EncoderBlockFn(torch.autograd.Function):
             g1, s_msa, bn, t, heads, a_ln_w, w_in16, w_out16, has_residual=True, g16=g1_16, db_out=db_out,
             adrop=ctx.adrop, arena=arena, consumer_drop=ctx.consumer_drop)
         return (g0.view(bn, t, d), a_dgam, a_dbet, dw_in, db_in, dw_out, db_out, m_dgam, m_dbet, dw1, db1, dw2, db2,
-                None, None, None, None, None, None, None, None)
+                None, None, None, None, None, None, None, None, None)
 
 
 # ---------------------------------------------------------------------------------------------------------

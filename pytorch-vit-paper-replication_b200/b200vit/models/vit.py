@@ -95,7 +95,7 @@ class MLPBlock(nn.Module):
         fc1, fc2 = self.mlp[0], self.mlp[3]
         return F_.MLPFn.apply(x, self.layer_norm.weight, self.layer_norm.bias, fc1.weight, fc1.bias, fc2.weight,
                               fc2.bias, F_.bf16_shadow(fc1.weight), F_.bf16_shadow(fc2.weight), self.mlp[2].p,
-                              self.training)
+                              self.training, torch.is_grad_enabled())
 
 
 class TransformerEncoderBlock(nn.Module):
@@ -121,7 +121,7 @@ class TransformerEncoderBlock(nn.Module):
             mha.out_proj.weight, mha.out_proj.bias, mlp.layer_norm.weight, mlp.layer_norm.bias, fc1.weight, fc1.bias,
             fc2.weight, fc2.bias, F_.bf16_shadow(mha.in_proj_weight), F_.bf16_shadow(mha.out_proj.weight),
             F_.bf16_shadow(fc1.weight), F_.bf16_shadow(fc2.weight), mha.num_heads, mlp.mlp[2].p, self.training,
-            mha.dropout)
+            mha.dropout, torch.is_grad_enabled())
 
 
 class ViT(nn.Module):

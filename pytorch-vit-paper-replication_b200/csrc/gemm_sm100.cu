@@ -868,7 +868,8 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
     B200_CHECK_ARG(op >= 0 && op <= 2, "gemm: bad op %d", op);
     B200_CHECK_ARG(epi >= 0 && epi < EPI_COUNT, "gemm: bad epilogue %d", epi);
     B200_CHECK_ARG(M > 0 && N > 0 && K > 0, "gemm: empty problem M=%d N=%d K=%d", M, N, K);
-    B200_CHECK_ARG(A && B && C, "gemm: null operand");
+    // C may be NULL only for the GELU epilogue (forward without a backward to follow: mask*gelu' is not needed)
+    B200_CHECK_ARG(A && B && (C || epi == EPI_BIAS_GELU), "gemm: null operand");
     B200_CHECK_ARG((lda % 8) == 0 && (ldb % 8) == 0, "gemm: lda/ldb must be multiples of 8 elements (TMA 16B stride), got %lld %lld", lda, ldb);
     B200_CHECK_ARG(((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0, "gemm: A/B must be 16-byte aligned");
     B200_CHECK_ARG(epi != EPI_BIAS_GELU || C2 != nullptr, "gemm: GELU epilogue needs the second output");

@@ -266,3 +266,29 @@ def test_uint8_images_equal_scaled_float_images(tiny):
     loss = m(xu8.to(dev())).square().mean()
     loss.backward()
     assert torch.isfinite(m.patch_embedding_block.patch_and_flatten[0].weight.grad).all()
+
+
+def test_frozen_backbone_trains_only_the_head(tiny):
+    """Feature-extractor fine-tuning (reference notebook cells 110-125 freeze the backbone and train a new head;
+    SURVEY 8f N3): with requires_grad=False on everything but the classifier, the encoder blocks save nothing and
+    run no backward kernels; the head's gradients equal those of the fully trainable model."""
+    from b200vit import _C
+    sd = sub(tiny, "sd0/")
+    X = torch.from_numpy(tiny["X"]).to(dev())
+    y = torch.from_numpy(tiny["y"]).to(dev())
+    full = build_tiny(sd).train()
+    torch.nn.functional.cross_entropy(full(X), y).backward()
+    frozen = build_tiny(sd).train()
+    for n, p in frozen.named_parameters():
+        p.requires_grad_(n.startswith("classifier") or n.startswith("layer_norm"))
+    l0 = _C.launch_count
+    loss = torch.nn.functional.cross_entropy(frozen(X), y)
+    fwd_launches = _C.launch_count - l0
+    loss.backward()
+    bwd_launches = _C.launch_count - l0 - fwd_launches
+    assert bwd_launches <= 4, bwd_launches                      # head + final LayerNorm only
+    for (n, p), (_, q) in zip(frozen.named_parameters(), full.named_parameters()):
+        if p.requires_grad:
+            assert rel_err(p.grad, q.grad) < 1e-5, n
+        else:
+            assert p.grad is None, n
