@@ -201,14 +201,14 @@ def _producer_dropout(x: torch.Tensor):
     return None
 
 
-def _msa_forward(x2d, bn, t, heads, ln_w, ln_b, w_in16, b_in, w_out16, b_out, residual, attn_p=0.0):
+def _msa_forward(x2d, bn, t, heads, ln_w, ln_b, w_in16, b_in, w_out16, b_out, residual, attn_p=0.0, eps=LN_EPS):
     r, d = x2d.shape
     if d != heads * HEAD_DIM:
         raise NotImplementedError(f"b200vit attention kernels need head_dim == 64 (embedding_dim {d}, heads {heads})")
     ln = _empty((r, d), torch.bfloat16, x2d)
     mean = _empty((r,), torch.float32, x2d)
     rstd = _empty((r,), torch.float32, x2d)
-    K.layernorm_fwd(x2d, d, ln_w, ln_b, ln, None, mean, rstd, r, d, LN_EPS)
+    K.layernorm_fwd(x2d, d, ln_w, ln_b, ln, None, mean, rstd, r, d, eps)
     qkv = _empty((r, 3 * d), torch.bfloat16, x2d)
     K.gemm(K.OP_NT, K.EPI_BF16, r, 3 * d, d, ln, d, w_in16, d, qkv, 3 * d, bias=b_in)
     o = _empty((r, d), torch.bfloat16, x2d)
@@ -263,13 +263,13 @@ def _msa_backward(g, saved, bn, t, heads, ln_w, w_in16, w_out16, has_residual, g
     return gx, (dgamma, dbeta, dw_in, db_in, dw_out, db_out)
 
 
-def _mlp_forward(x2d, ln_w, ln_b, w1_16, b1, w2_16, b2, p, residual, keep_preact):
+def _mlp_forward(x2d, ln_w, ln_b, w1_16, b1, w2_16, b2, p, residual, keep_preact, eps=LN_EPS):
     r, d = x2d.shape
     m = w1_16.shape[0]
     ln = _empty((r, d), torch.bfloat16, x2d)
     mean = _empty((r,), torch.float32, x2d)
     rstd = _empty((r,), torch.float32, x2d)
-    K.layernorm_fwd(x2d, d, ln_w, ln_b, ln, None, mean, rstd, r, d, LN_EPS)
+    K.layernorm_fwd(x2d, d, ln_w, ln_b, ln, None, mean, rstd, r, d, eps)
     key1 = next_dropout_key() if p > 0 else (0, 0)
     key2 = next_dropout_key() if p > 0 else (0, 0)
     a = _empty((r, m), torch.bfloat16, x2d) if keep_preact else None
@@ -323,12 +323,12 @@ class MSAFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, ln_w, ln_b, w_in, b_in, w_out, b_out, w_in16, w_out16, heads: int, attn_p: float = 0.0,
-                training: bool = False):
+                training: bool = False, eps: float = LN_EPS):
         _require_cuda(x, "MultiHeadSelfAttentionBlock")
         x = _f32c(x)
         bn, t, d = x.shape
         y, saved, adrop = _msa_forward(x.view(bn * t, d), bn, t, heads, ln_w, ln_b, w_in16, b_in, w_out16, b_out, None,
-                                       float(attn_p) if training else 0.0)
+                                       float(attn_p) if training else 0.0, eps)
         ctx.save_for_backward(ln_w, w_in16, w_out16, *saved)
         ctx.meta = (bn, t, heads)
         ctx.adrop = adrop
@@ -342,14 +342,15 @@ class MSAFn(torch.autograd.Function):
         gx, (dgam, dbet, dw_in, db_in, dw_out, db_out) = _msa_backward(
             _f32c(g).view(bn * t, d), tuple(saved), bn, t, heads, ln_w, w_in16, w_out16, has_residual=False,
             adrop=ctx.adrop)
-        return gx.view(bn, t, d), dgam, dbet, dw_in, db_in, dw_out, db_out, None, None, None, None, None
+        return gx.view(bn, t, d), dgam, dbet, dw_in, db_in, dw_out, db_out, None, None, None, None, None, None
 
 
 class MLPFn(torch.autograd.Function):
     """MLPBlock.forward (models/vit.py:128-131): LN -> Linear -> GELU -> Dropout -> Linear -> Dropout."""
 
     @staticmethod
-    def forward(ctx, x, ln_w, ln_b, w1, b1, w2, b2, w1_16, w2_16, p: float, training: bool, grad_mode: bool = True):
+    def forward(ctx, x, ln_w, ln_b, w1, b1, w2, b2, w1_16, w2_16, p: float, training: bool, grad_mode: bool = True,
+                eps: float = LN_EPS):
         # grad_mode: torch.is_grad_enabled() as seen by the CALLER (inside forward it is always False, and
         # needs_input_grad stays True under no_grad / inference_mode): without it, inference would save activations
         _require_cuda(x, "MLPBlock")
@@ -359,7 +360,7 @@ class MLPFn(torch.autograd.Function):
         x2d = x.view(-1, d)
         needs_bwd = bool(grad_mode) and any(ctx.needs_input_grad)
         y, saved, drop = _mlp_forward(x2d, ln_w, ln_b, w1_16, b1, w2_16, b2, float(p) if training else 0.0, None,
-                                      keep_preact=needs_bwd)
+                                      keep_preact=needs_bwd, eps=eps)
         if needs_bwd:
             ctx.save_for_backward(ln_w, w1_16, w2_16, *saved)
         ctx.drop = drop
@@ -372,7 +373,7 @@ class MLPFn(torch.autograd.Function):
         d = shape[-1]
         gx, (dgam, dbet, dw1, db1, dw2, db2), _, _ = _mlp_backward(
             _f32c(g).view(-1, d), tuple(saved), ctx.drop, ln_w, w1_16, w2_16, has_residual=False, want_bf16_out=False)
-        return gx.view(shape), dgam, dbet, dw1, db1, dw2, db2, None, None, None, None, None
+        return gx.view(shape), dgam, dbet, dw1, db1, dw2, db2, None, None, None, None, None, None
 
 
 class EncoderBlockFn(torch.autograd.Function):
@@ -382,7 +383,7 @@ class EncoderBlockFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, a_ln_w, a_ln_b, w_in, b_in, w_out, b_out, m_ln_w, m_ln_b, w1, b1, w2, b2,
                 w_in16, w_out16, w1_16, w2_16, heads: int, p: float, training: bool, attn_p: float = 0.0,
-                grad_mode: bool = True):
+                grad_mode: bool = True, eps_msa: float = LN_EPS, eps_mlp: float = LN_EPS):
         _require_cuda(x, "TransformerEncoderBlock")
         x = _f32c(x)
         bn, t, d = x.shape
@@ -390,9 +391,9 @@ class EncoderBlockFn(torch.autograd.Function):
         needs_bwd = bool(grad_mode) and any(ctx.needs_input_grad)
         ctx.consumer_drop = _producer_dropout(x) if needs_bwd else None      # see "cross-block hand-over" above
         x1, s_msa, adrop = _msa_forward(x2d, bn, t, heads, a_ln_w, a_ln_b, w_in16, b_in, w_out16, b_out, x2d,
-                                        float(attn_p) if training else 0.0)
+                                        float(attn_p) if training else 0.0, eps_msa)
         x2, s_mlp, drop = _mlp_forward(x1, m_ln_w, m_ln_b, w1_16, b1, w2_16, b2, float(p) if training else 0.0, x1,
-                                       keep_preact=needs_bwd)
+                                       keep_preact=needs_bwd, eps=eps_mlp)
         if needs_bwd:
             ctx.save_for_backward(a_ln_w, m_ln_w, w_in16, w_out16, w1_16, w2_16, *s_msa, *s_mlp)
         ctx.meta = (bn, t, heads, len(s_msa))
@@ -418,7 +419,7 @@ class EncoderBlockFn(torch.autograd.Function):
             g1, s_msa, bn, t, heads, a_ln_w, w_in16, w_out16, has_residual=True, g16=g1_16, db_out=db_out,
             adrop=ctx.adrop, arena=arena, consumer_drop=ctx.consumer_drop)
         return (g0.view(bn, t, d), a_dgam, a_dbet, dw_in, db_in, dw_out, db_out, m_dgam, m_dbet, dw1, db1, dw2, db2,
-                None, None, None, None, None, None, None, None, None)
+                None, None, None, None, None, None, None, None, None, None, None)
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -429,7 +430,7 @@ class HeadFn(torch.autograd.Function):
     normalises all T rows and discards T-1 of them; the result is identical."""
 
     @staticmethod
-    def forward(ctx, x, ln_w, ln_b, w, b):
+    def forward(ctx, x, ln_w, ln_b, w, b, eps: float = LN_EPS):
         _require_cuda(x, "ViT head")
         x = _f32c(x)
         bn, t, d = x.shape
@@ -437,7 +438,7 @@ class HeadFn(torch.autograd.Function):
         xn = _empty((bn, d), torch.float32, x)
         mean = _empty((bn,), torch.float32, x)
         rstd = _empty((bn,), torch.float32, x)
-        K.layernorm_fwd(x, t * d, ln_w, ln_b, None, xn, mean, rstd, bn, d, LN_EPS)
+        K.layernorm_fwd(x, t * d, ln_w, ln_b, None, xn, mean, rstd, bn, d, eps)
         logits = _empty((bn, c), torch.float32, x)
         K.head_fwd(xn, w, b, logits, bn, d, c)
         ctx.save_for_backward(x, ln_w, w, xn, mean, rstd)
@@ -457,14 +458,14 @@ class HeadFn(torch.autograd.Function):
         dgam = _empty((d,), torch.float32, x)
         dbet = _empty((d,), torch.float32, x)
         K.layernorm_bwd(None, dxn, x, t * d, mean, rstd, ln_w, None, gx, t * d, None, dgam, dbet, None, bn, d)
-        return gx, dgam, dbet, dw, db
+        return gx, dgam, dbet, dw, db, None
 
 
 class LayerNormFn(torch.autograd.Function):
     """Full-sequence nn.LayerNorm with f32 output (headless ViT, models/vit_no_classifier.py:225-226)."""
 
     @staticmethod
-    def forward(ctx, x, w, b):
+    def forward(ctx, x, w, b, eps: float = LN_EPS):
         _require_cuda(x, "LayerNorm")
         x = _f32c(x)
         d = x.shape[-1]
@@ -472,7 +473,7 @@ class LayerNormFn(torch.autograd.Function):
         y = torch.empty_like(x)
         mean = _empty((rows,), torch.float32, x)
         rstd = _empty((rows,), torch.float32, x)
-        K.layernorm_fwd(x, d, w, b, None, y, mean, rstd, rows, d, LN_EPS)
+        K.layernorm_fwd(x, d, w, b, None, y, mean, rstd, rows, d, eps)
         ctx.save_for_backward(x, w, mean, rstd)
         return y
 
@@ -486,7 +487,7 @@ class LayerNormFn(torch.autograd.Function):
         dgam = _empty((d,), torch.float32, x)
         dbet = _empty((d,), torch.float32, x)
         K.layernorm_bwd(None, g, x, d, mean, rstd, w, None, gx, d, None, dgam, dbet, None, rows, d)
-        return gx, dgam, dbet
+        return gx, dgam, dbet, None
 
 
 # ---------------------------------------------------------------------------------------------------------

@@ -71,7 +71,8 @@ class MultiHeadSelfAttentionBlock(nn.Module):
         # mha.dropout > 0 (attn_dropout): dropout on the attention probabilities in training mode, as torch does
         return F_.MSAFn.apply(x, self.layer_norm.weight, self.layer_norm.bias, mha.in_proj_weight, mha.in_proj_bias,
                               mha.out_proj.weight, mha.out_proj.bias, F_.bf16_shadow(mha.in_proj_weight),
-                              F_.bf16_shadow(mha.out_proj.weight), mha.num_heads, mha.dropout, self.training)
+                              F_.bf16_shadow(mha.out_proj.weight), mha.num_heads, mha.dropout, self.training,
+                              self.layer_norm.eps)
 
 
 class MLPBlock(nn.Module):
@@ -95,7 +96,7 @@ class MLPBlock(nn.Module):
         fc1, fc2 = self.mlp[0], self.mlp[3]
         return F_.MLPFn.apply(x, self.layer_norm.weight, self.layer_norm.bias, fc1.weight, fc1.bias, fc2.weight,
                               fc2.bias, F_.bf16_shadow(fc1.weight), F_.bf16_shadow(fc2.weight), self.mlp[2].p,
-                              self.training, torch.is_grad_enabled())
+                              self.training, torch.is_grad_enabled(), self.layer_norm.eps)
 
 
 class TransformerEncoderBlock(nn.Module):
@@ -121,7 +122,7 @@ class TransformerEncoderBlock(nn.Module):
             mha.out_proj.weight, mha.out_proj.bias, mlp.layer_norm.weight, mlp.layer_norm.bias, fc1.weight, fc1.bias,
             fc2.weight, fc2.bias, F_.bf16_shadow(mha.in_proj_weight), F_.bf16_shadow(mha.out_proj.weight),
             F_.bf16_shadow(fc1.weight), F_.bf16_shadow(fc2.weight), mha.num_heads, mlp.mlp[2].p, self.training,
-            mha.dropout, torch.is_grad_enabled())
+            mha.dropout, torch.is_grad_enabled(), msa.layer_norm.eps, mlp.layer_norm.eps)
 
 
 class ViT(nn.Module):
@@ -153,4 +154,5 @@ class ViT(nn.Module):
         x = self.patch_embedding_block(x)
         x = self.transformer_encoder(x)
         head = self.classifier[0]
-        return F_.HeadFn.apply(x, self.layer_norm.weight, self.layer_norm.bias, head.weight, head.bias)
+        return F_.HeadFn.apply(x, self.layer_norm.weight, self.layer_norm.bias, head.weight, head.bias,
+                               self.layer_norm.eps)

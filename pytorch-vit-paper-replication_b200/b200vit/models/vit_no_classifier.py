@@ -37,4 +37,4 @@ class ViT(nn.Module):
         x = self.patch_embedding_block(x)
         x = self.transformer_encoder(x)
         # unlike the classifier model, every token is returned, so every row is normalised
-        return F_.LayerNormFn.apply(x, self.layer_norm.weight, self.layer_norm.bias)
+        return F_.LayerNormFn.apply(x, self.layer_norm.weight, self.layer_norm.bias, self.layer_norm.eps)
