@@ -61,10 +61,9 @@ __device__ __forceinline__ float2 unpack_bf16(uint32_t v) {
     return __bfloat1622float2(t);
 }
 
-// erf-form GELU and its derivative (nn.GELU() default, reference models/vit.py:121). erf is evaluated with the
-// Abramowitz-Stegun 7.1.26 rational form (|error| <= 1.5e-7, far below the bf16 rounding of every consumer):
-// one MUFU.RCP + one MUFU.EX2 + a 5-term Horner polynomial, no branches. With u = |x|/sqrt(2),
-//   E = exp(-u^2) = exp(-x^2/2),  erf(u) = 1 - poly(t) E,  t = 1/(1 + 0.3275911 u)
+// erf-form GELU and its derivative (nn.GELU() default, reference models/vit.py:121). erf is evaluated with an
+// Abramowitz-Stegun rational form: one MUFU.RCP + one MUFU.EX2 + a short Horner polynomial, no branches. With
+// u = |x|/sqrt(2),  E = exp(-u^2) = exp(-x^2/2),  erf(u) = 1 - poly(t) E,  t = 1/(1 + p u)
 // and the same E gives the Gaussian density needed by the derivative.
 __device__ __forceinline__ float fast_rcp(float x) {
     float r;
@@ -76,15 +75,15 @@ __device__ __forceinline__ float fast_ex2(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
+// erf by Abramowitz & Stegun 7.1.25 (three coefficients, |error| <= 2.5e-5): every consumer rounds the result to bf16
+// (half an ulp is 2e-3 relative), so the five-coefficient 7.1.26 (1.5e-7) bought nothing for two more FMAs and a
+// multiply per element in the most instruction-bound epilogue of the step. u = |x|/sqrt2 is folded into the constants.
 __device__ __forceinline__ void gelu_terms(float x, float& one_minus_pe, float& e) {
-    const float u = fabsf(x) * 0.70710678118654752f;
-    const float t = fast_rcp(fmaf(0.3275911f, u, 1.0f));
-    float poly = fmaf(t, 1.061405429f, -1.453152027f);
-    poly = fmaf(poly, t, 1.421413741f);
-    poly = fmaf(poly, t, -0.284496736f);
-    poly = fmaf(poly, t, 0.254829592f);
+    const float t = fast_rcp(fmaf(0.47047f * 0.70710678118654752f, fabsf(x), 1.0f));
+    float poly = fmaf(t, 0.7478556f, -0.0958798f);
+    poly = fmaf(poly, t, 0.3480242f);
     poly *= t;
-    e = fast_ex2(u * u * -1.4426950408889634f);
+    e = fast_ex2(x * x * (-0.5f * 1.4426950408889634f));     // exp(-x^2 / 2)
     one_minus_pe = fmaf(-poly, e, 1.0f);          // erf(|x|/sqrt2)
 }
 // h = s * gelu(x), g = s * gelu'(x) from one set of shared terms (s = dropout scale 1/(1-p), folded into constants).
