@@ -72,7 +72,7 @@ def test_gemm_gelu_and_dgelu():
     a_ref = (A.float() @ B.float().t() + bias).requires_grad_(True)
     h_ref = torch.nn.functional.gelu(a_ref)
     h_ref.sum().backward()
-    assert rel_err(h, h_ref) < 5e-3            # erf via A&S 7.1.26 (1.5e-7) + bf16 output rounding
+    assert rel_err(h, h_ref) < 5e-3            # erf via A&S 7.1.25 (2.5e-5) + bf16 output rounding
     assert rel_err(gd, a_ref.grad) < 5e-3
     # backward epilogue: out = (G @ W) * gelu'(a)
     G = _rand_bf16((M, Kd), g)
