@@ -43,6 +43,7 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
                         bf16* __restrict__ out, float* __restrict__ lse, int num_heads_total, int T, int Nk, int H,
                         float scale_log2, float scale) {
     extern __shared__ uint8_t smem_raw[];
+    pdl_launch_dependents();
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t kv_bytes = (uint32_t)Nk * 128u;
     const uint32_t kv_stride = (kv_bytes + 1023u) & ~1023u;
@@ -87,6 +88,7 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot_ptr;
+    pdl_wait();       // the prologue above overlapped the previous kernel; global memory is touched from here on
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -871,6 +873,7 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
                          bf16* __restrict__ dqkv, float* __restrict__ dbias, int num_heads_total, int T, int Nk, int H,
                          float scale_log2, float scale) {
     extern __shared__ uint8_t smem_raw[];
+    pdl_launch_dependents();
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t tile_bytes = (uint32_t)Nk * 128u;
     const uint32_t tile_stride = (tile_bytes + 1023u) & ~1023u;
@@ -929,6 +932,7 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot_ptr;
+    pdl_wait();       // the prologue above overlapped the previous kernel; global memory is touched from here on
 
     if (warp < 2) {
         // ===================== two MMA issuers: warp 1 serves math group 0, warp 0 serves group 1 and issues the TMA loads ======
@@ -1241,6 +1245,7 @@ attention_fwd_long_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
                           bf16* __restrict__ out, float* __restrict__ lse, int num_items, int rounds, int T, int H,
                           float scale_log2, float scale) {
     extern __shared__ uint8_t smem_raw[];
+    pdl_launch_dependents();
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     constexpr uint32_t Q_BYTES = 2 * ATC_BM * 128;               // both query tiles of the pair
     constexpr uint32_t KV_BYTES = ATL_BN * 128;                  // one K or V block
@@ -1289,6 +1294,7 @@ attention_fwd_long_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot_ptr;
+    pdl_wait();       // the prologue above overlapped the previous kernel; global memory is touched from here on
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -1541,6 +1547,7 @@ attention_bwd_long_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_
                           const float* __restrict__ lse, const float* __restrict__ delta, bf16* __restrict__ dqkv,
                           int num_items, int rounds, int T, int H, float scale_log2, float scale) {
     extern __shared__ uint8_t smem_raw[];
+    pdl_launch_dependents();
     const int nc = (T + ATLB_W - 1) / ATLB_W;                    // column chunks per item
     const uint32_t Tp = (uint32_t)nc * ATLB_W;
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -1592,6 +1599,7 @@ attention_bwd_long_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot_ptr;
+    pdl_wait();       // the prologue above overlapped the previous kernel; global memory is touched from here on
 
     if (warp == 0) {
         // ===================== TMA producer + column statistics =====================
@@ -1883,8 +1891,8 @@ int attention_fwd_tc_launch(const bf16* qkv, bf16* out, float* lse, int batch, i
     B200_CUDA(cudaFuncSetAttribute(attention_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int total = batch * heads;
     const int grid = total < sm_count() ? total : sm_count();
-    attention_fwd_tc_kernel<<<grid, ATC_THREADS, smem, stream>>>(tmQ, tmKV, out, lse, total, tokens, Nk, heads,
-                                                               scale * 1.4426950408889634f, scale);
+    B200_CUDA(launch_kernel_pdl(attention_fwd_tc_kernel, dim3(grid), dim3(ATC_THREADS), smem, stream, tmQ, tmKV, out, lse, total,
+                                tokens, Nk, heads, scale * 1.4426950408889634f, scale));
     B200_LAUNCH_CHECK();
     return 0;
 }
@@ -1903,8 +1911,8 @@ int attention_fwd_long_launch(const bf16* qkv, bf16* out, float* lse, int batch,
     const long long items = (long long)batch * heads * rounds;
     B200_CHECK_ARG(items < (1LL << 31), "attention_fwd: too many work items");
     const int grid = items < sm_count() ? (int)items : sm_count();
-    attention_fwd_long_kernel<<<grid, ATC_THREADS, smem, stream>>>(tmQ, tmKV, out, lse, (int)items, rounds, tokens, heads,
-                                                                 scale * 1.4426950408889634f, scale);
+    B200_CUDA(launch_kernel_pdl(attention_fwd_long_kernel, dim3(grid), dim3(ATC_THREADS), smem, stream, tmQ, tmKV, out, lse,
+                                (int)items, rounds, tokens, heads, scale * 1.4426950408889634f, scale));
     B200_LAUNCH_CHECK();
     return 0;
 }
@@ -1930,8 +1938,8 @@ int attention_bwd_long_launch(const bf16* qkv, const bf16* dout, const float* ls
     const long long items = (long long)batch * heads * 2 * rounds;
     B200_CHECK_ARG(items < (1LL << 31), "attention_bwd: too many work items");
     const int grid = items < sm_count() ? (int)items : sm_count();
-    attention_bwd_long_kernel<<<grid, ATC_THREADS, smem, stream>>>(tx, txd, ty, tyd, lse, delta, dqkv, (int)items, rounds,
-                                                                 tokens, heads, scale * 1.4426950408889634f, scale);
+    B200_CUDA(launch_kernel_pdl(attention_bwd_long_kernel, dim3(grid), dim3(ATC_THREADS), smem, stream, tx, txd, ty, tyd, lse,
+                                delta, dqkv, (int)items, rounds, tokens, heads, scale * 1.4426950408889634f, scale));
     B200_LAUNCH_CHECK();
     return 0;
 }
@@ -1958,8 +1966,8 @@ int attention_bwd_tc_launch(const bf16* qkv, const bf16* out, const bf16* dout, 
         if (smem3 <= 232448) {
             if (dbias) B200_CUDA(cudaMemsetAsync(dbias, 0, sizeof(float) * 3 * heads * 64, stream));
             B200_CUDA(cudaFuncSetAttribute(attention_bwd_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
-            attention_bwd_tc3_kernel<<<grid, AT3_THREADS, smem3, stream>>>(tq, td, out, dout, lse, dqkv, dbias, total, tokens, Nk,
-                                                                         heads, scale * 1.4426950408889634f, scale);
+            B200_CUDA(launch_kernel_pdl(attention_bwd_tc3_kernel, dim3(grid), dim3(AT3_THREADS), smem3, stream, tq, td, out, dout,
+                                        lse, dqkv, dbias, total, tokens, Nk, heads, scale * 1.4426950408889634f, scale));
             B200_LAUNCH_CHECK();
             return 0;
         }

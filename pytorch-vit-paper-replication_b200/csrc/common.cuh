@@ -3,6 +3,7 @@
 // Everything in csrc/ is new code: the reference (models/vit.py, going_modular/engine.py)
 // has no native component; the arithmetic it delegates to torch.nn is re-implemented here.
 #pragma once
+#include <stdlib.h>
 
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -121,6 +122,41 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
         }
     }
     return v[0];
+}
+
+// ---------------------------------------------------------------------------------------------
+// Programmatic dependent launch. A step is ~340 back-to-back kernels on one stream, and between two of them the SMs
+// idle for ~2 us (grid launch latency) plus the next kernel's prologue (barrier init, TMEM allocation, descriptor
+// prefetch). Kernels launched through launch_kernel_pdl() may be scheduled while their predecessor is still running:
+// every CTA announces "dependents may launch" at its very start (pdl_launch_dependents) and waits for the
+// predecessor grid to complete and flush (pdl_wait) after its own prologue, before it touches global memory.
+// Without the launch attribute (B200VIT_PDL=0, or a predecessor that is not ours) both instructions are no-ops.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+inline bool pdl_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("B200VIT_PDL");
+        v = e ? atoi(e) : 1;
+    }
+    return v != 0;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                     Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 // ---------------------------------------------------------------------------------------------

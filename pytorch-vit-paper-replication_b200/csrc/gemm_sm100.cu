@@ -445,6 +445,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const GemmParams p) {
     extern __shared__ uint8_t smem_raw[];
+    pdl_launch_dependents();      // the next kernel on the stream may be scheduled as SMs free up
     // 128B swizzle atoms need 1024-byte aligned stage bases.
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t smem_a = smem_base;
@@ -478,6 +479,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
+    pdl_wait();                   // everything above ran under the previous kernel's tail; global memory from here on
 
     const int total_work = p.tiles_m * p.tiles_n * p.splits;
 
@@ -621,6 +623,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     constexpr int EW = Cfg2<EPI>::EW;
     constexpr int CHUNKS = 8 / (EW / 4);     // 32-column chunks per epilogue warp
     extern __shared__ uint8_t smem_raw[];
+    pdl_launch_dependents();      // the next kernel on the stream may be scheduled as SMs free up
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t smem_a = smem_base;
     const uint32_t smem_b = smem_base + STAGES2 * A_STAGE_BYTES;
@@ -655,6 +658,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     cluster_sync_all();     // barriers of both CTAs are initialised before any remote arrive / multicast commit
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
+    pdl_wait();                   // everything above ran under the previous kernel's tail; global memory from here on
 
     const int tiles_m2 = (p.M + 2 * BM - 1) / (2 * BM);
     const int total_work = tiles_m2 * p.tiles_n * p.splits;
@@ -944,12 +948,12 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
         const int total = tiles_m2 * p.tiles_n * p.splits;
         const int pairs = sm_count() / 2;
         const int grid = 2 * (total < pairs ? total : pairs);
-        kern<<<grid, threads2, smem2, stream>>>(tmA, tmB, p);   // cluster dims are compiled in
+        B200_CUDA(launch_kernel_pdl(kern, dim3(grid), dim3(threads2), (size_t)smem2, stream, tmA, tmB, p));   // cluster dims are compiled in
     } else {
         B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
         const int total = p.tiles_m * p.tiles_n * p.splits;
         const int grid = total < sm_count() ? total : sm_count();
-        kern<<<grid, GEMM_THREADS, GEMM_SMEM_BYTES, stream>>>(tmA, tmB, p);
+        B200_CUDA(launch_kernel_pdl(kern, dim3(grid), dim3(GEMM_THREADS), (size_t)GEMM_SMEM_BYTES, stream, tmA, tmB, p));
     }
     B200_LAUNCH_CHECK();
     return 0;

@@ -17,8 +17,10 @@ __global__ void __launch_bounds__(LN_WARPS * 32)
 layernorm_fwd_kernel(const float* __restrict__ x, long long row_stride, const float* __restrict__ gamma,
                      const float* __restrict__ beta, bf16* __restrict__ y_bf16, float* __restrict__ y_f32,
                      float* __restrict__ mean_out, float* __restrict__ rstd_out, long long rows, int D, float eps) {
+    pdl_launch_dependents();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nv = D >> 2;
+    pdl_wait();
     for (long long row = (long long)blockIdx.x * LN_WARPS + warp; row < rows; row += (long long)gridDim.x * LN_WARPS) {
         const float4* xr = reinterpret_cast<const float4*>(x + row * row_stride);
         float4 v[NV];                       // the whole row lives in registers: one global read
@@ -82,8 +84,8 @@ int layernorm_fwd_launch(const float* x, long long row_stride, const float* gamm
     if (blocks > cap) blocks = cap;
     const int nvl = (dim / 4 + 31) / 32;
     B200_CHECK_ARG(nvl <= 16, "layernorm_fwd: dim must be <= 2048 (got %d)", dim);
-#define LN_FWD_CASE(NV) layernorm_fwd_kernel<NV><<<(unsigned)blocks, LN_WARPS * 32, 0, stream>>>( \
-        x, row_stride, gamma, beta, y_bf16, y_f32, mean, rstd, rows, dim, eps)
+#define LN_FWD_CASE(NV) B200_CUDA(launch_kernel_pdl(layernorm_fwd_kernel<NV>, dim3((unsigned)blocks), dim3(LN_WARPS * 32), (size_t)0, stream, \
+        x, row_stride, gamma, beta, y_bf16, y_f32, mean, rstd, rows, dim, eps))
     if (nvl <= 1) LN_FWD_CASE(1);
     else if (nvl <= 2) LN_FWD_CASE(2);
     else if (nvl <= 4) LN_FWD_CASE(4);
@@ -115,6 +117,7 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
     // Column accumulators live in shared memory, one private slab per warp ([acc][warp][D]): keeping them in
     // registers (24 values per lane per accumulator at D=768) starved the kernel of occupancy.
     extern __shared__ float sacc[];
+    pdl_launch_dependents();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int nv = D >> 2;
     float4* acc_g = reinterpret_cast<float4*>(sacc + (size_t)(0 * LN_WARPS + warp) * D);
@@ -126,6 +129,7 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy_bf16, const float* __restrict__
         if (HAS_NEXT) acc_n[i] = make_float4(0, 0, 0, 0);
     }
     __syncwarp();
+    pdl_wait();       // accumulators were cleared under the previous kernel's tail; global memory from here on
     const float4* gamma4 = reinterpret_cast<const float4*>(gamma);
     const bool want_cols = dgamma != nullptr || dbeta != nullptr;
 
@@ -249,13 +253,13 @@ int layernorm_bwd_launch(const bf16* dy_bf16, const float* dy_f32, const float* 
         B200_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<NV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * 4 * LN_WARPS * 1024)); \
         B200_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<NV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 4 * LN_WARPS * 1024)); \
         if (gout_bf16)                                                                                          \
-            layernorm_bwd_kernel<NV, true><<<(unsigned)blocks, LN_WARPS * 32, smem, stream>>>(                   \
+            B200_CUDA(launch_kernel_pdl(layernorm_bwd_kernel<NV, true>, dim3((unsigned)blocks), dim3(LN_WARPS * 32), smem, stream, \
                 dy_bf16, dy_f32, x, row_stride, mean, rstd, gamma, gin, gout, gout_stride, gout_bf16, dgamma,   \
-                dbeta, dbias_next, rows, dim, drop);                                                            \
+                dbeta, dbias_next, rows, dim, drop));                                                           \
         else                                                                                                    \
-            layernorm_bwd_kernel<NV, false><<<(unsigned)blocks, LN_WARPS * 32, smem, stream>>>(                  \
+            B200_CUDA(launch_kernel_pdl(layernorm_bwd_kernel<NV, false>, dim3((unsigned)blocks), dim3(LN_WARPS * 32), smem, stream, \
                 dy_bf16, dy_f32, x, row_stride, mean, rstd, gamma, gin, gout, gout_stride, gout_bf16, dgamma,   \
-                dbeta, dbias_next, rows, dim, drop);                                                            \
+                dbeta, dbias_next, rows, dim, drop));                                                           \
     } while (0)
     if (nvl <= 1) LN_BWD_CASE(1);
     else if (nvl <= 2) LN_BWD_CASE(2);
