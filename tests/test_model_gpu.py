@@ -292,3 +292,39 @@ def test_frozen_backbone_trains_only_the_head(tiny):
             assert rel_err(p.grad, q.grad) < 1e-5, n
         else:
             assert p.grad is None, n
+
+
+def test_backward_handover_falls_back_when_the_gradient_is_replaced(tiny):
+    """The LayerNorm backward of block i+1 hands bf16(mask * g) to block i keyed by g's storage address
+    (functional.py, "cross-block hand-over"). A tensor hook that replaces or edits g must not be served stale data:
+    the consumer falls back to computing it from the gradient it actually received."""
+    sd = sub(tiny, "sd0/")
+    X = torch.from_numpy(tiny["X"]).to(dev())
+    y = torch.from_numpy(tiny["y"]).to(dev())
+
+    def grads(hook):
+        m = build_tiny(sd, mlp_dropout=0.0).train()
+        handle = None
+        if hook is not None:
+            blk = m.transformer_encoder[0]
+            handle = blk.register_forward_hook(lambda mod, inp, out: out.register_hook(hook) and None)
+        torch.nn.functional.cross_entropy(m(X), y).backward()
+        if handle is not None:
+            handle.remove()
+        return {n: p.grad.clone() for n, p in m.named_parameters()}
+
+    base = grads(None)
+    cloned = grads(lambda g: g.clone())                     # same values at another address
+    for n in base:
+        assert rel_err(cloned[n], base[n]) < 1e-4, n
+    doubled = grads(lambda g: g * 2.0)                      # the consumer must see the modified gradient
+    n0 = "transformer_encoder.0.mlp_block.mlp.3.weight"
+    assert rel_err(doubled[n0], 2.0 * base[n0]) < 1e-3
+    n1 = "transformer_encoder.1.mlp_block.mlp.3.weight"     # upstream of the hook: unchanged
+    assert rel_err(doubled[n1], base[n1]) < 1e-4
+
+    def inplace(g):
+        g.mul_(2.0)                                          # same address, edited in place: version counter moved
+        return g
+    edited = grads(inplace)
+    assert rel_err(edited[n0], 2.0 * base[n0]) < 1e-3
