@@ -6,7 +6,9 @@ sys.path.insert(0, str(ROOT / "pytorch-vit-paper-replication_b200"))
 import torch
 from b200vit import kernels as K
 dev = torch.device("cuda:0")
-R, D, M = 50432, 768, 3072
+# usage: perf_elementwise.py [R D]   (default 50432 768: ViT-B/16 at B=256; ViT-L/16-384 at B=64: 36928 1024)
+R, D = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) >= 3 else (50432, 768)
+M = 4 * D
 def timeit(f, n=10):
     for _ in range(3): f()
     torch.cuda.synchronize()
@@ -27,6 +29,8 @@ t = timeit(lambda: K.layernorm_bwd(dy, None, x, D, mean, rstd, gam, gin, gout, D
 print(f"ln_bwd nocols {t:7.1f} us  {R*D*14/t/1e3:7.0f} GB/s")
 t = timeit(lambda: K.layernorm_bwd(dy, None, x, D, mean, rstd, gam, gin, gout, D, g16, dg, db, dbn, R, D))
 print(f"ln_bwd+next   {t:7.1f} us  {R*D*16/t/1e3:7.0f} GB/s")
+t = timeit(lambda: K.layernorm_bwd(dy, None, x, D, mean, rstd, gam, gin, gout, D, g16, dg, db, dbn, R, D, 0.1, 1, 2))
+print(f"ln_bwd+next p {t:7.1f} us  {R*D*16/t/1e3:7.0f} GB/s")
 da = torch.randn(R, M, device=dev).bfloat16(); o = torch.empty(M, device=dev)
 t = timeit(lambda: K.colsum_bf16(da, M, o, R, M))
 print(f"colsum[R,M]   {t:7.1f} us  {R*M*2/t/1e3:7.0f} GB/s")
