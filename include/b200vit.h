@@ -187,7 +187,9 @@ int b200vit_l2norm_sq(const void* const* ptrs_dev, const long long* sizes_dev, i
  *   - The first call on each device looks up the device address of the built-in array (cudaGetSymbolAddress);
  *     make that first call before starting any stream capture.
  *   - All calls on a device share the one array: two calls that overlap on the GPU (different streams) race on it.
- *     Nothing has to be cleared between calls -- every slot that is read is written first in the same call. */
+ *     Nothing has to be cleared between calls -- every slot that is read is written first in the same call.
+ *   - The looked-up address is cached per device ordinal for the life of the process. cudaDeviceReset() destroys the
+ *     context the address belongs to; a host that resets a device must not call this entry point on it afterwards. */
 int b200vit_l2norm_sq_noalloc(const void* const* ptrs_dev, const long long* sizes_dev, int num_tensors,
                               long long max_size, float* out_sumsq, void* stream);
 
@@ -203,6 +205,49 @@ int b200vit_l2norm_sq_noalloc(const void* const* ptrs_dev, const long long* size
 int b200vit_adam_step(const void* table_dev, int num_tensors, long long max_size, const float* lrs_host,
                       const float* wds_host, int num_groups, float beta1, float beta2, float eps, int step,
                       int decoupled, const float* grad_sumsq, float max_norm, float grad_scale, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Strict-precision ("fp32 mode") entry points. The reference computes in fp32 end to end (default-dtype nn modules,
+ * models/vit.py:28-31, 83, 86-90, 115, 119-124, 216-222, run unchanged by going_modular/engine.py:50-66). In this
+ * mode activations stay f32 between kernels and every contraction is still ONE b200vit_gemm launch on the tcgen05
+ * tensor cores, fed split operands: x = hi + lo with hi = bf16(x), lo = bf16(x - hi), concatenated along the
+ * contraction dimension as A' = [hi | lo | hi], B' = [hi | hi | lo], K' = 3K, so that the fp32 accumulator receives
+ * a_hi b_hi + a_lo b_hi + a_hi b_lo (error <= ~2^-16 per product). Logits then agree with the reference to < 1e-3.
+ * ------------------------------------------------------------------------------------------------ */
+
+/* Write the three bf16 parts of src f32 [rows, cols] (leading dimension ld_src) to dst + k * part_stride (k = 0..2),
+ * each [rows, cols] with leading dimension ld_dst. pattern 0 = (hi, lo, hi) for the A operand, 1 = (hi, hi, lo) for B.
+ * Concatenate along columns with part_stride = cols, ld_dst = 3 * cols; along rows with part_stride = rows * ld_dst.
+ * dropout_p > 0 multiplies the source by the (seed, offset) mask with element index source_row * cols + col (reading
+ * the gradient of an nn.Dropout output in place, models/vit.py:43, 125); row_period > 0 reads source row
+ * r + r / row_period + 1 (skips the class-token row of every image, models/vit.py:59). */
+int b200vit_split_bf16x3(const float* src, long long ld_src, long long rows, int cols, void* dst_bf16, long long ld_dst,
+                         long long part_stride, int pattern, float dropout_p, unsigned long long seed,
+                         unsigned long long offset, int row_period, void* stream);
+
+/* b200vit_im2col_patches with f32 output [B*(H/P)*(W/P), C*P*P] (models/vit.py:28-34, 53-56). */
+int b200vit_im2col_patches_f32(const float* image, float* patches, int batch, int channels, int height, int width,
+                               int patch, void* stream);
+
+/* h = dropout(gelu_erf(a)) on f32 (nn.GELU + nn.Dropout, models/vit.py:121-122; erff, not the polynomial of the bf16
+ * epilogue) and its backward da = dh * dropout_mask/(1-p) * gelu_erf'(a). Element index i of the mask. */
+int b200vit_gelu_f32_fwd(const float* a, float* h, long long n, float dropout_p, unsigned long long seed,
+                         unsigned long long offset, void* stream);
+int b200vit_gelu_f32_bwd(const float* a, const float* dh, float* da, long long n, float dropout_p,
+                         unsigned long long seed, unsigned long long offset, void* stream);
+
+/* out[n] = sum_m mask[m, n] * x[m, n] for an f32 matrix (bias gradients, autograd of nn.Linear models/vit.py:119, 123
+ * and of the MHA projections :86-90); same dropout / row_period conventions as b200vit_split_bf16x3. */
+int b200vit_colsum_f32(const float* x, long long ld, long long rows, int cols, float* out, float dropout_p,
+                       unsigned long long seed, unsigned long long offset, int row_period, void* stream);
+
+/* f32 self-attention (the scaled_dot_product_attention inside nn.MultiheadAttention, models/vit.py:86-97) on CUDA
+ * cores: qkv f32 [B, T, 3, H, 64] -> out f32 [B, T, H*64], lse f32 [B, H, T]; any T, head_dim 64, no dropout.
+ * Backward: delta is an OUTPUT here (f32 [B, H, T], rowsum(dout * out)), dqkv f32 [B, T, 3, H, 64] is overwritten. */
+int b200vit_attention_f32_fwd(const float* qkv, float* out, float* lse, int batch, int tokens, int heads, int head_dim,
+                              float scale, void* stream);
+int b200vit_attention_f32_bwd(const float* qkv, const float* out, const float* dout, const float* lse, float* delta,
+                              float* dqkv, int batch, int tokens, int heads, int head_dim, float scale, void* stream);
 
 #ifdef __cplusplus
 }

@@ -43,6 +43,13 @@ _SIGNATURES = {
     "b200vit_l2norm_sq": [_p, _p, _i, _ll, _p, _i, _p, _p],
     "b200vit_l2norm_sq_noalloc": [_p, _p, _i, _ll, _p, _p],
     "b200vit_adam_step": [_p, _i, _ll, _p, _p, _i, _f, _f, _f, _i, _i, _p, _f, _f, _p],
+    "b200vit_split_bf16x3": [_p, _ll, _ll, _i, _p, _ll, _ll, _i, _f, _ull, _ull, _i, _p],
+    "b200vit_im2col_patches_f32": [_p, _p, _i, _i, _i, _i, _i, _p],
+    "b200vit_gelu_f32_fwd": [_p, _p, _ll, _f, _ull, _ull, _p],
+    "b200vit_gelu_f32_bwd": [_p, _p, _p, _ll, _f, _ull, _ull, _p],
+    "b200vit_colsum_f32": [_p, _ll, _ll, _i, _p, _f, _ull, _ull, _i, _p],
+    "b200vit_attention_f32_fwd": [_p, _p, _p, _i, _i, _i, _i, _f, _p],
+    "b200vit_attention_f32_bwd": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _f, _p],
 }
 
 # GEMM enums (include/b200vit.h)
@@ -113,7 +120,7 @@ def check(rc: int, what: str) -> None:
 
 # CUDA kernels launched by one successful call of each entry point (memsets are not counted).
 KERNELS_PER_CALL = {"b200vit_l2norm_sq": 2, "b200vit_l2norm_sq_noalloc": 2,
-                    "b200vit_head_bwd": 2}
+                    "b200vit_head_bwd": 2, "b200vit_attention_f32_bwd": 2}
 launch_count = 0
 
 

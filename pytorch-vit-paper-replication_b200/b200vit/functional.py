@@ -14,6 +14,7 @@ Data layout in HBM (R = B*T token rows, D = embedding dim, M = mlp size, H heads
 from __future__ import annotations
 
 import math
+import os
 import weakref
 from typing import List, Optional, Tuple
 
@@ -23,6 +24,44 @@ from . import kernels as K
 
 LN_EPS = 1e-5  # nn.LayerNorm default, reference models/vit.py:83,115,216
 HEAD_DIM = 64
+MAX_LN_DIM = 1024   # csrc/layernorm.cu: the backward kernels keep a row in registers up to this width
+
+# ---------------------------------------------------------------------------------------------------------
+# precision mode: "bf16" (default; bf16 GEMM operands, fp32 accumulation -- logits within 2e-2 of the reference) or
+# "fp32" (split-operand GEMMs and fp32 activations, b200vit.fp32 -- logits within 1e-3; 3-4x slower, for parity runs)
+# ---------------------------------------------------------------------------------------------------------
+_PRECISIONS = ("bf16", "fp32")
+_precision = os.environ.get("B200VIT_PRECISION", "bf16")
+if _precision not in _PRECISIONS:
+    raise RuntimeError(f"B200VIT_PRECISION must be one of {_PRECISIONS}, got {_precision!r}")
+
+
+def get_precision() -> str:
+    return _precision
+
+
+def set_precision(mode: str) -> str:
+    """Select the arithmetic of every b200vit module forward that follows; returns the previous mode."""
+    global _precision
+    if mode not in _PRECISIONS:
+        raise ValueError(f"precision must be one of {_PRECISIONS}, got {mode!r}")
+    prev, _precision = _precision, mode
+    return prev
+
+
+class precision:
+    """Context manager: `with b200vit.precision("fp32"): logits = model(x)`. The backward of a graph recorded inside
+    runs in the same mode wherever it is called."""
+
+    def __init__(self, mode: str):
+        self.mode = mode
+
+    def __enter__(self):
+        self.prev = set_precision(self.mode)
+        return self
+
+    def __exit__(self, *a):
+        set_precision(self.prev)
 
 # ---------------------------------------------------------------------------------------------------------
 # bf16 shadows of fp32 master weights
@@ -71,14 +110,39 @@ def shadow_entry(p: torch.Tensor) -> Optional[_Shadow]:
 # ---------------------------------------------------------------------------------------------------------
 # dropout seeds: a mask is a function of (seed, offset, element index); offsets count dropout sites
 # ---------------------------------------------------------------------------------------------------------
-_dropout_calls = 0
+# The counter is the Philox offset of torch's own CUDA generator for the device: `torch.manual_seed` resets it,
+# `torch.cuda.get_rng_state` / `set_rng_state` (and therefore checkpoints and torch.utils.checkpoint's RNG
+# preservation) capture and replay it, and two runs from the same seed in one process draw the same masks.
+# `_dropout_stream` is mixed into the seed: b200vit.dp.DataParallel sets it to the rank so that ranks seeded alike
+# (the usual `torch.manual_seed(42)` everywhere) still draw independent masks for their shards of the global batch.
+_dropout_stream = 0
+_cpu_counter = [None, 0]      # test doubles without CUDA: (seed the count belongs to, count)
 
 
-def next_dropout_key() -> Tuple[int, int]:
-    """(seed, offset) for one dropout site invocation. The seed follows torch.manual_seed()."""
-    global _dropout_calls
-    _dropout_calls += 1
-    return torch.initial_seed() & 0xFFFFFFFFFFFFFFFF, _dropout_calls
+def set_dropout_stream(stream: int) -> int:
+    """Give this process its own family of dropout masks (the data-parallel rank); returns the previous value."""
+    global _dropout_stream
+    prev, _dropout_stream = _dropout_stream, int(stream)
+    return prev
+
+
+def next_dropout_key(device=None) -> Tuple[int, int]:
+    """(seed, offset) for one dropout site invocation; follows torch.manual_seed() and torch's CUDA RNG state."""
+    if torch.cuda.is_available():
+        dev = torch.device("cuda") if device is None else torch.device(device)
+        idx = dev.index if dev.index is not None else torch.cuda.current_device()
+        gen = torch.cuda.default_generators[idx]
+        seed, off = gen.initial_seed(), gen.get_offset()
+        gen.set_offset(off + 4)                     # Philox offsets advance in steps of 4, as torch's own draws do
+        count = off // 4 + 1
+    else:
+        seed = torch.initial_seed()
+        if _cpu_counter[0] != seed:
+            _cpu_counter[0], _cpu_counter[1] = seed, 0
+        _cpu_counter[1] += 1
+        count = _cpu_counter[1]
+    seed = (seed ^ (_dropout_stream * 0x9E3779B97F4A7C15)) & 0xFFFFFFFFFFFFFFFF
+    return seed, count
 
 
 def _f32c(t: torch.Tensor) -> torch.Tensor:
@@ -142,7 +206,7 @@ class PatchEmbedFn(torch.autograd.Function):
         patches = K.im2col_patches(img, patch)
         x = _empty((bn, t, d), torch.float32, img)
         p = float(p_drop) if training else 0.0
-        seed, off = next_dropout_key() if p > 0 else (0, 0)
+        seed, off = next_dropout_key(img.device) if p > 0 else (0, 0)
         K.gemm(K.OP_NT, K.EPI_PATCH, bn * np_, d, kdim, patches, kdim, w16, kdim, x, d, bias=b, aux=pos, ldaux=d,
                dropout_p=p, seed=seed, offset=off, row_period=np_)
         K.class_token_rows(cls, pos, x, bn, t, d, p, seed, off)
@@ -213,7 +277,7 @@ def _msa_forward(x2d, bn, t, heads, ln_w, ln_b, w_in16, b_in, w_out16, b_out, re
     K.gemm(K.OP_NT, K.EPI_BF16, r, 3 * d, d, ln, d, w_in16, d, qkv, 3 * d, bias=b_in)
     o = _empty((r, d), torch.bfloat16, x2d)
     lse = _empty((bn, heads, t), torch.float32, x2d)
-    akey = next_dropout_key() if attn_p > 0 else (0, 0)      # dropout on the attention probabilities (vit.py:86-90)
+    akey = next_dropout_key(x2d.device) if attn_p > 0 else (0, 0)      # dropout on the attention probabilities (vit.py:86-90)
     K.attention_fwd(qkv, o, lse, bn, t, heads, HEAD_DIM, 1.0 / math.sqrt(HEAD_DIM), attn_p, akey[0], akey[1])
     y = _empty((r, d), torch.float32, x2d)
     K.gemm(K.OP_NT, K.EPI_BIAS_RES, r, d, d, o, d, w_out16, d, y, d, bias=b_out, aux=residual, ldaux=d)
@@ -270,8 +334,8 @@ def _mlp_forward(x2d, ln_w, ln_b, w1_16, b1, w2_16, b2, p, residual, keep_preact
     mean = _empty((r,), torch.float32, x2d)
     rstd = _empty((r,), torch.float32, x2d)
     K.layernorm_fwd(x2d, d, ln_w, ln_b, ln, None, mean, rstd, r, d, eps)
-    key1 = next_dropout_key() if p > 0 else (0, 0)
-    key2 = next_dropout_key() if p > 0 else (0, 0)
+    key1 = next_dropout_key(x2d.device) if p > 0 else (0, 0)
+    key2 = next_dropout_key(x2d.device) if p > 0 else (0, 0)
     a = _empty((r, m), torch.bfloat16, x2d) if keep_preact else None
     h = _empty((r, m), torch.bfloat16, x2d)
     K.gemm(K.OP_NT, K.EPI_BIAS_GELU, r, m, d, ln, d, w1_16, d, a, m, C2=h, ldc2=m, bias=b1, dropout_p=p,

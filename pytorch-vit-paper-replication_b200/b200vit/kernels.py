@@ -176,6 +176,47 @@ def l2norm_sq_noalloc(ptrs_dev, sizes_dev, num_tensors, max_size, out_sumsq) -> 
             stream_ptr(out_sumsq.device))
 
 
+# ---- strict-precision ("fp32 mode") entry points ----------------------------------------------------------
+def split_bf16x3(src: torch.Tensor, ld_src: int, rows: int, cols: int, dst: torch.Tensor, ld_dst: int,
+                 part_stride: int, pattern: int, p: float = 0.0, seed: int = 0, offset: int = 0,
+                 row_period: int = 0) -> None:
+    _C.call("b200vit_split_bf16x3", _ptr(src), ld_src, rows, cols, _ptr(dst), ld_dst, part_stride, pattern, float(p),
+            int(seed), int(offset), row_period, stream_ptr(src.device))
+
+
+def im2col_patches_f32(image: torch.Tensor, patch: int) -> torch.Tensor:
+    _chk(image, torch.float32, "image")
+    b, c, h, w = image.shape
+    out = torch.empty((b * (h // patch) * (w // patch), c * patch * patch), dtype=torch.float32, device=image.device)
+    _C.call("b200vit_im2col_patches_f32", _ptr(image), _ptr(out), b, c, h, w, patch, stream_ptr(image.device))
+    return out
+
+
+def gelu_f32_fwd(a, h, p=0.0, seed=0, offset=0) -> None:
+    _C.call("b200vit_gelu_f32_fwd", _ptr(a), _ptr(h), a.numel(), float(p), int(seed), int(offset),
+            stream_ptr(a.device))
+
+
+def gelu_f32_bwd(a, dh, da, p=0.0, seed=0, offset=0) -> None:
+    _C.call("b200vit_gelu_f32_bwd", _ptr(a), _ptr(dh), _ptr(da), a.numel(), float(p), int(seed), int(offset),
+            stream_ptr(a.device))
+
+
+def colsum_f32(x, ld, rows, cols, out, p=0.0, seed=0, offset=0, row_period=0) -> None:
+    _C.call("b200vit_colsum_f32", _ptr(x), ld, rows, cols, _ptr(out), float(p), int(seed), int(offset), row_period,
+            stream_ptr(x.device))
+
+
+def attention_f32_fwd(qkv, out, lse, batch, tokens, heads, head_dim, scale) -> None:
+    _C.call("b200vit_attention_f32_fwd", _ptr(qkv), _ptr(out), _ptr(lse), batch, tokens, heads, head_dim, float(scale),
+            stream_ptr(qkv.device))
+
+
+def attention_f32_bwd(qkv, out, dout, lse, delta, dqkv, batch, tokens, heads, head_dim, scale) -> None:
+    _C.call("b200vit_attention_f32_bwd", _ptr(qkv), _ptr(out), _ptr(dout), _ptr(lse), _ptr(delta), _ptr(dqkv), batch,
+            tokens, heads, head_dim, float(scale), stream_ptr(qkv.device))
+
+
 def adam_step(table_dev, num_tensors, max_size, lrs, wds, beta1, beta2, eps, step, decoupled, grad_sumsq, max_norm,
               grad_scale) -> None:
     import ctypes

@@ -20,7 +20,20 @@ from __future__ import annotations
 import torch
 from torch import nn
 
+from .. import fp32 as FP_
 from .. import functional as F_
+
+
+def _check_geometry(embedding_dim: int, num_heads: int) -> None:
+    """The attention kernels are written for 64-wide heads and the LayerNorm backward for rows of at most 1024
+    values (ViT-B/16: 768 = 12 x 64, ViT-L/16: 1024 = 16 x 64). The reference accepts any pair; say so at construction
+    instead of failing inside the first forward."""
+    if embedding_dim != num_heads * F_.HEAD_DIM:
+        raise NotImplementedError(
+            f"b200vit supports head_dim == {F_.HEAD_DIM} only: embedding_dim {embedding_dim} with {num_heads} heads "
+            f"gives {embedding_dim / num_heads:g}")
+    if embedding_dim > F_.MAX_LN_DIM:
+        raise NotImplementedError(f"b200vit supports embedding_dim <= {F_.MAX_LN_DIM} (got {embedding_dim})")
 
 
 class PatchEmbedding(nn.Module):
@@ -50,6 +63,9 @@ class PatchEmbedding(nn.Module):
 
     def forward(self, x: torch.Tensor):
         conv = self.patch_and_flatten[0]
+        if F_.get_precision() == "fp32":
+            return FP_.PatchEmbedF32Fn.apply(x, conv.weight, conv.bias, self.class_token, self.position_embedding,
+                                             self.patch_size, self.dropout.p, self.training)
         return F_.PatchEmbedFn.apply(x, conv.weight, conv.bias, self.class_token, self.position_embedding,
                                      F_.bf16_shadow(conv.weight), self.patch_size, self.dropout.p, self.training)
 
@@ -62,12 +78,17 @@ class MultiHeadSelfAttentionBlock(nn.Module):
                  num_heads: int = 12,
                  attn_dropout: float = 0):
         super().__init__()
+        _check_geometry(embedding_dim, num_heads)
         self.layer_norm = nn.LayerNorm(normalized_shape=embedding_dim)
         self.multi_head_attention = nn.MultiheadAttention(embed_dim=embedding_dim, num_heads=num_heads,
                                                           dropout=attn_dropout, batch_first=True)
 
     def forward(self, x: torch.Tensor):
         mha = self.multi_head_attention
+        if F_.get_precision() == "fp32":
+            return FP_.MSAF32Fn.apply(x, self.layer_norm.weight, self.layer_norm.bias, mha.in_proj_weight,
+                                      mha.in_proj_bias, mha.out_proj.weight, mha.out_proj.bias, mha.num_heads,
+                                      mha.dropout, self.training, self.layer_norm.eps)
         # mha.dropout > 0 (attn_dropout): dropout on the attention probabilities in training mode, as torch does
         return F_.MSAFn.apply(x, self.layer_norm.weight, self.layer_norm.bias, mha.in_proj_weight, mha.in_proj_bias,
                               mha.out_proj.weight, mha.out_proj.bias, F_.bf16_shadow(mha.in_proj_weight),
@@ -94,6 +115,9 @@ class MLPBlock(nn.Module):
 
     def forward(self, x: torch.Tensor):
         fc1, fc2 = self.mlp[0], self.mlp[3]
+        if F_.get_precision() == "fp32":
+            return FP_.MLPF32Fn.apply(x, self.layer_norm.weight, self.layer_norm.bias, fc1.weight, fc1.bias, fc2.weight,
+                                      fc2.bias, self.mlp[2].p, self.training, self.layer_norm.eps)
         return F_.MLPFn.apply(x, self.layer_norm.weight, self.layer_norm.bias, fc1.weight, fc1.bias, fc2.weight,
                               fc2.bias, F_.bf16_shadow(fc1.weight), F_.bf16_shadow(fc2.weight), self.mlp[2].p,
                               self.training, torch.is_grad_enabled(), self.layer_norm.eps)
@@ -117,6 +141,12 @@ class TransformerEncoderBlock(nn.Module):
         msa, mlp = self.msa_block, self.mlp_block
         mha = msa.multi_head_attention
         fc1, fc2 = mlp.mlp[0], mlp.mlp[3]
+        if F_.get_precision() == "fp32":
+            return FP_.EncoderBlockF32Fn.apply(
+                x, msa.layer_norm.weight, msa.layer_norm.bias, mha.in_proj_weight, mha.in_proj_bias,
+                mha.out_proj.weight, mha.out_proj.bias, mlp.layer_norm.weight, mlp.layer_norm.bias, fc1.weight,
+                fc1.bias, fc2.weight, fc2.bias, mha.num_heads, mlp.mlp[2].p, self.training, mha.dropout,
+                msa.layer_norm.eps, mlp.layer_norm.eps)
         return F_.EncoderBlockFn.apply(
             x, msa.layer_norm.weight, msa.layer_norm.bias, mha.in_proj_weight, mha.in_proj_bias,
             mha.out_proj.weight, mha.out_proj.bias, mlp.layer_norm.weight, mlp.layer_norm.bias, fc1.weight, fc1.bias,

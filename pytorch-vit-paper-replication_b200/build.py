@@ -31,6 +31,7 @@ SOURCES = [
     "elementwise.cu",
     "head_loss.cu",
     "optim.cu",
+    "fp32_mode.cu",
 ]
 
 NVCC_FLAGS = [

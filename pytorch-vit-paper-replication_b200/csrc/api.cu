@@ -135,4 +135,42 @@ int b200vit_adam_step(const void* table_dev, int num_tensors, long long max_size
                             grad_sumsq, max_norm, grad_scale, (cudaStream_t)stream);
 }
 
+int b200vit_split_bf16x3(const float* src, long long ld_src, long long rows, int cols, void* dst_bf16, long long ld_dst,
+                         long long part_stride, int pattern, float dropout_p, unsigned long long seed,
+                         unsigned long long offset, int row_period, void* stream) {
+    return split_bf16x3_launch(src, ld_src, rows, cols, (bf16*)dst_bf16, ld_dst, part_stride, pattern, dropout_p, seed,
+                               offset, row_period, (cudaStream_t)stream);
+}
+
+int b200vit_im2col_patches_f32(const float* image, float* patches, int batch, int channels, int height, int width,
+                               int patch, void* stream) {
+    return im2col_f32_launch(image, patches, batch, channels, height, width, patch, (cudaStream_t)stream);
+}
+
+int b200vit_gelu_f32_fwd(const float* a, float* h, long long n, float dropout_p, unsigned long long seed,
+                         unsigned long long offset, void* stream) {
+    return gelu_f32_fwd_launch(a, h, n, dropout_p, seed, offset, (cudaStream_t)stream);
+}
+
+int b200vit_gelu_f32_bwd(const float* a, const float* dh, float* da, long long n, float dropout_p,
+                         unsigned long long seed, unsigned long long offset, void* stream) {
+    return gelu_f32_bwd_launch(a, dh, da, n, dropout_p, seed, offset, (cudaStream_t)stream);
+}
+
+int b200vit_colsum_f32(const float* x, long long ld, long long rows, int cols, float* out, float dropout_p,
+                       unsigned long long seed, unsigned long long offset, int row_period, void* stream) {
+    return colsum_f32_launch(x, ld, rows, cols, out, dropout_p, seed, offset, row_period, (cudaStream_t)stream);
+}
+
+int b200vit_attention_f32_fwd(const float* qkv, float* out, float* lse, int batch, int tokens, int heads, int head_dim,
+                              float scale, void* stream) {
+    return attention_f32_fwd_launch(qkv, out, lse, batch, tokens, heads, head_dim, scale, (cudaStream_t)stream);
+}
+
+int b200vit_attention_f32_bwd(const float* qkv, const float* out, const float* dout, const float* lse, float* delta,
+                              float* dqkv, int batch, int tokens, int heads, int head_dim, float scale, void* stream) {
+    return attention_f32_bwd_launch(qkv, out, dout, lse, delta, dqkv, batch, tokens, heads, head_dim, scale,
+                                    (cudaStream_t)stream);
+}
+
 }  // extern "C"

@@ -68,4 +68,22 @@ int adam_step_launch(const void* table_dev, int num_tensors, long long max_size,
                      int num_groups, float beta1, float beta2, float eps, int step, int decoupled,
                      const float* grad_sumsq, float max_norm, float grad_scale, cudaStream_t stream);
 
+// strict-precision ("fp32 mode") helpers, fp32_mode.cu
+int split_bf16x3_launch(const float* src, long long ld_src, long long rows, int cols, bf16* dst, long long ld_dst,
+                        long long part_stride, int pattern, float drop_p, unsigned long long seed,
+                        unsigned long long offset, int row_period, cudaStream_t stream);
+int im2col_f32_launch(const float* image, float* patches, int batch, int channels, int height, int width, int patch,
+                      cudaStream_t stream);
+int gelu_f32_fwd_launch(const float* a, float* h, long long n, float drop_p, unsigned long long seed,
+                        unsigned long long offset, cudaStream_t stream);
+int gelu_f32_bwd_launch(const float* a, const float* dh, float* da, long long n, float drop_p, unsigned long long seed,
+                        unsigned long long offset, cudaStream_t stream);
+int colsum_f32_launch(const float* x, long long ld, long long rows, int cols, float* out, float drop_p,
+                      unsigned long long seed, unsigned long long offset, int row_period, cudaStream_t stream);
+int attention_f32_fwd_launch(const float* qkv, float* out, float* lse, int batch, int tokens, int heads, int head_dim,
+                             float scale, cudaStream_t stream);
+int attention_f32_bwd_launch(const float* qkv, const float* out, const float* dout, const float* lse, float* delta,
+                             float* dqkv, int batch, int tokens, int heads, int head_dim, float scale,
+                             cudaStream_t stream);
+
 }  // namespace b200vit
