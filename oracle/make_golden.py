@@ -15,6 +15,10 @@ The reference is Python and cannot travel to the GPU box, so its outputs are fro
                        the same RNG consumption (tests check b200vit's constructor reproduces them).
   headless_tiny.npz    models/vit_no_classifier.py forward on the tiny config (weights = vit_tiny_train sd0 minus
                        the classifier: asserted identical here).
+  engine_tiny.npz      the reference's own engine.test_step (engine.py:81-130) on the tiny model at its initial weights
+                       over a ragged 3-batch loader, and engine.train (engine.py:132-211) for 3 epochs (4 train
+                       batches, the same test loader): the four metric lists it returns.   (`--only engine` writes
+                       just this file.)
 """
 from __future__ import annotations
 
@@ -52,6 +56,34 @@ def notebook_recipe(model, total_steps):
     return optimizer, sched, torch.nn.CrossEntropyLoss()
 
 
+def engine_fixture(ViT, engine):
+    """engine.test_step / engine.train of the unmodified reference on the tiny model (seed 42 weights = sd0 of
+    vit_tiny_train.npz)."""
+    torch.manual_seed(42)
+    model = ViT(**TINY)
+    g = torch.Generator().manual_seed(11)
+    sizes_train, sizes_test = [8, 8, 8, 6], [8, 8, 5]          # ragged last batches: mean of per-batch means
+    train = [(torch.rand(n, 3, 64, 64, generator=g), torch.randint(0, 10, (n,), generator=g)) for n in sizes_train]
+    test = [(torch.rand(n, 3, 64, 64, generator=g), torch.randint(0, 10, (n,), generator=g)) for n in sizes_test]
+    loss_fn = torch.nn.CrossEntropyLoss()
+    t_loss, t_acc = engine.test_step(model=model, dataloader=test, loss_fn=loss_fn, device="cpu")
+    epochs = 3
+    total_steps = 40                    # schedule horizon: 2 warm-up steps, then the decay (12 steps are run)
+    optimizer, sched, loss_fn = notebook_recipe(model, total_steps)
+    res = engine.train(model=model, train_dataloader=train, test_dataloader=test, optimizer=optimizer, loss_fn=loss_fn,
+                       lr_scheduler=sched, epochs=epochs, device="cpu")
+    out = dict(test_step_loss=np.float64(t_loss), test_step_acc=np.float64(t_acc), epochs=np.int64(epochs),
+               total_steps=np.int64(total_steps))
+    for k, v in res.items():
+        out["train/" + k] = np.array(v, dtype=np.float64)
+    for i, (X, y) in enumerate(train):
+        out[f"train_X{i}"], out[f"train_y{i}"] = X.numpy(), y.numpy()
+    for i, (X, y) in enumerate(test):
+        out[f"test_X{i}"], out[f"test_y{i}"] = X.numpy(), y.numpy()
+    np.savez_compressed(OUT / "engine_tiny.npz", **out)
+    print("engine fixture: test_step", t_loss, t_acc, "train", res)
+
+
 def main():
     if not REF.exists():
         sys.exit("reference not mounted at /root/reference")
@@ -63,6 +95,9 @@ def main():
 
     OUT.mkdir(parents=True, exist_ok=True)
     torch.set_num_threads(8)
+    if "--only" in sys.argv and sys.argv[sys.argv.index("--only") + 1] == "engine":
+        engine_fixture(ViT, engine)
+        return
 
     # ---- tiny training fixture -------------------------------------------------------------------
     torch.manual_seed(42)
@@ -126,6 +161,7 @@ def main():
                         notebook=np.array([[0.6136, -0.9092, 0.5918]], dtype=np.float32),
                         **{f"chk/{k}": v for k, v in checks.items()})
     print("train-mode logits", out_train, "eval", out_eval)
+    engine_fixture(ViT, engine)
     print("written to", OUT)
 
 

@@ -231,3 +231,35 @@ class OracleTrainer:
                             self.weight_decay if k in self.decay else 0.0)
         self.step_idx += 1
         return loss.item(), accuracy(logits.detach(), y)
+
+    def epoch(self, loader) -> Tuple[float, float]:
+        """engine.train_step over a whole loader (engine.py:45-79): mean of the per-batch losses / accuracies."""
+        tot_l = tot_a = 0.0
+        for X, y in loader:
+            l, a = self.step(X, y)
+            tot_l += l
+            tot_a += a
+        return tot_l / len(loader), tot_a / len(loader)
+
+
+def evaluate(sd: Dict[str, Tensor], cfg: ViTConfig, loader) -> Tuple[float, float]:
+    """engine.test_step (engine.py:81-130): eval-mode forward under no_grad, mean of per-batch loss / accuracy."""
+    tot_l = tot_a = 0.0
+    with torch.no_grad():
+        for X, y in loader:
+            logits = vit_forward(X, sd, cfg, training=False)
+            tot_l += cross_entropy(logits, y).item()
+            tot_a += accuracy(logits, y)
+    return tot_l / len(loader), tot_a / len(loader)
+
+
+def train(sd: Dict[str, Tensor], cfg: ViTConfig, train_loader, test_loader, epochs: int, total_steps: int):
+    """engine.train (engine.py:132-211) with the notebook recipe: the four per-epoch metric lists."""
+    tr = OracleTrainer(sd, cfg, total_steps=total_steps)
+    res = {"train_loss": [], "train_acc": [], "test_loss": [], "test_acc": []}
+    for _ in range(epochs):
+        tl, ta = tr.epoch(train_loader)
+        el, ea = evaluate(tr.sd, cfg, test_loader)
+        res["train_loss"].append(tl); res["train_acc"].append(ta)
+        res["test_loss"].append(el); res["test_acc"].append(ea)
+    return res

@@ -1,7 +1,6 @@
 """Parity cases for the other BASELINE.json configs (they are test cases, not bench lines):
 config 2 (1000-class head), config 3 (ViT-L/16 @384: 577 tokens, d=1024, 16 heads -> long-sequence attention path,
-LayerNorm D=1024), config 4 (headless forward-only sweep over batch sizes), plus the north-star 200-step seeded
-loss curve (tiny ViT so that the CPU oracle finishes in seconds)."""
+LayerNorm D=1024), config 4 (headless forward-only sweep over batch sizes). The 200-step loss curves are in test_loss_curve_gpu.py."""
 import numpy as np
 import pytest
 import torch
@@ -95,41 +94,3 @@ def test_headless_vit_b16_forward_b1():
         out = m.to(dev()).eval()(X.to(dev()))
     assert out.shape == (1, 197, 768)
     assert rel_err(out, ref) < BF16_TOL
-
-
-def test_loss_curve_200_steps_within_one_percent():
-    """North-star gate: 200 seeded optimizer steps (notebook recipe: Adam coupled L2, clip 1.0, warm-up + linear decay,
-    dropout 0) of b200vit on the GPU vs the fp32 CPU oracle: the loss curves stay within 1 %."""
-    from b200vit.going_modular import engine
-    from b200vit.nn import CrossEntropyLoss
-    from common import notebook_recipe
-    from b200vit.models.vit import ViT
-    tiny = load_npz("vit_tiny_train.npz")
-    sd0 = sub(tiny, "sd0/")
-    steps = 200
-    g = torch.Generator().manual_seed(77)
-    pool = [(torch.rand(16, 3, 64, 64, generator=g), torch.randint(0, 10, (16,), generator=g)) for _ in range(8)]
-    batches = [pool[i % 8] for i in range(steps)]
-    tr = O.OracleTrainer(sd0, O.ViTConfig(**TINY), total_steps=steps)
-    ref = [tr.step(X, y)[0] for X, y in batches]
-    m = ViT(**TINY)
-    m.load_state_dict(sd0)
-    m = m.to(dev())
-    opt, sched = notebook_recipe(m, steps, fused=True)
-    loss_fn = CrossEntropyLoss()
-    ours = [engine.train_step(m, [b], loss_fn, opt, sched, dev())[0] for b in batches]
-    ref, ours = np.array(ref), np.array(ours)
-    assert ref[-1] < 0.8 * ref[0], "the run must actually learn for the comparison to mean something"
-    rel = np.abs(ours - ref) / np.abs(ref)
-    import json, os
-    if os.path.isdir("gpurun_out"):
-        json.dump({"oracle": ref.tolist(), "b200vit": ours.tolist()}, open("gpurun_out/loss_curve_200.json", "w"))
-    # The run is chaotic late on (lr 1e-3, 8 memorised batches): split-K atomics reorder fp32 sums from run to run and
-    # the per-step deviation at the tail wanders between 0.3 % and 1 %. The 1 % gate is applied to the curve smoothed
-    # over one pass through the batch pool (SURVEY 7.4-4); single steps get 2.5 %.
-    k = np.ones(8) / 8
-    sm_ref, sm_ours = np.convolve(ref, k, mode="valid"), np.convolve(ours, k, mode="valid")
-    sm_rel = np.abs(sm_ours - sm_ref) / sm_ref
-    assert sm_rel.max() < 1e-2, (sm_rel.max(), int(sm_rel.argmax()))
-    assert rel[:100].max() < 1e-2, rel[:100].max()
-    assert rel.max() < 2.5e-2, (rel.max(), int(rel.argmax()))

@@ -60,6 +60,23 @@ def test_oracle_train_steps_match_reference_engine(tiny):
             assert rel_err(tr.sd[k], v) < 1e-4, k
 
 
+def test_oracle_test_step_and_train_match_reference_engine(tiny):
+    """engine.test_step (engine.py:81-130) and engine.train (engine.py:132-211) of the unmodified reference, recorded
+    in tests/golden/engine_tiny.npz, vs the oracle's restatements."""
+    from common import engine_loaders
+    eng = load_npz("engine_tiny.npz")
+    train, test = engine_loaders(eng)
+    assert [len(y) for _, y in train] == [8, 8, 8, 6] and [len(y) for _, y in test] == [8, 8, 5]
+    sd = sub(tiny, "sd0/")
+    l, a = O.evaluate(sd, tiny_cfg(), test)
+    assert abs(l - float(eng["test_step_loss"])) < 1e-5 and a == pytest.approx(float(eng["test_step_acc"]), abs=1e-12)
+    res = O.train(sd, tiny_cfg(), train, test, int(eng["epochs"]), int(eng["total_steps"]))
+    for k in ("train_loss", "test_loss"):
+        np.testing.assert_allclose(res[k], eng["train/" + k], rtol=2e-4)
+    for k in ("train_acc", "test_acc"):
+        np.testing.assert_allclose(res[k], eng["train/" + k], atol=1e-12)
+
+
 def test_lr_schedule_matches_torch_sequential_lr():
     lin = torch.nn.Linear(2, 2)
     opt = torch.optim.Adam(lin.parameters(), lr=1e-3)
