@@ -163,6 +163,7 @@ int b200vit_head_bwd(const float* xn, const float* w, const float* dlogits, floa
 /* nn.CrossEntropyLoss() (mean) fused with its gradient and the accuracy counter:
  *   *loss = mean_b(logsumexp(z_b) - z_b[y_b]) ; dlogits (optional) = (softmax(z) - onehot(y)) / B ;
  *   *correct (optional) = #{b : argmax(z_b) == y_b}.
+ * A label outside [0, classes) makes *loss and that sample's dlogits row NaN (torch raises a device-side assert there).
  * Replaces loss_fn(y_pred, y) and the argmax(softmax(.)) == y count of going_modular/engine.py:53, 73-74, 121-125. */
 int b200vit_softmax_ce(const float* logits, const long long* labels, float* loss, float* dlogits, int* correct,
                        int batch, int classes, void* stream);

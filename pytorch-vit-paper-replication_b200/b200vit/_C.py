@@ -122,9 +122,29 @@ def check(rc: int, what: str) -> None:
 KERNELS_PER_CALL = {"b200vit_l2norm_sq": 2, "b200vit_l2norm_sq_noalloc": 2,
                     "b200vit_head_bwd": 2, "b200vit_attention_f32_bwd": 2}
 launch_count = 0
+call_count = 0          # Python -> C transitions (one per entry-point call)
+want_device = None      # CUDA device ordinal of the tensors of the call being prepared (set by kernels.stream_ptr)
+_current_device = None  # bound lazily to torch.cuda.current_device
 
 
 def call(name: str, *args) -> None:
-    global launch_count
-    check(getattr(lib(), name)(*args), name)
+    """Invoke one entry point and raise on a non-zero return. Kernels launch on the stream that kernels.stream_ptr()
+    looked up for the tensors' device; if that is not the CUDA current device (a model on cuda:1 without a prior
+    torch.cuda.set_device(1)) the call runs under a device guard, as torch's own operators do."""
+    global launch_count, call_count, _current_device
+    fn = getattr(lib(), name)
+    dev = want_device
+    if dev is not None:
+        if _current_device is None:
+            import torch
+            _current_device = torch.cuda.current_device
+        if dev != _current_device():
+            import torch
+            with torch.cuda.device(dev):
+                check(fn(*args), name)
+            launch_count += KERNELS_PER_CALL.get(name, 1)
+            call_count += 1
+            return
+    check(fn(*args), name)
     launch_count += KERNELS_PER_CALL.get(name, 1)
+    call_count += 1

@@ -11,22 +11,35 @@ wrapper is the one exchange step that data-parallel training of its hot path nee
 Mechanics
   * parameters are grouped, in reverse registration order (~ the order backward produces gradients), into
     buckets of ~`bucket_mb` MB backed by one flat fp32 buffer each;
-  * a post-accumulate-grad hook moves each fresh gradient into its slice of the bucket and makes `p.grad` a
-    view of that slice (so the reduced values are seen by clip_grad_norm_ / any optimizer without a copy back);
+  * the b200vit encoder blocks write their parameter gradients STRAIGHT into their bucket slices (the weight-gradient
+    GEMMs accumulate there; b200vit.functional.grad_out), so `p.grad` is born as a view of the bucket and nothing is
+    copied; gradients produced by anything else (other modules, stock torch layers) are moved into their slice by a
+    post-accumulate-grad hook, after which `p.grad` is that view too (the reduced values are seen by
+    clip_grad_norm_ / any optimizer without a copy back);
   * the flat buffers are all-reduced (SUM) asynchronously on NCCL's own stream -- each one as soon as it is complete
     (default), or all of them from the end-of-backward engine callback (`overlap=False`);
   * the end-of-backward callback waits for the outstanding reductions, so gradients are final when
     `loss.backward()` returns (the reference engine calls clip_grad_norm_ right after, engine.py:60-63).
 Gradients hold the SUM over ranks; `grad_scale` (1/world) is applied by FusedAdam on the fly, or call
 `average_gradients()` before a stock optimizer.
+
+Gradient accumulation over micro-batches: run every micro-step but the last under `no_sync()`. A second synchronised
+backward on top of already reduced gradients (no `zero_grad()` and no `no_sync()` in between) would reduce the first
+step's sum a second time; it is detected and refused.
+
+Every rank gets its own family of dropout masks (functional.set_dropout_stream(rank)): ranks seeded alike -- the usual
+`torch.manual_seed(42)` on all of them -- still drop independently over their shards of the global batch.
 """
 from __future__ import annotations
 
-from typing import List, Optional
+import os
+from typing import List, Optional, Tuple
 
 import torch
 import torch.distributed as dist
 from torch import nn
+
+from . import functional as F_
 
 
 class _Bucket:
@@ -34,13 +47,19 @@ class _Bucket:
         self.params = params
         n = sum(p.numel() for p in params)
         self.flat = torch.zeros(n, dtype=params[0].dtype, device=params[0].device)
-        self.views = []
+        self.offsets = []
         off = 0
         for p in params:
-            self.views.append(self.flat[off:off + p.numel()].view(p.shape))
+            self.offsets.append(off)
             off += p.numel()
         self.pending = len(params)
         self.work = None
+
+    def view(self, i: int) -> torch.Tensor:
+        """A FRESH tensor object over parameter i's slice (autograd adopts a gradient without copying only when nobody
+        else holds a reference to the tensor object it is handed)."""
+        p = self.params[i]
+        return self.flat[self.offsets[i]:self.offsets[i] + p.numel()].view(p.shape)
 
 
 class DataParallel(nn.Module):
@@ -51,7 +70,6 @@ class DataParallel(nn.Module):
         # continues; overlap=False starts them all at the end of backward. Measured on 2 B200 (batch 256 per GPU):
         # 37.05 ms/step overlapped, 37.39 ms at the end, 36.1 ms single-GPU. B200VIT_DP_OVERLAP=0/1 overrides.
         if overlap is None:
-            import os
             overlap = os.environ.get("B200VIT_DP_OVERLAP", "1") == "1"
         self.overlap = bool(overlap)
         if not dist.is_initialized():
@@ -59,12 +77,15 @@ class DataParallel(nn.Module):
         self.module = module
         self.group = process_group
         self.world = dist.get_world_size(process_group)
+        self.rank = dist.get_rank(process_group)
         self.grad_scale = 1.0 / self.world
         self.sync = True
+        F_.set_dropout_stream(self.rank)
         if broadcast:
-            for t in list(module.parameters()) + list(module.buffers()):
-                dist.broadcast(t.data, src=dist.get_global_rank(process_group, 0) if process_group else 0,
-                               group=process_group)
+            src = dist.get_global_rank(process_group, 0) if process_group else 0
+            with torch.no_grad():       # in place on the tensor itself: bumps its version, so bf16 shadows made before
+                for t in list(module.parameters()) + list(module.buffers()):      # wrapping are re-cast, not stale
+                    dist.broadcast(t, src=src, group=process_group)
         params = [p for p in module.parameters() if p.requires_grad]
         limit = int(bucket_mb * 1024 * 1024)
         self.buckets: List[_Bucket] = []
@@ -82,14 +103,23 @@ class DataParallel(nn.Module):
             for i, p in enumerate(b.params):
                 self._where[p] = (b, i)
                 p.register_post_accumulate_grad_hook(self._on_grad)
+                F_.register_grad_destination(p, lambda b=b, i=i: b.view(i))
         self._callback_queued = False
 
     # -- hooks ---------------------------------------------------------------------------------------
     def _on_grad(self, p: nn.Parameter) -> None:
         b, i = self._where[p]
-        view = b.views[i]
-        if p.grad.data_ptr() != view.data_ptr():
-            view.copy_(p.grad)
+        g = p.grad
+        # same tensor object as when it was reduced, and exactly one in-place write since: autograd's `grad += new`
+        # (zero_grad(set_to_none=False) writes every slice of the bucket first; set_to_none=True makes new objects)
+        if self.sync and getattr(g, "_b200vit_reduced", None) == g._version - 1:
+            raise RuntimeError(
+                "DataParallel: a synchronised backward accumulated into gradients that were already all-reduced; the "
+                "earlier sum would be reduced again. Call zero_grad() between optimizer steps, and run every "
+                "micro-batch but the last of a gradient-accumulation step under DataParallel.no_sync().")
+        if g.data_ptr() != b.flat.data_ptr() + b.offsets[i] * b.flat.element_size():
+            view = b.view(i)
+            view.copy_(g)
             p.grad = view
         if not self.sync:
             return
@@ -106,14 +136,17 @@ class DataParallel(nn.Module):
                 # not started yet (overlap off), or some parameters of this bucket got no gradient this step:
                 # reduce what is there (the missing ones are zero)
                 if b.pending != 0:
-                    for p, v in zip(b.params, b.views):
+                    for j, p in enumerate(b.params):
                         if p.grad is None:
-                            v.zero_()
+                            b.view(j).zero_()
                 b.work = dist.all_reduce(b.flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
         for b in self.buckets:
             if b.work is not None:
                 b.work.wait()
                 b.work = None
+                for p in b.params:
+                    if p.grad is not None:
+                        p.grad._b200vit_reduced = p.grad._version
             b.pending = len(b.params)
         self._callback_queued = False
 
@@ -125,6 +158,16 @@ class DataParallel(nn.Module):
         """Turn the summed gradients into means (only needed with optimizers that have no grad_scale)."""
         for b in self.buckets:
             b.flat.mul_(self.grad_scale)
+
+    def reduce_metrics(self, loss: float, acc: float) -> Tuple[float, float]:
+        """Mean over ranks of the two epoch metrics (one 2-element all-reduce per epoch): what engine.train_step /
+        test_step return is then the figure for the GLOBAL batches, as a single-process run of the reference over the
+        whole data would report (engine.py:77-79, 128-130), identical on every rank."""
+        dev = self.buckets[0].flat.device if self.buckets else torch.device("cpu")
+        t = torch.tensor([loss, acc], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        t /= self.world
+        return float(t[0]), float(t[1])
 
     class _NoSync:
         def __init__(self, dp):

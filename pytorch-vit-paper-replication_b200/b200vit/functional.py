@@ -107,6 +107,18 @@ def shadow_entry(p: torch.Tensor) -> Optional[_Shadow]:
     return _lookup(p)
 
 
+def refresh_shadows(model: torch.nn.Module) -> None:
+    """Re-cast every bf16 weight shadow of `model` now. Shadows follow a parameter's version counter and storage
+    address; writes that bypass the counter -- `p.data.add_(...)` in old-style optimizers, EMA weight swaps through
+    `.data`, `dist.broadcast(p.data, ...)` -- leave them stale. Call this after such a write (in-place ops on the
+    parameter itself under `torch.no_grad()`, `load_state_dict`, `optimizer.step()` need nothing)."""
+    for p in model.parameters():
+        e = _lookup(p)
+        if e is not None:
+            e.version = -1
+            bf16_shadow(p)
+
+
 # ---------------------------------------------------------------------------------------------------------
 # dropout seeds: a mask is a function of (seed, offset, element index); offsets count dropout sites
 # ---------------------------------------------------------------------------------------------------------
@@ -116,7 +128,6 @@ def shadow_entry(p: torch.Tensor) -> Optional[_Shadow]:
 # `_dropout_stream` is mixed into the seed: b200vit.dp.DataParallel sets it to the rank so that ranks seeded alike
 # (the usual `torch.manual_seed(42)` everywhere) still draw independent masks for their shards of the global batch.
 _dropout_stream = 0
-_cpu_counter = [None, 0]      # test doubles without CUDA: (seed the count belongs to, count)
 
 
 def set_dropout_stream(stream: int) -> int:
@@ -135,12 +146,9 @@ def next_dropout_key(device=None) -> Tuple[int, int]:
         seed, off = gen.initial_seed(), gen.get_offset()
         gen.set_offset(off + 4)                     # Philox offsets advance in steps of 4, as torch's own draws do
         count = off // 4 + 1
-    else:
+    else:       # CPU test doubles only: draw the counter from torch's CPU generator, which has no offset to advance
         seed = torch.initial_seed()
-        if _cpu_counter[0] != seed:
-            _cpu_counter[0], _cpu_counter[1] = seed, 0
-        _cpu_counter[1] += 1
-        count = _cpu_counter[1]
+        count = int(torch.empty((), dtype=torch.int64).random_(0, 1 << 62))
     seed = (seed ^ (_dropout_stream * 0x9E3779B97F4A7C15)) & 0xFFFFFFFFFFFFFFFF
     return seed, count
 
@@ -165,6 +173,42 @@ def _zeros(shape, like: torch.Tensor) -> torch.Tensor:
     return torch.zeros(shape, dtype=torch.float32, device=like.device)
 
 
+# ---------------------------------------------------------------------------------------------------------
+# Where parameter gradients are written. By default a backward node allocates them; a data-parallel wrapper may
+# register, per parameter, a slice of its flat all-reduce buffer as the destination (b200vit.dp): the weight-gradient
+# GEMMs then accumulate straight into the communication buffer and `p.grad` is born as a view of it -- no gather copy.
+# ---------------------------------------------------------------------------------------------------------
+_GRAD_DEST: dict = {}      # id(parameter) -> (weakref to it, callable returning a fresh view of its destination)
+
+
+def register_grad_destination(p: torch.Tensor, make_view) -> None:
+    key = id(p)
+    _GRAD_DEST[key] = (weakref.ref(p, lambda _r, k=key: _GRAD_DEST.pop(k, None)), make_view)
+
+
+def unregister_grad_destination(p: torch.Tensor) -> None:
+    _GRAD_DEST.pop(id(p), None)
+
+
+def grad_out(p: Optional[torch.Tensor], shape, like: torch.Tensor, zero: bool, arena=None) -> torch.Tensor:
+    """Buffer for the gradient of parameter `p`: its registered destination when it has one and no gradient has been
+    accumulated yet this step (`p.grad is None`; otherwise autograd must add, so a temporary is returned), else the
+    next piece of `arena` (zero-filled) or a fresh allocation."""
+    if p is not None and p.grad is None:
+        e = _GRAD_DEST.get(id(p))
+        if e is not None and e[0]() is p:
+            t = e[1]()
+            if tuple(t.shape) == tuple(shape) and t.device == like.device:
+                if zero:
+                    t.zero_()
+                if arena:
+                    arena.skip()
+                return t
+    if arena:
+        return arena.take()
+    return _zeros(shape, like) if zero else _empty(shape, torch.float32, like)
+
+
 class _ZeroArena:
     """One zero-filled fp32 allocation carved into the accumulate-into buffers of a backward node (split-K weight
     gradients, atomically accumulated bias gradients): one fill launch instead of one per buffer. Each piece starts
@@ -184,6 +228,9 @@ class _ZeroArena:
 
     def take(self) -> torch.Tensor:
         return self._views.pop(0)
+
+    def skip(self) -> None:
+        self._views.pop(0)
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -285,32 +332,35 @@ def _msa_forward(x2d, bn, t, heads, ln_w, ln_b, w_in16, b_in, w_out16, b_out, re
 
 
 def _msa_backward(g, saved, bn, t, heads, ln_w, w_in16, w_out16, has_residual, g16=None, db_out=None,
-                  adrop=(0.0, (0, 0)), arena=None, consumer_drop=None):
+                  adrop=(0.0, (0, 0)), arena=None, consumer_drop=None, params=None):
+    # params (optional): the Parameters (ln_w, ln_b, w_in, b_in, w_out, b_out) whose gradients are produced here; when a
+    # gradient destination is registered for one of them (data parallel) its gradient is written there directly
     x2d, mean, rstd, ln, qkv, o, lse = saved
     r, d = x2d.shape
     dev = x2d.device
+    P = params if params is not None else (None,) * 6
     if g16 is None:
         g16 = _empty((r, d), torch.bfloat16, x2d)
-        db_out = _empty((d,), torch.float32, x2d)
+        db_out = grad_out(P[5], (d,), x2d, zero=False)
         K.dropout_cast(g, g16, db_out, r, d, 0.0, 0, 0)
     if arena is None:
         arena = _ZeroArena(x2d, [(d, d), (3 * d, d)])
-    dw_out = arena.take()
+    dw_out = grad_out(P[4], (d, d), x2d, zero=True, arena=arena)
     K.gemm(K.OP_TN, K.EPI_ACCUM, d, d, r, g16, d, o, d, dw_out, d, split_k=K.split_k_for(d, d, r, dev))
     do = _empty((r, d), torch.bfloat16, x2d)
     K.gemm(K.OP_NN, K.EPI_BF16, r, d, d, g16, d, w_out16, d, do, d)
     delta = _empty((bn, heads, t), torch.float32, x2d)
     dqkv = _empty((r, 3 * d), torch.bfloat16, x2d)
-    db_in = _empty((3 * d,), torch.float32, x2d)       # in_proj_bias gradient: column sums of dqkv, from the same kernel
+    db_in = grad_out(P[3], (3 * d,), x2d, zero=False)  # in_proj_bias gradient: column sums of dqkv, from the same kernel
     K.attention_bwd(qkv, o, do, lse, delta, dqkv, bn, t, heads, HEAD_DIM, 1.0 / math.sqrt(HEAD_DIM), dbias=db_in,
                     dropout_p=adrop[0], seed=adrop[1][0], offset=adrop[1][1])
-    dw_in = arena.take()
+    dw_in = grad_out(P[2], (3 * d, d), x2d, zero=True, arena=arena)
     K.gemm(K.OP_TN, K.EPI_ACCUM, 3 * d, d, r, dqkv, 3 * d, ln, d, dw_in, d, split_k=K.split_k_for(3 * d, d, r, dev))
     dln = _empty((r, d), torch.bfloat16, x2d)
     K.gemm(K.OP_NN, K.EPI_BF16, r, d, 3 * d, dqkv, 3 * d, w_in16, d, dln, d)
     gx = _empty((r, d), torch.float32, x2d)
-    dgamma = _empty((d,), torch.float32, x2d)
-    dbeta = _empty((d,), torch.float32, x2d)
+    dgamma = grad_out(P[0], (d,), x2d, zero=False)
+    dbeta = grad_out(P[1], (d,), x2d, zero=False)
     if consumer_drop is None:
         K.layernorm_bwd(dln, None, x2d, d, mean, rstd, ln_w, g if has_residual else None, gx, d, None, dgamma, dbeta,
                         None, r, d)
@@ -346,37 +396,41 @@ def _mlp_forward(x2d, ln_w, ln_b, w1_16, b1, w2_16, b2, p, residual, keep_preact
     return y, (x2d, mean, rstd, ln, a, h), (p, key1, key2)
 
 
-def _mlp_backward(g, saved, drop, ln_w, w1_16, w2_16, has_residual, want_bf16_out, arena=None):
+def _mlp_backward(g, saved, drop, ln_w, w1_16, w2_16, has_residual, want_bf16_out, arena=None, params=None,
+                  next_bias_param=None):
+    # params (optional): the Parameters (ln_w, ln_b, w1, b1, w2, b2); next_bias_param: the bias whose gradient the
+    # LayerNorm backward below emits on the side (out_proj.bias of the same block) -- see _msa_backward
     x2d, mean, rstd, ln, a, h = saved
     p, key1, key2 = drop
     r, d = x2d.shape
     m = w1_16.shape[0]
     dev = x2d.device
+    P = params if params is not None else (None,) * 6
     side = _GRAD_SIDE.pop(g.data_ptr(), None)
     if side is not None and side[2] == p and side[3] == tuple(key2) and side[4] == g._version and \
             side[0].shape == (r, d):
         g16, db2 = side[0], side[1]     # produced by the next block's LayerNorm backward together with g
     else:
         g16 = _empty((r, d), torch.bfloat16, x2d)
-        db2 = _empty((d,), torch.float32, x2d)
+        db2 = grad_out(P[5], (d,), x2d, zero=False)
         K.dropout_cast(g, g16, db2, r, d, p, key2[0], key2[1])
     if arena is None:
         arena = _ZeroArena(x2d, [(d, m), (m,), (m, d)])
-    dw2 = arena.take()
+    dw2 = grad_out(P[4], (d, m), x2d, zero=True, arena=arena)
     K.gemm(K.OP_TN, K.EPI_ACCUM, d, m, r, g16, d, h, m, dw2, m, split_k=K.split_k_for(d, m, r, dev))
     da = _empty((r, m), torch.bfloat16, x2d)
-    db1 = arena.take()
+    db1 = grad_out(P[3], (m,), x2d, zero=True, arena=arena)
     # a = mask * gelu'(pre-activation); the epilogue also accumulates the fc1 bias gradient (column sums of da) into db1
     K.gemm(K.OP_NN, K.EPI_DGELU, r, m, d, g16, d, w2_16, m, da, m, bias=db1, aux=a, ldaux=m)
-    dw1 = arena.take()
+    dw1 = grad_out(P[2], (m, d), x2d, zero=True, arena=arena)
     K.gemm(K.OP_TN, K.EPI_ACCUM, m, d, r, da, m, ln, d, dw1, d, split_k=K.split_k_for(m, d, r, dev))
     dln = g16  # reuse: g16 is dead after the two GEMMs above (same shape / dtype)
     K.gemm(K.OP_NN, K.EPI_BF16, r, d, m, da, m, w1_16, d, dln, d)
     gx = _empty((r, d), torch.float32, x2d)
-    dgamma = _empty((d,), torch.float32, x2d)
-    dbeta = _empty((d,), torch.float32, x2d)
+    dgamma = grad_out(P[0], (d,), x2d, zero=False)
+    dbeta = grad_out(P[1], (d,), x2d, zero=False)
     gx16 = _empty((r, d), torch.bfloat16, x2d) if want_bf16_out else None
-    dbn = _empty((d,), torch.float32, x2d) if want_bf16_out else None
+    dbn = grad_out(next_bias_param, (d,), x2d, zero=False) if want_bf16_out else None
     K.layernorm_bwd(dln, None, x2d, d, mean, rstd, ln_w, g if has_residual else None, gx, d, gx16, dgamma, dbeta,
                     dbn, r, d)
     return gx, (dgamma, dbeta, dw1, db1, dw2, db2), gx16, dbn
@@ -449,6 +503,8 @@ class EncoderBlockFn(torch.autograd.Function):
                 w_in16, w_out16, w1_16, w2_16, heads: int, p: float, training: bool, attn_p: float = 0.0,
                 grad_mode: bool = True, eps_msa: float = LN_EPS, eps_mlp: float = LN_EPS):
         _require_cuda(x, "TransformerEncoderBlock")
+        # the Parameters themselves (not saved tensors): backward asks functional.grad_out where each gradient goes
+        ctx.grad_params = (a_ln_w, a_ln_b, w_in, b_in, w_out, b_out, m_ln_w, m_ln_b, w1, b1, w2, b2)
         x = _f32c(x)
         bn, t, d = x.shape
         x2d = x.view(bn * t, d)
@@ -476,12 +532,17 @@ class EncoderBlockFn(torch.autograd.Function):
         d = g.shape[-1]
         g2 = _f32c(g).view(bn * t, d)
         m = w1_16.shape[0]
-        arena = _ZeroArena(g2, [(d, m), (m,), (m, d), (d, d), (3 * d, d)])     # in the order the helpers take them
+        gp = ctx.grad_params
+        direct = any(id(q) in _GRAD_DEST for q in gp)
+        # one zero-fill for the five accumulate-into buffers -- unless they live in a registered destination
+        # (False = no arena: whatever is not written to a destination is allocated on demand)
+        arena = False if direct else _ZeroArena(g2, [(d, m), (m,), (m, d), (d, d), (3 * d, d)])   # in the order taken
         g1, (m_dgam, m_dbet, dw1, db1, dw2, db2), g1_16, db_out = _mlp_backward(
-            g2, s_mlp, ctx.drop, m_ln_w, w1_16, w2_16, has_residual=True, want_bf16_out=True, arena=arena)
+            g2, s_mlp, ctx.drop, m_ln_w, w1_16, w2_16, has_residual=True, want_bf16_out=True, arena=arena,
+            params=gp[6:12], next_bias_param=gp[5])
         g0, (a_dgam, a_dbet, dw_in, db_in, dw_out, db_out) = _msa_backward(
             g1, s_msa, bn, t, heads, a_ln_w, w_in16, w_out16, has_residual=True, g16=g1_16, db_out=db_out,
-            adrop=ctx.adrop, arena=arena, consumer_drop=ctx.consumer_drop)
+            adrop=ctx.adrop, arena=arena, consumer_drop=ctx.consumer_drop, params=gp[0:6])
         return (g0.view(bn, t, d), a_dgam, a_dbet, dw_in, db_in, dw_out, db_out, m_dgam, m_dbet, dw1, db1, dw2, db2,
                 None, None, None, None, None, None, None, None, None, None, None)
 

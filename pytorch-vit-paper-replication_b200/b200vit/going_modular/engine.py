@@ -10,6 +10,13 @@ What differs from the reference is only *how* the same numbers are produced:
     optimizer kernel; any other torch optimizer takes the reference's clip_grad_norm_ + step() path;
   * with `b200vit.nn.CrossEntropyLoss`, the accuracy count comes out of the loss kernel.
 Any iterable of (X, y) batches with a len() works as a dataloader, as in the reference.
+
+Two additions that the reference does not have, both inert unless asked for:
+  * under `b200vit.dp.DataParallel` the two epoch metrics are averaged over the ranks (one 2-element all-reduce per
+    epoch), so every rank returns the figure for the global batches;
+  * `train_step(..., accumulation_steps=k)` (keyword-only) makes one optimizer step per k loader batches -- gradients
+    of the k micro-batches are averaged, all but the last backward run under `DataParallel.no_sync()` -- which is how a
+    global batch that does not fit (BASELINE.json configs[2]: 4096 images on 1 or 2 GPUs) is run with unchanged math.
 """
 from __future__ import annotations
 
@@ -89,11 +96,13 @@ class _EpochMetrics:
         self.host[self.i].copy_(pair, non_blocking=True)
         self.i += 1
 
-    def means(self) -> Tuple[float, float]:
+    def means(self, model=None) -> Tuple[float, float]:
         if self.dev.type == "cuda":
             torch.cuda.current_stream(self.dev).synchronize()
         tot = self.host[:self.i].double().sum(dim=0)
-        return float(tot[0]) / self.n, float(tot[1]) / self.n
+        loss, acc = float(tot[0]) / self.n, float(tot[1]) / self.n
+        reduce = getattr(model, "reduce_metrics", None)        # b200vit.dp.DataParallel: mean over the ranks
+        return reduce(loss, acc) if callable(reduce) else (loss, acc)
 
 
 def _batch_correct(loss_fn, logits: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
@@ -108,19 +117,40 @@ def train_step(model: torch.nn.Module,
                loss_fn: torch.nn.Module,
                optimizer: torch.optim.Optimizer,
                lr_scheduler: torch.optim.lr_scheduler,
-               device: torch.device) -> Tuple[float, float]:
+               device: torch.device,
+               *, accumulation_steps: int = 1) -> Tuple[float, float]:
     """One epoch of training; returns (mean batch loss, mean batch accuracy)."""
     model.train()
     metrics = _EpochMetrics(len(dataloader), device)
     fused_opt = isinstance(optimizer, _FusedAdam)
+    k = int(accumulation_steps)
+    if k < 1:
+        raise ValueError("accumulation_steps must be >= 1")
+    no_sync = getattr(model, "no_sync", None)
+    inv_k = None        # upstream gradient 1/k handed to backward(): averages the k micro-batch gradients
 
     for batch, (X, y) in enumerate(_device_batches(dataloader, device)):
         y_pred = model(X)
         loss = loss_fn(y_pred, y)
         metrics.add(loss, _batch_correct(loss_fn, y_pred.detach(), y) / len(y_pred))
 
-        optimizer.zero_grad()
-        loss.backward()
+        if k == 1:
+            optimizer.zero_grad()
+            loss.backward()
+        else:
+            micro = batch % k
+            if micro == 0:
+                optimizer.zero_grad()
+            if inv_k is None:
+                inv_k = torch.full_like(loss.detach(), 1.0 / k)
+            if micro != k - 1:
+                if callable(no_sync):
+                    with no_sync():
+                        loss.backward(inv_k)
+                else:
+                    loss.backward(inv_k)
+                continue
+            loss.backward(inv_k)
 
         if fused_opt:
             optimizer.step(max_norm=MAX_GRAD_NORM)
@@ -129,7 +159,7 @@ def train_step(model: torch.nn.Module,
             optimizer.step()
         lr_scheduler.step()
 
-    return metrics.means()
+    return metrics.means(model)
 
 
 def test_step(model: torch.nn.Module,
@@ -144,7 +174,7 @@ def test_step(model: torch.nn.Module,
             logits = model(X)
             loss = loss_fn(logits, y)
             metrics.add(loss, _batch_correct(loss_fn, logits, y) / len(logits))
-    return metrics.means()
+    return metrics.means(model)
 
 
 test_step.__test__ = False  # the name comes from the reference API; it is not a pytest test

@@ -27,9 +27,14 @@ def _ptr(t: Optional[torch.Tensor]):
 
 
 def stream_ptr(device=None):
-    """cudaStream_t of torch's current stream (0 / NULL for the CPU test double)."""
+    """cudaStream_t of torch's current stream on `device` (0 / NULL for the CPU test double). Also tells _C.call which
+    device the call belongs to, so that it can guard the launch when that is not the current device."""
     if torch.cuda.is_available():
-        return torch.cuda.current_stream(device).cuda_stream
+        idx = getattr(device, "index", None)
+        if idx is None:
+            idx = torch.cuda.current_device()
+        _C.want_device = idx
+        return torch.cuda.current_stream(idx).cuda_stream
     return None
 
 

@@ -178,15 +178,14 @@ class FusedAdam(torch.optim.Optimizer):
         K.adam_step(self._table_dev, self._num, self._max_size, [g["lr"] for g in self.param_groups],
                     [g["weight_decay"] for g in self.param_groups], g0["betas"][0], g0["betas"][1], g0["eps"], step,
                     g0["decoupled_weight_decay"], sumsq, max_norm if max_norm else 0.0, self.grad_scale)
-        shared = self._shared_step
-        shared_bumped = False
+        # Advance every DISTINCT step tensor once. Parameters created together share one tensor object, and
+        # state_dict() / load_state_dict() (deepcopy with a memo, also through torch.save / torch.load) preserve that
+        # aliasing without restoring `_shared_step` -- so identity, not `_shared_step`, decides what gets bumped.
+        seen = set()
         for _, p in items:
             st_step = self.state[p]["step"]
-            if st_step is shared:
-                if not shared_bumped:
-                    shared += 1
-                    shared_bumped = True
-            else:
+            if id(st_step) not in seen:
+                seen.add(id(st_step))
                 st_step += 1
         torch.autograd.graph.increment_version([p for _, p in items])   # the kernel wrote p behind autograd's back
         for _, p in items:

@@ -130,16 +130,19 @@ __global__ void softmax_ce_kernel(const float* __restrict__ logits, const long l
     se = s_val[0];
 
     const long long y = labels[b];
+    const bool y_ok = y >= 0 && y < C;
     const float invB = 1.0f / (float)B;
     if (dlogits) {
         for (int c = threadIdx.x; c < C; c += blockDim.x) {
             const float p = expf(z[c] - mx) / se;
-            dlogits[(long long)b * C + c] = (p - (c == y ? 1.f : 0.f)) * invB;
+            // a label outside [0, C) poisons its row (and the loss, below) with NaN: torch raises for it
+            // (device-side assert); a kernel cannot raise without a host sync, but it must not pass silently
+            dlogits[(long long)b * C + c] = y_ok ? (p - (c == y ? 1.f : 0.f)) * invB : __int_as_float(0x7fc00000);
         }
     }
     if (threadIdx.x == 0) {
-        if (y >= 0 && y < C) atomicAdd(loss, (logf(se) + mx - z[y]) * invB);
-        if (correct && arg == (int)y) atomicAdd(correct, 1);
+        atomicAdd(loss, y_ok ? (logf(se) + mx - z[y]) * invB : __int_as_float(0x7fc00000));
+        if (correct && y_ok && arg == (int)y) atomicAdd(correct, 1);
     }
 }
 

@@ -39,7 +39,11 @@ def main():
     loss = loss_fn(dp(X[rank * per:(rank + 1) * per].to(dev)), y[rank * per:(rank + 1) * per].to(dev))
     loss.backward()
     grads = {k: p.grad.detach().clone() * dp.grad_scale for k, p in model.named_parameters()}
-
+    # every gradient lives in its bucket; the encoder blocks' 12 x layers gradients were written there directly
+    for b in dp.buckets:
+        lo, hi = b.flat.data_ptr(), b.flat.data_ptr() + b.flat.numel() * 4
+        for p in b.params:
+            assert lo <= p.grad.data_ptr() < hi
     ref = ViT(**TINY).to(dev)
     ref.load_state_dict(model.state_dict())
     loss_fn(ref(X.to(dev)), y.to(dev)).backward()
@@ -58,6 +62,39 @@ def main():
     gathered = [torch.empty_like(flat) for _ in range(world)]
     dist.all_gather(gathered, flat)
     assert all(torch.equal(gathered[0], t) for t in gathered), "weights diverged across ranks after the step"
+    # ranks seeded alike still draw different dropout masks (the rank is folded into the mask key)
+    from b200vit.models import vit as vitmod
+    torch.manual_seed(42)
+    pe = vitmod.PatchEmbedding(image_size=64, patch_size=16, embedding_dropout=0.5, embedding_dim=128).to(dev).train()
+    img = torch.rand(2, 3, 64, 64, generator=torch.Generator().manual_seed(9)).to(dev)
+    torch.manual_seed(42)
+    keep = (pe(img) != 0).to(torch.uint8).flatten()
+    masks = [torch.empty_like(keep) for _ in range(world)]
+    dist.all_gather(masks, keep)
+    assert not torch.equal(masks[0], masks[1]), "ranks 0 and 1 drew the same dropout mask"
+    # epoch metrics are averaged over ranks
+    l, a = dp.reduce_metrics(float(rank), 1.0)
+    assert abs(l - (world - 1) / 2) < 1e-12 and a == 1.0
+    # gradient accumulation through the engine: 2 micro-batches of 2 == 1 batch of 4 per rank
+    from b200vit.going_modular import engine
+    xs, ys = X[rank * per:(rank + 1) * per].to(dev), y[rank * per:(rank + 1) * per].to(dev)
+    model.zero_grad()
+    sched = torch.optim.lr_scheduler.LambdaLR(opt, lambda s: 1.0)
+    engine.train_step(dp, [(xs[:2], ys[:2]), (xs[2:], ys[2:])], loss_fn, opt, sched, dev, accumulation_steps=2)
+    acc_w = torch.cat([p.detach().flatten() for p in model.parameters()])
+    gathered = [torch.empty_like(acc_w) for _ in range(world)]
+    dist.all_gather(gathered, acc_w)
+    assert all(torch.equal(gathered[0], t) for t in gathered), "weights diverged after the accumulated step"
+    # LAST (it leaves the gradients in an undefined state): a second synchronised backward without zero_grad() must
+    # be refused -- it would reduce the first sum again
+    model.zero_grad()
+    loss_fn(dp(xs), ys).backward()
+    try:
+        loss_fn(dp(xs), ys).backward()
+        raise AssertionError("double synchronised backward was not detected")
+    except RuntimeError as e:
+        assert "already all-reduced" in str(e), e
+    torch.cuda.synchronize()
     if rank == 0:
         print(f"dp_check ok: world={world} buckets={len(dp.buckets)} worst grad rel err {worst:.2e}", flush=True)
     dist.destroy_process_group()

@@ -99,6 +99,23 @@ def _dp_worker(rank, world, port, out):
         ref.zero_grad()
         nn.functional.cross_entropy(ref(X), y, reduction="sum").backward()
         err2 = max((a.grad - b.grad).abs().max().item() for a, b in zip(net.parameters(), ref.parameters()))
+        # a second synchronised backward on top of reduced gradients is refused
+        refused = False
+        try:
+            nn.functional.cross_entropy(dp(xs), ys).backward()
+        except RuntimeError as e:
+            refused = "already all-reduced" in str(e)
+        assert refused
+        for b in dp.buckets:
+            if b.work is not None:
+                b.work.wait()
+                b.work = None
+            b.pending = len(b.params)
+        dp._callback_queued = False
+        l, a = dp.reduce_metrics(float(rank + 1), 0.5)
+        assert abs(l - (world + 1) / 2) < 1e-12 and a == 0.5
+        from b200vit import functional as F_
+        assert F_._dropout_stream == rank
         out.put((rank, err, same, err2))
     finally:
         dist.destroy_process_group()
@@ -120,3 +137,94 @@ def test_data_parallel_gloo_world2():
         assert same, "parameters differ across ranks after broadcast"
         assert err < 1e-6, f"rank {rank}: averaged DP gradient differs from full-batch gradient by {err}"
         assert err2 < 1e-5, f"rank {rank}: accumulated (no_sync) DP gradient differs by {err2}"
+
+
+class _StubLib:
+    """Test double for libb200vit.so: every entry point succeeds without doing anything (host logic only)."""
+
+    def __getattr__(self, name):
+        if name == "b200vit_last_error":
+            return lambda: b""
+        return lambda *a: 0
+
+
+def test_fused_adam_step_counter_survives_state_dict_round_trip():
+    """All parameters of a FusedAdam share ONE step tensor; state_dict()/load_state_dict() keep that aliasing. The
+    step must advance by one per optimizer step before and after a resume (not once per parameter)."""
+    from b200vit import _C
+    from b200vit.optim import FusedAdam
+    _C.set_library(_StubLib())
+    try:
+        def make():
+            torch.manual_seed(0)
+            return [nn.Parameter(torch.randn(4, 3)) for _ in range(5)]
+
+        def step(ps, opt, n):
+            for _ in range(n):
+                for p in ps:
+                    p.grad = torch.ones_like(p)
+                opt.step(max_norm=1.0)
+
+        ps = make()
+        opt = FusedAdam(ps, lr=1e-3)
+        step(ps, opt, 3)
+        assert {int(opt.state[p]["step"]) for p in ps} == {3}
+        import io
+        buf = io.BytesIO()
+        torch.save(opt.state_dict(), buf)
+        buf.seek(0)
+        ps2 = make()
+        opt2 = FusedAdam(ps2, lr=1e-3)
+        opt2.load_state_dict(torch.load(buf))
+        assert {int(opt2.state[p]["step"]) for p in ps2} == {3}
+        step(ps2, opt2, 3)
+        assert {int(opt2.state[p]["step"]) for p in ps2} == {6}
+        # a parameter that joins after the first step counts from its own zero, as in torch.optim.Adam
+        late = nn.Parameter(torch.randn(2))
+        opt2.add_param_group({"params": [late]})
+        late.grad = torch.ones_like(late)
+        step(ps2, opt2, 1)
+        assert int(opt2.state[late]["step"]) == 1 and {int(opt2.state[p]["step"]) for p in ps2} == {7}
+    finally:
+        _C.set_library(None)
+
+
+def test_engine_gradient_accumulation_equals_one_large_batch():
+    """train_step(accumulation_steps=k): k micro-batches -> one optimizer step with the averaged gradient."""
+    from b200vit.going_modular import engine
+    g = torch.Generator().manual_seed(3)
+    X, y = torch.randn(16, 6, generator=g), torch.randint(0, 3, (16,), generator=g)
+
+    def make():
+        torch.manual_seed(2)
+        m = nn.Sequential(nn.Linear(6, 16), nn.Tanh(), nn.Linear(16, 3))
+        opt = torch.optim.SGD(m.parameters(), lr=0.1)
+        return m, opt, torch.optim.lr_scheduler.LinearLR(opt, start_factor=0.5, total_iters=4)
+
+    m1, o1, s1 = make()
+    engine.train_step(m1, [(X[:8], y[:8]), (X[8:], y[8:])], nn.CrossEntropyLoss(), o1, s1, torch.device("cpu"))
+    ma, oa, sa = make()
+    micro = [(X[i:i + 4], y[i:i + 4]) for i in range(0, 16, 4)]
+    la, _ = engine.train_step(ma, micro, nn.CrossEntropyLoss(), oa, sa, torch.device("cpu"), accumulation_steps=2)
+    for a, b in zip(m1.parameters(), ma.parameters()):
+        assert torch.allclose(a, b, atol=1e-6)
+    assert sa.last_epoch == s1.last_epoch == 2                  # the schedule advances per optimizer step
+    with pytest.raises(ValueError):
+        engine.train_step(ma, micro, nn.CrossEntropyLoss(), oa, sa, torch.device("cpu"), accumulation_steps=0)
+
+
+def test_dropout_keys_follow_seed_and_stream():
+    """Dropout keys: reproducible from torch.manual_seed, fresh per call, different per data-parallel rank."""
+    from b200vit import functional as F_
+    torch.manual_seed(7)
+    a = [F_.next_dropout_key() for _ in range(3)]
+    torch.manual_seed(7)
+    b = [F_.next_dropout_key() for _ in range(3)]
+    assert a == b and len(set(a)) == 3
+    prev = F_.set_dropout_stream(1)
+    try:
+        torch.manual_seed(7)
+        c = [F_.next_dropout_key() for _ in range(3)]
+    finally:
+        F_.set_dropout_stream(prev)
+    assert all(x[0] != y[0] and x[1] == y[1] for x, y in zip(a, c))

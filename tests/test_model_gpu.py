@@ -328,3 +328,46 @@ def test_backward_handover_falls_back_when_the_gradient_is_replaced(tiny):
         return g
     edited = grads(inplace)
     assert rel_err(edited[n0], 2.0 * base[n0]) < 1e-3
+
+
+def test_fused_adam_save_load_resume_matches_torch_adam():
+    """Optimizer state round trip: FusedAdam -> state_dict -> torch.save/load -> a NEW FusedAdam -> more
+    steps, against torch.optim.Adam doing the same: parameters and the step counter stay in lock-step."""
+    import io
+    from b200vit.optim import FusedAdam
+    g = torch.Generator().manual_seed(8)
+    shapes = [(300, 77), (1000,), (64, 64), (5,)]
+    mk = lambda ps: [{"params": ps[:2], "weight_decay": 0.03}, {"params": ps[2:], "weight_decay": 0.0}]
+    ps_a = [torch.nn.Parameter(torch.randn(s, generator=g).to(dev())) for s in shapes]
+    ps_b = [torch.nn.Parameter(p.detach().clone()) for p in ps_a]
+    oa, ob = FusedAdam(mk(ps_a), lr=1e-3), torch.optim.Adam(mk(ps_b), lr=1e-3)
+
+    def run(oa, ob, ps_a, ps_b, n):
+        for _ in range(n):
+            for pa, pb in zip(ps_a, ps_b):
+                gr = torch.randn(pa.shape, generator=g).to(dev()) * 0.01
+                pa.grad, pb.grad = gr.clone(), gr.clone()
+            oa.step()
+            ob.step()
+
+    run(oa, ob, ps_a, ps_b, 3)
+    buf = io.BytesIO()
+    torch.save(oa.state_dict(), buf)
+    buf.seek(0)
+    ps_a2 = [torch.nn.Parameter(p.detach().clone()) for p in ps_a]
+    oa2 = FusedAdam(mk(ps_a2), lr=1e-3)
+    oa2.load_state_dict(torch.load(buf))
+    run(oa2, ob, ps_a2, ps_b, 4)
+    for pa, pb in zip(ps_a2, ps_b):
+        assert rel_err(pa, pb) < 1e-5
+        assert int(oa2.state[pa]["step"]) == int(ob.state[pb]["step"]) == 7
+
+
+def test_cross_entropy_flags_out_of_range_labels():
+    """torch raises for a label outside [0, C); the fused kernel cannot raise without a sync, so it poisons the loss."""
+    from b200vit.nn import CrossEntropyLoss
+    logits = torch.randn(4, 5, device=dev(), requires_grad=True)
+    good = CrossEntropyLoss()(logits, torch.tensor([0, 4, 2, 1], device=dev()))
+    assert torch.isfinite(good)
+    bad = CrossEntropyLoss()(logits, torch.tensor([0, 5, 2, 1], device=dev()))
+    assert torch.isnan(bad)

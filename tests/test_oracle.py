@@ -152,7 +152,12 @@ def test_constructor_signatures_match_reference():
                 ("embedding_dropout", 0.1)]
     assert params(vit.ViT.__init__) == vit_args + [("num_classes", 1000)]
     assert params(vit_no_classifier.ViT.__init__) == vit_args
-    assert [n for n, _ in params(engine.train_step)] == ["model", "dataloader", "loss_fn", "optimizer", "lr_scheduler", "device"]
+    # the reference's positional parameters, in order; anything more must be keyword-only with a default (an extension
+    # that a reference caller never sees): accumulation_steps
+    sig = inspect.signature(engine.train_step).parameters.values()
+    assert [p.name for p in sig if p.kind != inspect.Parameter.KEYWORD_ONLY] == \
+        ["model", "dataloader", "loss_fn", "optimizer", "lr_scheduler", "device"]
+    assert all(p.default is not E for p in sig if p.kind == inspect.Parameter.KEYWORD_ONLY)
     assert [n for n, _ in params(engine.test_step)] == ["model", "dataloader", "loss_fn", "device"]
     assert [n for n, _ in params(engine.train)] == ["model", "train_dataloader", "test_dataloader", "optimizer",
                                                     "loss_fn", "lr_scheduler", "epochs", "device"]
