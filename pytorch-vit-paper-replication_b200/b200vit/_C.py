@@ -127,6 +127,49 @@ want_device = None      # CUDA device ordinal of the tensors of the call being p
 _current_device = None  # bound lazily to torch.cuda.current_device
 
 
+_timing = None          # list of (name, first five args, start event, end event) while a CallTimer is active
+
+
+class CallTimer:
+    """Measurement aid: CUDA events (on the launching stream) around every entry-point call made inside the `with`
+    block, so that the time each kernel family takes INSIDE a real step can be read back -- `by_name()` after the block
+    synchronises and returns {entry point: [milliseconds per call, ...]} and `gemms()` the (op, epilogue, M, N, K, ms)
+    list. The events sit between consecutive launches, which switches off the programmatic-dependent-launch overlap of
+    a kernel's prologue with its predecessor's tail: the figures are a few microseconds per launch pessimistic."""
+
+    def __enter__(self):
+        global _timing
+        self.records = _timing = []
+        return self
+
+    def __exit__(self, *a):
+        global _timing
+        _timing = None
+
+    def by_name(self):
+        import torch
+        torch.cuda.synchronize()
+        out = {}
+        for name, _head, e0, e1 in self.records:
+            out.setdefault(name, []).append(e0.elapsed_time(e1))
+        return out
+
+    def gemms(self):
+        import torch
+        torch.cuda.synchronize()
+        return [(*head, e0.elapsed_time(e1)) for name, head, e0, e1 in self.records if name == "b200vit_gemm"]
+
+
+def _timed_call(fn, name, args):
+    import torch
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    rc = fn(*args)
+    e1.record()
+    _timing.append((name, tuple(args[:5]), e0, e1))
+    return rc
+
+
 def call(name: str, *args) -> None:
     """Invoke one entry point and raise on a non-zero return. Kernels launch on the stream that kernels.stream_ptr()
     looked up for the tensors' device; if that is not the CUDA current device (a model on cuda:1 without a prior
@@ -145,6 +188,6 @@ def call(name: str, *args) -> None:
             launch_count += KERNELS_PER_CALL.get(name, 1)
             call_count += 1
             return
-    check(fn(*args), name)
+    check(fn(*args) if _timing is None else _timed_call(fn, name, args), name)
     launch_count += KERNELS_PER_CALL.get(name, 1)
     call_count += 1
