@@ -107,6 +107,80 @@ __device__ __forceinline__ float gelu_exact_grad(float x) {
     return fmaf(x * 0.3989422804014327f, e, cdf);  // cdf + x pdf
 }
 
+// ---------------------------------------------------------------------------------------------
+// Packed fp32 arithmetic (sm_100: FFMA2 / FMUL2 / FADD2 operate on an aligned register pair per issue slot). The GELU
+// epilogue of the fc1 GEMM is bound by instruction issue, not by the tensor pipe: evaluating the erf polynomial,
+// the value and the derivative for TWO adjacent columns per instruction halves its floating-point issue count.
+// ---------------------------------------------------------------------------------------------
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+// Constants of gelu_value_and_grad2, pre-multiplied by the dropout scale s and broadcast to both halves.
+struct GeluConst2 {
+    f32x2 c_p, one, na, nb, nc, k_exp, hs, c2s;
+    uint32_t hs_bits;
+};
+__device__ __forceinline__ GeluConst2 make_gelu_const2(float s) {
+    GeluConst2 g;
+    const float hs = 0.5f * s;
+    g.c_p = pack2(0.47047f * 0.70710678118654752f, 0.47047f * 0.70710678118654752f);
+    g.one = pack2(1.0f, 1.0f);
+    g.na = pack2(-0.7478556f, -0.7478556f);       // the polynomial is built NEGATED: erf = 1 + (-poly) e
+    g.nb = pack2(0.0958798f, 0.0958798f);
+    g.nc = pack2(-0.3480242f, -0.3480242f);
+    g.k_exp = pack2(-0.5f * 1.4426950408889634f, -0.5f * 1.4426950408889634f);
+    g.hs = pack2(hs, hs);
+    g.c2s = pack2(0.3989422804014327f * s, 0.3989422804014327f * s);
+    g.hs_bits = __float_as_uint(hs);
+    return g;
+}
+// (h, g) = s * (gelu(x), gelu'(x)) for two values at once; same formulas as gelu_value_and_grad.
+__device__ __forceinline__ void gelu_value_and_grad2(float x0, float x1, const GeluConst2& k, f32x2& h, f32x2& g) {
+    const f32x2 x = pack2(x0, x1);
+    const f32x2 ax = pack2(fabsf(x0), fabsf(x1));
+    const f32x2 d = fma2(k.c_p, ax, k.one);
+    float d0, d1;
+    unpack2(d, d0, d1);
+    const f32x2 t = pack2(fast_rcp(d0), fast_rcp(d1));
+    f32x2 np = fma2(t, k.na, k.nb);
+    np = fma2(np, t, k.nc);
+    np = mul2(np, t);                                   // -poly(t)
+    float q0, q1;
+    unpack2(mul2(mul2(x, x), k.k_exp), q0, q1);
+    const f32x2 e = pack2(fast_ex2(q0), fast_ex2(q1));  // exp(-x^2 / 2)
+    const f32x2 erf_abs = fma2(np, e, k.one);           // erf(|x| / sqrt2)
+    h = mul2(fma2(ax, erf_abs, x), k.hs);
+    const f32x2 shs = pack2(__uint_as_float((__float_as_uint(x0) & 0x80000000u) | k.hs_bits),
+                            __uint_as_float((__float_as_uint(x1) & 0x80000000u) | k.hs_bits));   // copysign(hs, x)
+    g = fma2(mul2(x, k.c2s), e, fma2(shs, erf_abs, k.hs));
+}
+__device__ __forceinline__ uint32_t pack_bf16_2(f32x2 v) {
+    float lo, hi;
+    unpack2(v, lo, hi);
+    return pack_bf16(lo, hi);
+}
+
 // Column sums of a 32 x 32 block held one ROW per lane (v[j] = element (row = lane, column = j)): returns, in lane
 // j, the sum over the 32 rows of column j. Butterfly transpose-reduce: at every stage a lane keeps one half of its
 // columns and sends the other half to its partner (31 shuffles in total); v is destroyed.
@@ -183,17 +257,41 @@ __device__ __forceinline__ uint32_t mix32(uint32_t x) {     // "lowbias32" integ
     x ^= x >> 16;
     return x;
 }
+// Random words of a block of 8 elements. One multiply-xorshift hash of (block counter, key) gives the block's base
+// word (word 0); words 1-3 are cheap bijections of it (xor a constant, multiply, fold the high half down). A kernel
+// that needs all four pays 6 + 3 x 4 integer instructions per 8 elements instead of 4 full hashes (the fc1 epilogue is
+// bound by instruction issue); one that needs a single word pays 6 + 4.
+__device__ __forceinline__ uint32_t dropout_base(const DropoutParams& d, uint64_t blk) {
+    const uint32_t hi = (uint32_t)(blk >> 32);              // zero for tensors below 2^35 elements
+    uint32_t x = (uint32_t)blk * 0x9E3779B1u + (d.key_lo ^ (hi * 0x85EBCA6Bu + (hi ? d.key_hi : 0u)));
+    x ^= x >> 15; x *= 0x846ca68bu;
+    x ^= x >> 16;
+    return x;
+}
+__device__ __forceinline__ uint32_t dropout_derive(uint32_t base, uint32_t j) {
+    if (j == 0) return base;
+    const uint32_t c = j == 1 ? 0x7feb352du : (j == 2 ? 0xC2B2AE35u : 0x27D4EB2Fu);
+    uint32_t x = (base ^ c) * 0x9E3779B1u;
+    return x ^ (x >> 15);
+}
 __device__ __forceinline__ uint32_t dropout_word(const DropoutParams& d, uint64_t blk, uint32_t j) {
-    const uint32_t ctr = ((uint32_t)blk << 2) | j;
-    const uint32_t hi = (uint32_t)(blk >> 30);              // zero for tensors below 2^33 elements
-    return mix32(ctr ^ d.key_lo ^ (hi * 0x9E3779B9u + (hi ? d.key_hi : 0u)));
+    return dropout_derive(dropout_base(d, blk), j);
+}
+__device__ __forceinline__ void dropout_words4(const DropoutParams& d, uint64_t blk, uint32_t (&w)[4]) {
+    const uint32_t b = dropout_base(d, blk);
+    w[0] = b;
+    w[1] = dropout_derive(b, 1);
+    w[2] = dropout_derive(b, 2);
+    w[3] = dropout_derive(b, 3);
 }
 
 // Multipliers (0 or scale) for the 8 consecutive elements [8*blk, 8*blk+8).
 __device__ __forceinline__ void dropout_mult8(const DropoutParams& d, uint64_t blk, float (&m)[8]) {
+    uint32_t ws[4];
+    dropout_words4(d, blk, ws);
 #pragma unroll
     for (uint32_t i = 0; i < 4; ++i) {
-        const uint32_t w = dropout_word(d, blk, i);
+        const uint32_t w = ws[i];
         m[2 * i]     = ((w & 0x7FFFu) >= d.thr15) ? d.scale : 0.0f;
         m[2 * i + 1] = (((w >> 16) & 0x7FFFu) >= d.thr15) ? d.scale : 0.0f;
     }
@@ -209,7 +307,9 @@ __device__ __forceinline__ float dropout_mult1(const DropoutParams& d, uint64_t 
 // bf16 pair. Same keep decision as dropout_mult8 / dropout_mult1 (the scale must be applied separately).
 __device__ __forceinline__ uint32_t dropout_mask2(const DropoutParams& d, uint32_t w) {
     const uint32_t t = ((w & 0x7FFF7FFFu) | 0x80008000u) - (d.thr15 * 0x00010001u);
-    return ((t >> 15) & 0x00010001u) * 0xFFFFu;
+    uint32_t m;     // bits 15 / 31 (no borrow = keep) replicated over their half-words: PRMT with sign-replicating selectors
+    asm("prmt.b32 %0, %1, %1, 0xBB99;" : "=r"(m) : "r"(t));
+    return m;
 }
 
 inline DropoutParams make_dropout(float p, uint64_t seed, uint64_t offset) {

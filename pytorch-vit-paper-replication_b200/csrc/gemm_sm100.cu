@@ -356,16 +356,25 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
         const bool want_gd = p.C != nullptr;
         const unsigned long long e0 = (unsigned long long)epi_out_row<EPI>(p, row) * (unsigned long long)p.N + (unsigned long long)col0;
         const bool blk8 = (p.N & 7) == 0;
+        const GeluConst2 gk = make_gelu_const2(p.drop.scale);
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-            float hv[8], gv[8];
+            // two columns per instruction (FFMA2): value and derivative of four column pairs
+            uint32_t hp[4], gp[4];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) gelu_value_and_grad(v[8 * c + i], p.drop.scale, hv[i], gv[i]);
+            for (int j = 0; j < 4; ++j) {
+                f32x2 h2, g2;
+                gelu_value_and_grad2(v[8 * c + 2 * j], v[8 * c + 2 * j + 1], gk, h2, g2);
+                hp[j] = pack_bf16_2(h2);
+                gp[j] = pack_bf16_2(g2);
+            }
             uint32_t mk[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};
             if (p.drop.p > 0.f) {
                 if (blk8) {
+                    uint32_t ws[4];
+                    dropout_words4(p.drop, (e0 >> 3) + c, ws);
 #pragma unroll
-                    for (uint32_t j = 0; j < 4; ++j) mk[j] = dropout_mask2(p.drop, dropout_word(p.drop, (e0 >> 3) + c, j));
+                    for (uint32_t j = 0; j < 4; ++j) mk[j] = dropout_mask2(p.drop, ws[j]);
                 } else {
 #pragma unroll
                     for (int j = 0; j < 4; ++j)
@@ -374,10 +383,8 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
                 }
             }
             if (want_gd)
-                sts128(stg + stg_off_b16(lane, c), pack_bf16(gv[0], gv[1]) & mk[0], pack_bf16(gv[2], gv[3]) & mk[1],
-                       pack_bf16(gv[4], gv[5]) & mk[2], pack_bf16(gv[6], gv[7]) & mk[3]);
-            sts128(stg + 2048 + stg_off_b16(lane, c), pack_bf16(hv[0], hv[1]) & mk[0], pack_bf16(hv[2], hv[3]) & mk[1],
-                   pack_bf16(hv[4], hv[5]) & mk[2], pack_bf16(hv[6], hv[7]) & mk[3]);
+                sts128(stg + stg_off_b16(lane, c), gp[0] & mk[0], gp[1] & mk[1], gp[2] & mk[2], gp[3] & mk[3]);
+            sts128(stg + 2048 + stg_off_b16(lane, c), hp[0] & mk[0], hp[1] & mk[1], hp[2] & mk[2], hp[3] & mk[3]);
         }
         __syncwarp();
         if (want_gd) store_b16_tile(reinterpret_cast<bf16*>(p.C), p.ldc);
