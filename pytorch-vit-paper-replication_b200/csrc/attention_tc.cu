@@ -965,8 +965,9 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
             mbar_wait(full_bar, it & 1);
             tc_fence_after();
             auto width = [&](int c) { return min(AT3_W, Nk - c * AT3_W); };
-            auto issue_1 = [&](int s) {        // S^T and dP^T of (my) step s into my group's chunk accumulators
-                const int t = s / nc, c = s % nc;
+            // (t, c) of step s is carried along instead of divided out: a runtime integer division is ~25 instructions with
+            // two dependent MUFU/I2F round trips, on the critical issue path of every step
+            auto issue_1 = [&](int t, int c) {  // S^T and dP^T of (my) step (t, c) into my group's chunk accumulators
                 const uint32_t xo = (uint32_t)t * (ATC_BM * 128), yo = (uint32_t)c * (AT3_W * 128);
                 const uint32_t idesc1 = make_idesc_bf16(ATC_BM, width(c), 0, 0);
 #pragma unroll
@@ -979,7 +980,7 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
                 umma_commit_elect(s_ready(my_g));
             };
             const int s_first = ((S0 & 1u) == (uint32_t)my_g) ? 0 : 1;
-            if (s_first < nsteps) issue_1(s_first);
+            if (s_first < nsteps) issue_1(nc == 1 ? s_first : 0, nc == 1 ? 0 : s_first);
             bool dq_waited = false;
             for (int t = 0; t < nt; ++t) {
                 const uint32_t tile_idx = (uint32_t)it * nt + t;        // key tiles so far, all heads
@@ -1019,7 +1020,14 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
                                                make_smem_desc_sw128(sB + k * 2048, 1024, 0), idesc3, (t > 0 || k > 0) ? 1u : 0u);
                         umma_commit_elect(ds_free(m));
                     }
-                    if (s + 2 < nsteps) issue_1(s + 2);
+                    // (Queueing the next S^T / dP^T BEFORE the dQ MMAs shortens the chain the math group waits on by 4 %,
+                    // but it lets the two issuers' dV / dK MMAs of neighbouring chunks reach the tensor core in a
+                    // timing-dependent order: the fp32 sums then differ in the last bit from run to run. Not taken.)
+                    if (s + 2 < nsteps) {
+                        int t2 = t, c2 = c + 2;
+                        while (c2 >= nc) { c2 -= nc; ++t2; }
+                        issue_1(t2, c2);
+                    }
                 }
                 if (first_mine) umma_commit_elect(kv_ready);    // no chunk of this tile was mine (single-chunk tiles)
             }
@@ -1120,8 +1128,7 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
                 }
             };
             int pending_tile = -1;          // tile whose dV/dK this group still has to read out
-            for (int s = 0; s < nsteps; ++s) {
-                const int t = s / nc, c = s % nc;
+            for (int s = 0, t = 0, c = 0; s < nsteps; ++s, c = (c + 1 == nc ? 0 : c + 1), t += (c == 0)) {
                 if (((S0 + s) & 1) != (uint32_t)g) {
                     // the other group's step; if it is the last chunk of a tile, this group reads its half of the tile's
                     // gradients after its own NEXT step (or at the end of the head)

@@ -1,17 +1,26 @@
-"""Launch the two representative GEMMs of the step a few times (for ncu captures; not a pytest file)."""
+"""Launch named GEMMs of the training step a few times, with their real epilogues (for ncu captures and quick timing;
+not a pytest file):   python tests/perf_one_gemm.py fc1_fwd fc2_dgrad ...   (names: bench.gemm_shapes_per_step)"""
 import sys
 from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT / "pytorch-vit-paper-replication_b200"))
+sys.path.insert(0, str(ROOT))
 import torch
-from b200vit import kernels as K
+import bench
 dev = torch.device("cuda:0")
-R, D, M = 50432, 768, 3072
-ln = torch.randn(R, D, device=dev).bfloat16(); w1 = torch.randn(M, D, device=dev).bfloat16(); b1 = torch.randn(M, device=dev)
-a = torch.empty(R, M, device=dev, dtype=torch.bfloat16); h = torch.empty_like(a)
-da = torch.randn(R, M, device=dev).bfloat16(); dln = torch.empty(R, D, device=dev, dtype=torch.bfloat16)
-for _ in range(3):
-    K.gemm(K.OP_NT, K.EPI_BIAS_GELU, R, M, D, ln, D, w1, D, a, M, C2=h, ldc2=M, bias=b1, dropout_p=0.1, seed=1, offset=2)   # fc1 forward
-    K.gemm(K.OP_NN, K.EPI_BF16, R, D, M, da, M, w1, D, dln, D)                                                            # fc1 dgrad
-torch.cuda.synchronize()
-print("ok")
+names = sys.argv[1:] or ["fc1_fwd", "fc1_dgrad"]
+shapes = {s[0]: s for s in bench.gemm_shapes_per_step(256)}
+for n in names:
+    name, op, epi, M, N, Kd, _ = shapes[n]
+    run = bench.make_gemm_runner(name, op, epi, M, N, Kd, dev)
+    for _ in range(3):
+        run()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        run()
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 100
+    print(f"{n:12s} {us:7.1f} us  {2.0 * M * N * Kd / us / 1e6:7.1f} TFLOP/s")
