@@ -109,7 +109,7 @@ def make_gemm_runner(name, op, epi, M, N, Kd, dev):
         aux, ldaux, period = torch.randn(197, N, device=dev), N, 196
     if name in ("fc1_fwd", "fc2_fwd", "fc2_dgrad", "patch_fwd"):
         p = 0.1
-    split = K.split_k_for(M, N, Kd, dev) if epi == K.EPI_ACCUM else 1
+    split = 0 if epi == K.EPI_ACCUM else 1
 
     def run():
         K.gemm(op, epi, M, N, Kd, A, lda, B, ldb, C, N, C2=C2, ldc2=N, bias=bias, aux=aux, ldaux=ldaux,

@@ -168,6 +168,10 @@ int b200vit_head_bwd(const float* xn, const float* w, const float* dlogits, floa
 int b200vit_softmax_ce(const float* logits, const long long* labels, float* loss, float* dlogits, int* correct,
                        int batch, int classes, void* stream);
 
+/* Prediction post-processing: probs f32 [B, C] = softmax(logits) per row, labels int64 [B] = argmax (first maximal index);
+ * either output may be NULL. Replaces torch.softmax(dim=1) + torch.argmax(dim=1) of going_modular/predictions.py:62-66. */
+int b200vit_softmax_top1(const float* logits, float* probs, long long* labels, int batch, int classes, void* stream);
+
 /* dst = src * (*scalar_dev): chain rule with the upstream scalar gradient of the loss. */
 int b200vit_scale_by_scalar(const float* src, const float* scalar_dev, float* dst, long long n, void* stream);
 

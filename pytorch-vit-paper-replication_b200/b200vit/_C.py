@@ -40,6 +40,7 @@ _SIGNATURES = {
     "b200vit_head_bwd": [_p, _p, _p, _p, _p, _p, _i, _i, _i, _p],
     "b200vit_softmax_ce": [_p, _p, _p, _p, _p, _i, _i, _p],
     "b200vit_scale_by_scalar": [_p, _p, _p, _ll, _p],
+    "b200vit_softmax_top1": [_p, _p, _p, _i, _i, _p],
     "b200vit_l2norm_sq": [_p, _p, _i, _ll, _p, _i, _p, _p],
     "b200vit_l2norm_sq_noalloc": [_p, _p, _i, _ll, _p, _p],
     "b200vit_adam_step": [_p, _i, _ll, _p, _p, _i, _f, _f, _f, _i, _i, _p, _f, _f, _p],

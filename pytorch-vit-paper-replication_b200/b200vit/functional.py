@@ -275,7 +275,7 @@ class PatchEmbedFn(torch.autograd.Function):
         K.patch_grad_rows(gx, gy, bn, t, d, p, seed, off)
         gw = _zeros((d, kdim), gx)
         K.gemm(K.OP_TN, K.EPI_ACCUM, d, kdim, rows, gy, d, patches, kdim, gw, kdim,
-               split_k=K.split_k_for(d, kdim, rows, gx.device))
+               split_k=0)
         return None, gw.view(wshape), g_b, g_cls, g_pos, None, None, None, None
 
 
@@ -346,7 +346,7 @@ def _msa_backward(g, saved, bn, t, heads, ln_w, w_in16, w_out16, has_residual, g
     if arena is None:
         arena = _ZeroArena(x2d, [(d, d), (3 * d, d)])
     dw_out = grad_out(P[4], (d, d), x2d, zero=True, arena=arena)
-    K.gemm(K.OP_TN, K.EPI_ACCUM, d, d, r, g16, d, o, d, dw_out, d, split_k=K.split_k_for(d, d, r, dev))
+    K.gemm(K.OP_TN, K.EPI_ACCUM, d, d, r, g16, d, o, d, dw_out, d, split_k=0)
     do = _empty((r, d), torch.bfloat16, x2d)
     K.gemm(K.OP_NN, K.EPI_BF16, r, d, d, g16, d, w_out16, d, do, d)
     delta = _empty((bn, heads, t), torch.float32, x2d)
@@ -355,7 +355,7 @@ def _msa_backward(g, saved, bn, t, heads, ln_w, w_in16, w_out16, has_residual, g
     K.attention_bwd(qkv, o, do, lse, delta, dqkv, bn, t, heads, HEAD_DIM, 1.0 / math.sqrt(HEAD_DIM), dbias=db_in,
                     dropout_p=adrop[0], seed=adrop[1][0], offset=adrop[1][1])
     dw_in = grad_out(P[2], (3 * d, d), x2d, zero=True, arena=arena)
-    K.gemm(K.OP_TN, K.EPI_ACCUM, 3 * d, d, r, dqkv, 3 * d, ln, d, dw_in, d, split_k=K.split_k_for(3 * d, d, r, dev))
+    K.gemm(K.OP_TN, K.EPI_ACCUM, 3 * d, d, r, dqkv, 3 * d, ln, d, dw_in, d, split_k=0)
     dln = _empty((r, d), torch.bfloat16, x2d)
     K.gemm(K.OP_NN, K.EPI_BF16, r, d, 3 * d, dqkv, 3 * d, w_in16, d, dln, d)
     gx = _empty((r, d), torch.float32, x2d)
@@ -417,13 +417,13 @@ def _mlp_backward(g, saved, drop, ln_w, w1_16, w2_16, has_residual, want_bf16_ou
     if arena is None:
         arena = _ZeroArena(x2d, [(d, m), (m,), (m, d)])
     dw2 = grad_out(P[4], (d, m), x2d, zero=True, arena=arena)
-    K.gemm(K.OP_TN, K.EPI_ACCUM, d, m, r, g16, d, h, m, dw2, m, split_k=K.split_k_for(d, m, r, dev))
+    K.gemm(K.OP_TN, K.EPI_ACCUM, d, m, r, g16, d, h, m, dw2, m, split_k=0)
     da = _empty((r, m), torch.bfloat16, x2d)
     db1 = grad_out(P[3], (m,), x2d, zero=True, arena=arena)
     # a = mask * gelu'(pre-activation); the epilogue also accumulates the fc1 bias gradient (column sums of da) into db1
     K.gemm(K.OP_NN, K.EPI_DGELU, r, m, d, g16, d, w2_16, m, da, m, bias=db1, aux=a, ldaux=m)
     dw1 = grad_out(P[2], (m, d), x2d, zero=True, arena=arena)
-    K.gemm(K.OP_TN, K.EPI_ACCUM, m, d, r, da, m, ln, d, dw1, d, split_k=K.split_k_for(m, d, r, dev))
+    K.gemm(K.OP_TN, K.EPI_ACCUM, m, d, r, da, m, ln, d, dw1, d, split_k=0)
     dln = g16  # reuse: g16 is dead after the two GEMMs above (same shape / dtype)
     K.gemm(K.OP_NN, K.EPI_BF16, r, d, m, da, m, w1_16, d, dln, d)
     gx = _empty((r, d), torch.float32, x2d)

@@ -22,6 +22,7 @@ from typing import Dict, Tuple
 import torch
 
 from . import functional as F_
+from . import kernels as K
 
 
 class _Entry:
@@ -89,3 +90,29 @@ class GraphedForward:
         entry.static_in.copy_(x, non_blocking=True)
         entry.graph.replay()
         return entry.static_out
+
+
+def predict(model: torch.nn.Module, images: torch.Tensor, device=None, graphed: "GraphedForward | None" = None):
+    """Class probabilities and top-1 labels for a batch of images: the numerical part of the reference's
+    `pred_and_plot_image` (going_modular/predictions.py:56-66 -- `model.to(device)`, `model.eval()`,
+    `torch.inference_mode()`, forward, `torch.softmax(dim=1)`, `torch.argmax(dim=1)`; loading / resizing the picture and
+    plotting stay with the caller).
+
+    images: float [B, 3, H, W] (already transformed) or uint8 [B, 3, H, W] (scaled by 1/255 on the device); host or
+    device tensors. Returns (probs float32 [B, C], labels int64 [B]) on the device. Pass a `GraphedForward` of the same
+    model as `graphed` to replay a recorded CUDA graph (small-batch latency)."""
+    if device is not None:
+        model.to(device)
+    model.eval()
+    dev = next(model.parameters()).device
+    x = images.to(dev, non_blocking=True)
+    with torch.inference_mode():
+        logits = graphed(x) if graphed is not None else model(x)
+        if logits.dim() != 2:
+            raise ValueError("predict() needs a classifier model (logits [batch, classes])")
+        logits = logits.float().contiguous()
+        bn, c = logits.shape
+        probs = torch.empty_like(logits)
+        labels = torch.empty(bn, dtype=torch.int64, device=dev)
+        K.softmax_top1(logits, probs, labels, bn, c)
+    return probs, labels

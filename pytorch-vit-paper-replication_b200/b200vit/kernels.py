@@ -18,7 +18,7 @@ __all__ = [
     "OP_NT", "OP_NN", "OP_TN", "EPI_BF16", "EPI_BIAS_GELU", "EPI_BIAS_RES", "EPI_DGELU", "EPI_ACCUM", "EPI_F32",
     "EPI_PATCH", "gemm", "cast_bf16", "im2col_patches", "class_token_rows", "embed_param_grads", "patch_grad_rows",
     "layernorm_fwd", "layernorm_bwd", "colsum_bf16", "dropout_cast", "attention_fwd", "attention_bwd", "head_fwd",
-    "head_bwd", "softmax_ce", "scale_by_scalar", "l2norm_sq", "l2norm_sq_noalloc", "adam_step", "stream_ptr", "split_k_for",
+    "head_bwd", "softmax_ce", "scale_by_scalar", "l2norm_sq", "l2norm_sq_noalloc", "adam_step", "stream_ptr",
 ]
 
 
@@ -57,15 +57,11 @@ def sm_count(device) -> int:
     return _SM_COUNT[idx]
 
 
-def split_k_for(m: int, n: int, k: int, device=None) -> int:
-    """Split-K factor for weight-gradient GEMMs: 0 = let the library pick (enough work items for ~2 waves)."""
-    return 0
-
-
 def gemm(op: int, epi: int, M: int, N: int, K: int, A: torch.Tensor, lda: int, B: torch.Tensor, ldb: int,
          C: Optional[torch.Tensor], ldc: int, *, C2: Optional[torch.Tensor] = None, ldc2: int = 0,
          bias: Optional[torch.Tensor] = None, aux: Optional[torch.Tensor] = None, ldaux: int = 0,
          dropout_p: float = 0.0, seed: int = 0, offset: int = 0, row_period: int = 0, split_k: int = 1) -> None:
+    """split_k: 1 = none; 0 = let the library pick (weight gradients: enough work items for about two waves)."""
     _C.call("b200vit_gemm", op, epi, M, N, K, _ptr(A), lda, _ptr(B), ldb, _ptr(C), ldc, _ptr(C2), ldc2, _ptr(bias),
             _ptr(aux), ldaux, float(dropout_p), int(seed), int(offset), row_period, split_k, stream_ptr(A.device))
 
@@ -164,6 +160,10 @@ def head_bwd(xn, w, dlogits, dxn, dw, db, batch, dim, classes) -> None:
 def softmax_ce(logits, labels, loss, dlogits, correct, batch, classes) -> None:
     _C.call("b200vit_softmax_ce", _ptr(logits), _ptr(labels), _ptr(loss), _ptr(dlogits), _ptr(correct), batch, classes,
             stream_ptr(logits.device))
+
+
+def softmax_top1(logits, probs, labels, batch, classes) -> None:
+    _C.call("b200vit_softmax_top1", _ptr(logits), _ptr(probs), _ptr(labels), batch, classes, stream_ptr(logits.device))
 
 
 def scale_by_scalar(src, scalar_dev, dst) -> None:

@@ -118,6 +118,10 @@ int b200vit_softmax_ce(const float* logits, const long long* labels, float* loss
     return softmax_ce_launch(logits, labels, loss, dlogits, correct, batch, classes, (cudaStream_t)stream);
 }
 
+int b200vit_softmax_top1(const float* logits, float* probs, long long* labels, int batch, int classes, void* stream) {
+    return softmax_top1_launch(logits, probs, labels, batch, classes, (cudaStream_t)stream);
+}
+
 int b200vit_scale_by_scalar(const float* src, const float* scalar_dev, float* dst, long long n, void* stream) {
     return scale_by_scalar_launch(src, scalar_dev, dst, n, (cudaStream_t)stream);
 }

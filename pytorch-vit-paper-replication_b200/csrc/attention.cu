@@ -1,5 +1,6 @@
-// Fused multi-head self-attention, forward and backward, for head_dim 64 and short sequences
-// (197 / 577 tokens). Replaces the scaled_dot_product_attention call inside nn.MultiheadAttention
+// Fused multi-head self-attention, forward and backward, for head_dim 64: the dispatch between the kernel families
+// and the mma.sync family itself (FA2-style; used for attn_dropout > 0 and for sequences beyond 2048 tokens -- the
+// 197- and 577-token cases of the benchmark configs run the tcgen05 kernels of attention_tc.cu). Replaces the scaled_dot_product_attention call inside nn.MultiheadAttention
 // (reference models/vit.py:86-97, need_weights=False, no mask, softmax scale 1/sqrt(head_dim)) and the
 // q/k/v head split / merge copies around it: the kernels read Q, K, V straight out of the packed
 // in-projection output [B, T, 3, H, 64] and write the merged-head output [B, T, H*64].
@@ -7,7 +8,6 @@
 // Flash-style: scores never reach HBM; the forward keeps only the per-row log-sum-exp, the backward
 // recomputes P. Two backward passes without atomics: (dK, dV) per key block and dQ per query block.
 // Tensor-core path: mma.sync m16n8k16 bf16 with fp32 accumulation, ldmatrix from XOR-swizzled smem.
-// (4 % of the step's FLOPs; the tcgen05 port of this kernel is the next optimisation step.)
 #include "common.cuh"
 #include "launchers.h"
 
@@ -438,230 +438,9 @@ attention_bwd_dq_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ d
 }
 
 
-// =============================================================================================
-// Resident variants for short sequences (T <= 256, i.e. the 197-token ViT-B/16 case): one CTA per (batch, head)
-// keeps the WHOLE Q / K / V (/ dO) of that head in shared memory (row count padded to 16), so global memory is
-// touched once, there is a single load phase and no block-wide synchronisation inside the compute loops.
-// Work items are 16-row tiles handed to warps round-robin.
-// =============================================================================================
-__device__ __forceinline__ void load_rows(uint8_t* s, const bf16* g, long long row_stride, int T, int Tp,
-                                          int nthreads) {
-    const uint32_t sbase = smem_addr(s);
-    for (int c = threadIdx.x; c < Tp * 8; c += nthreads) {
-        const int r = c >> 3, ch = c & 7;
-        const uint32_t dst = sbase + tile_off(r, ch);
-        if (r < T) {
-            const bf16* src = g + (long long)r * row_stride + ch * 8;
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
-        } else {
-            asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(dst), "r"(0u) : "memory");
-        }
-    }
-}
+constexpr int AT_TC_MAX_T = 256;      // the single-head-resident tcgen05 kernels (attention_tc.cu)
 
-__global__ void __launch_bounds__(256)
-attention_fwd_resident_kernel(const bf16* __restrict__ qkv, bf16* __restrict__ out, float* __restrict__ lse, int T,
-                              int Tp, int H, float scale_log2, float scale) {
-    extern __shared__ __align__(128) uint8_t smem_dyn[];
-    uint8_t* sQ = smem_dyn;
-    uint8_t* sK = sQ + Tp * 128;
-    uint8_t* sV = sK + Tp * 128;
-    const int bh = blockIdx.x, b = bh / H, h = bh % H;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-    const int tq = lane & 3, gq = lane >> 2;
-    const long long rs = 3LL * H * AT_HD;
-    const bf16* gQ = qkv + (long long)b * T * rs + (long long)h * AT_HD;
-    load_rows(sQ, gQ, rs, T, Tp, blockDim.x);
-    load_rows(sK, gQ + (long long)H * AT_HD, rs, T, Tp, blockDim.x);
-    load_rows(sV, gQ + 2LL * H * AT_HD, rs, T, Tp, blockDim.x);
-    cp_async_wait_all();
-    __syncthreads();
-
-    bf16* gO = out + (long long)b * T * H * AT_HD + (long long)h * AT_HD;
-    float* L = lse + (long long)bh * T;
-    for (int qt = warp; qt * 16 < T; qt += nwarps) {
-        uint32_t qf[4][4];
-        load_a_frags(sQ, qt * 16, lane, qf);
-        float o[8][4];
-        zero_acc(o);
-        float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-        for (int k0 = 0; k0 < Tp; k0 += AT_BLOCK) {
-            const int npairs = min(4, (Tp - k0) >> 4);
-            float s[8][4];
-            zero_acc(s);
-            mma_a_bT(s, qf, sK + k0 * 128, lane, npairs);
-            float mx0 = -INFINITY, mx1 = -INFINITY;
-#pragma unroll
-            for (int nt = 0; nt < 8; ++nt) {
-                const int key = k0 + nt * 8 + 2 * tq;
-                if (key >= T) { s[nt][0] = -INFINITY; s[nt][2] = -INFINITY; }
-                if (key + 1 >= T) { s[nt][1] = -INFINITY; s[nt][3] = -INFINITY; }
-                mx0 = fmaxf(mx0, fmaxf(s[nt][0], s[nt][1]));
-                mx1 = fmaxf(mx1, fmaxf(s[nt][2], s[nt][3]));
-            }
-            mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
-            mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-            mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
-            mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-            const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
-            const float c0 = exp2f((m0 - mn0) * scale_log2), c1 = exp2f((m1 - mn1) * scale_log2);
-            m0 = mn0; m1 = mn1;
-            float rs0 = 0.f, rs1 = 0.f;
-#pragma unroll
-            for (int nt = 0; nt < 8; ++nt) {
-                s[nt][0] = exp2f((s[nt][0] - mn0) * scale_log2);
-                s[nt][1] = exp2f((s[nt][1] - mn0) * scale_log2);
-                s[nt][2] = exp2f((s[nt][2] - mn1) * scale_log2);
-                s[nt][3] = exp2f((s[nt][3] - mn1) * scale_log2);
-                rs0 += s[nt][0] + s[nt][1];
-                rs1 += s[nt][2] + s[nt][3];
-            }
-            l0 = l0 * c0 + rs0;
-            l1 = l1 * c1 + rs1;
-#pragma unroll
-            for (int nt = 0; nt < 8; ++nt) { o[nt][0] *= c0; o[nt][1] *= c0; o[nt][2] *= c1; o[nt][3] *= c1; }
-            mma_p_b(o, s, sV + k0 * 128, lane, npairs);
-        }
-        l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
-        l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-        l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
-        l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-        const int row0 = qt * 16;
-        store_acc_bf16(o, gO, (long long)H * AT_HD, row0, T, lane, 1.f / l0, 1.f / l1);
-        if (tq == 0) {
-            if (row0 + gq < T) L[row0 + gq] = m0 * scale + logf(l0);
-            if (row0 + gq + 8 < T) L[row0 + gq + 8] = m1 * scale + logf(l1);
-        }
-    }
-}
-
-// Fused backward: delta, (dK, dV) per 16-key tile and dQ per 16-query tile, all from the resident tiles.
-__global__ void __launch_bounds__(128, 2)
-attention_bwd_resident_kernel(const bf16* __restrict__ qkv, const bf16* __restrict__ out, const bf16* __restrict__ dout,
-                              const float* __restrict__ lse, bf16* __restrict__ dqkv, int T, int Tp, int H,
-                              float scale_log2, float scale) {
-    extern __shared__ __align__(128) uint8_t smem_dyn[];
-    uint8_t* sQ = smem_dyn;
-    uint8_t* sK = sQ + Tp * 128;
-    uint8_t* sV = sK + Tp * 128;
-    uint8_t* sdO = sV + Tp * 128;
-    float* sLse = reinterpret_cast<float*>(sdO + Tp * 128);   // lse * log2(e); +inf for padded rows
-    float* sDelta = sLse + Tp;
-    const int bh = blockIdx.x, b = bh / H, h = bh % H;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-    const int tq = lane & 3, gq = lane >> 2;
-    const long long rs = 3LL * H * AT_HD;
-    const long long os = (long long)H * AT_HD;
-    const bf16* gQ = qkv + (long long)b * T * rs + (long long)h * AT_HD;
-    const bf16* gdO = dout + (long long)b * T * os + (long long)h * AT_HD;
-    const bf16* gO = out + (long long)b * T * os + (long long)h * AT_HD;
-    const float LOG2E = 1.4426950408889634f;
-
-    load_rows(sQ, gQ, rs, T, Tp, blockDim.x);
-    load_rows(sK, gQ + (long long)H * AT_HD, rs, T, Tp, blockDim.x);
-    load_rows(sV, gQ + 2LL * H * AT_HD, rs, T, Tp, blockDim.x);
-    load_rows(sdO, gdO, os, T, Tp, blockDim.x);
-    // while the async copies fly: delta[t] = sum_d dO[t,d] * O[t,d] straight from global, one warp per row
-    const float* Lg = lse + (long long)bh * T;
-    for (int t = warp; t < Tp; t += nwarps) {
-        float d = 0.f;
-        if (t < T) {
-            const float2 fo = unpack_bf16(reinterpret_cast<const uint32_t*>(gO + (long long)t * os)[lane]);
-            const float2 fd = unpack_bf16(reinterpret_cast<const uint32_t*>(gdO + (long long)t * os)[lane]);
-            d = warp_sum(fo.x * fd.x + fo.y * fd.y);
-        }
-        if (lane == 0) {
-            sDelta[t] = d;
-            sLse[t] = t < T ? Lg[t] * LOG2E : INFINITY;
-        }
-    }
-    cp_async_wait_all();
-    __syncthreads();
-
-    const int ntiles = Tp >> 4;
-    const long long rs_out = rs;
-    bf16* gdQ = dqkv + (long long)b * T * rs + (long long)h * AT_HD;
-    bf16* gdK = gdQ + (long long)H * AT_HD;
-    bf16* gdV = gdQ + 2LL * H * AT_HD;
-
-    // items 0 .. ntiles-1: (dK, dV) of key tile i ; items ntiles .. 2*ntiles-1: dQ of query tile i - ntiles
-    for (int item = warp; item < 2 * ntiles; item += nwarps) {
-        if (item < ntiles) {
-            const int kt = item;
-            uint32_t kf[4][4], vf[4][4];
-            load_a_frags(sK, kt * 16, lane, kf);
-            load_a_frags(sV, kt * 16, lane, vf);
-            float dk[8][4], dv[8][4];
-            zero_acc(dk);
-            zero_acc(dv);
-            for (int q0 = 0; q0 < Tp; q0 += AT_BLOCK) {
-                const int npairs = min(4, (Tp - q0) >> 4);
-                float st[8][4], dpt[8][4];
-                zero_acc(st);
-                zero_acc(dpt);
-                mma_a_bT(st, kf, sQ + q0 * 128, lane, npairs);      // S^T  = K Q^T
-                mma_a_bT(dpt, vf, sdO + q0 * 128, lane, npairs);    // dP^T = V dO^T
-#pragma unroll
-                for (int nt = 0; nt < 8; ++nt) {
-                    if (nt >= 2 * npairs) continue;
-                    const int q = q0 + nt * 8 + 2 * tq;
-                    const float ls0 = sLse[q], ls1 = sLse[q + 1];
-                    const float d0 = sDelta[q], d1 = sDelta[q + 1];
-                    const float p0 = exp2f(st[nt][0] * scale_log2 - ls0);
-                    const float p1 = exp2f(st[nt][1] * scale_log2 - ls1);
-                    const float p2 = exp2f(st[nt][2] * scale_log2 - ls0);
-                    const float p3 = exp2f(st[nt][3] * scale_log2 - ls1);
-                    st[nt][0] = p0; st[nt][1] = p1; st[nt][2] = p2; st[nt][3] = p3;
-                    dpt[nt][0] = p0 * (dpt[nt][0] - d0) * scale;
-                    dpt[nt][1] = p1 * (dpt[nt][1] - d1) * scale;
-                    dpt[nt][2] = p2 * (dpt[nt][2] - d0) * scale;
-                    dpt[nt][3] = p3 * (dpt[nt][3] - d1) * scale;
-                }
-                mma_p_b(dv, st, sdO + q0 * 128, lane, npairs);      // dV += P^T dO
-                mma_p_b(dk, dpt, sQ + q0 * 128, lane, npairs);      // dK += dS^T Q
-            }
-            store_acc_bf16(dk, gdK, rs_out, kt * 16, T, lane, 1.f, 1.f);
-            store_acc_bf16(dv, gdV, rs_out, kt * 16, T, lane, 1.f, 1.f);
-        } else {
-            const int qt = item - ntiles;
-            uint32_t qf[4][4], dof[4][4];
-            load_a_frags(sQ, qt * 16, lane, qf);
-            load_a_frags(sdO, qt * 16, lane, dof);
-            const int r_lo = qt * 16 + gq, r_hi = r_lo + 8;
-            const float ls0 = sLse[r_lo], ls1 = sLse[r_hi];
-            const float dl0 = sDelta[r_lo], dl1 = sDelta[r_hi];
-            float dq[8][4];
-            zero_acc(dq);
-            for (int k0 = 0; k0 < Tp; k0 += AT_BLOCK) {
-                const int npairs = min(4, (Tp - k0) >> 4);
-                float s[8][4], dp[8][4];
-                zero_acc(s);
-                zero_acc(dp);
-                mma_a_bT(s, qf, sK + k0 * 128, lane, npairs);       // S  = Q K^T
-                mma_a_bT(dp, dof, sV + k0 * 128, lane, npairs);     // dP = dO V^T
-#pragma unroll
-                for (int nt = 0; nt < 8; ++nt) {
-                    const int key = k0 + nt * 8 + 2 * tq;
-                    const bool v0 = key < T, v1 = key + 1 < T;
-                    const float p0 = v0 ? exp2f(s[nt][0] * scale_log2 - ls0) : 0.f;
-                    const float p1 = v1 ? exp2f(s[nt][1] * scale_log2 - ls0) : 0.f;
-                    const float p2 = v0 ? exp2f(s[nt][2] * scale_log2 - ls1) : 0.f;
-                    const float p3 = v1 ? exp2f(s[nt][3] * scale_log2 - ls1) : 0.f;
-                    dp[nt][0] = p0 * (dp[nt][0] - dl0) * scale;
-                    dp[nt][1] = p1 * (dp[nt][1] - dl0) * scale;
-                    dp[nt][2] = p2 * (dp[nt][2] - dl1) * scale;
-                    dp[nt][3] = p3 * (dp[nt][3] - dl1) * scale;
-                }
-                mma_p_b(dq, dp, sK + k0 * 128, lane, npairs);       // dQ += dS K
-            }
-            store_acc_bf16(dq, gdQ, rs_out, qt * 16, T, lane, 1.f, 1.f);
-        }
-    }
-}
-
-constexpr int AT_RESIDENT_MAX_T = 256;
-
-// B200VIT_ATTN_MODE=1 selects the mma.sync kernels for short sequences too (A/B measurements, debugging).
+// B200VIT_ATTN_MODE=1 forces the mma.sync kernels below for every length (A/B measurements, debugging).
 static int attention_mode() {
     static int mode = -1;
     if (mode < 0) {
@@ -672,26 +451,18 @@ static int attention_mode() {
 }
 
 // ---------------------------------------------------------------------------------------------
+// Dispatch: tokens <= 256 -> tcgen05 kernels with the whole head resident; <= 2048 -> tcgen05 streaming kernels;
+// longer (or B200VIT_ATTN_MODE=1) -> the FA2-style mma.sync kernels of this file.
+// ---------------------------------------------------------------------------------------------
 int attention_fwd_launch(const bf16* qkv, bf16* out, float* lse, int batch, int tokens, int heads, int head_dim,
                          float scale, cudaStream_t stream) {
     B200_CHECK_ARG(qkv && out && lse, "attention_fwd: null pointer");
     B200_CHECK_ARG(head_dim == AT_HD, "attention_fwd: head_dim must be 64 (got %d)", head_dim);
     B200_CHECK_ARG(batch > 0 && tokens > 0 && heads > 0, "attention_fwd: bad sizes");
     B200_CHECK_ARG(((uintptr_t)qkv % 16) == 0 && ((uintptr_t)out % 16) == 0, "attention_fwd: unaligned pointer");
-    if (tokens <= AT_RESIDENT_MAX_T && attention_mode() == 0)
-        return attention_fwd_tc_launch(qkv, out, lse, batch, tokens, heads, scale, stream);
-    if (attention_mode() == 0) return attention_fwd_long_launch(qkv, out, lse, batch, tokens, heads, scale, stream);
-    if (tokens <= AT_RESIDENT_MAX_T) {
-        const int Tp = (tokens + 15) & ~15;
-        const int ntiles = Tp / 16;
-        const int rounds = (ntiles + 7) / 8;
-        const int nwarps = (ntiles + rounds - 1) / rounds;      // balanced: 13 tiles -> 7 warps x 2 rounds
-        const size_t smem = (size_t)3 * Tp * 128;
-        B200_CUDA(cudaFuncSetAttribute(attention_fwd_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attention_fwd_resident_kernel<<<batch * heads, nwarps * 32, smem, stream>>>(
-            qkv, out, lse, tokens, Tp, heads, scale * 1.4426950408889634f, scale);
-        B200_LAUNCH_CHECK();
-        return 0;
+    if (attention_mode() == 0) {
+        if (tokens <= AT_TC_MAX_T) return attention_fwd_tc_launch(qkv, out, lse, batch, tokens, heads, scale, stream);
+        if (tokens <= AT_LONG_MAX_T) return attention_fwd_long_launch(qkv, out, lse, batch, tokens, heads, scale, stream);
     }
     dim3 grid(batch * heads, (tokens + AT_BLOCK - 1) / AT_BLOCK);
     attention_fwd_kernel<false><<<grid, AT_THREADS, 0, stream>>>(qkv, out, lse, tokens, heads, scale * 1.4426950408889634f,
@@ -706,18 +477,8 @@ int attention_bwd_launch(const bf16* qkv, const bf16* out, const bf16* dout, con
     B200_CHECK_ARG(qkv && out && dout && lse && delta && dqkv, "attention_bwd: null pointer");
     B200_CHECK_ARG(head_dim == AT_HD, "attention_bwd: head_dim must be 64 (got %d)", head_dim);
     B200_CHECK_ARG(batch > 0 && tokens > 0 && heads > 0, "attention_bwd: bad sizes");
-    if (tokens <= AT_RESIDENT_MAX_T && attention_mode() == 0)
+    if (tokens <= AT_TC_MAX_T && attention_mode() == 0)
         return attention_bwd_tc_launch(qkv, out, dout, lse, dqkv, dbias, batch, tokens, heads, scale, stream);
-    if (tokens <= AT_RESIDENT_MAX_T) {
-        // delta is computed inside the fused kernel (kept in shared memory); the scratch buffer is not touched
-        const int Tp = (tokens + 15) & ~15;
-        const size_t smem = (size_t)4 * Tp * 128 + (size_t)2 * Tp * sizeof(float);
-        B200_CUDA(cudaFuncSetAttribute(attention_bwd_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attention_bwd_resident_kernel<<<batch * heads, 128, smem, stream>>>(
-            qkv, out, dout, lse, dqkv, tokens, Tp, heads, scale * 1.4426950408889634f, scale);
-        B200_LAUNCH_CHECK();
-        return dbias ? colsum_bf16_launch(dqkv, 3LL * heads * AT_HD, dbias, (long long)batch * tokens, 3 * heads * AT_HD, stream) : 0;
-    }
     const long long rows = (long long)batch * tokens * heads;
     attention_delta_kernel<<<(unsigned)((rows * 8 + 255) / 256), 256, 0, stream>>>(out, dout, delta, batch, tokens, heads);
     B200_LAUNCH_CHECK();

@@ -242,615 +242,11 @@ attention_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
     }
 }
 
-// =============================================================================================
-// Backward (persistent). Per (batch, head) the producer stages the FULL Q, K, V and dO tiles of the head once
-// (2-deep ring) and computes the per-token statistics lse*log2e and delta = rowsum(dO * O) * scale; the head is
-// then processed as 2*nt work items that all read those resident tiles:
-//   items 0..nt-1   "KV" item, 128 keys:    S^T = K_t Q^T, dP^T = V_t dO^T  ->  dV_t = P^T dO, dK_t = dS^T Q
-//   items nt..2nt-1 "Q" item, 128 queries:  S   = Q_t K^T, dP   = dO_t V^T  ->  dQ_t = dS K
-// Both are the same program on different operands: acc0 = X Y^T, acc1 = X' Y'^T (UMMA 128 x Nk x 64 into two
-// 256-column TMEM regions); 16 math warps (4 TMEM lane quarters x 4 column quarters) turn (acc0, acc1) into
-// P = exp2(acc0*c - lse) and dS = P (acc1*scale - delta), store them as bf16 pairs IN PLACE (each column quarter
-// packs into the front of its own column range), and the second round of UMMAs (A operand from TMEM, B = the
-// resident full tiles re-used as MN-major operands) produces the 128 x 64 gradients. The statistics index
-// (lse, delta) is the column for KV items and the row for Q items.
-// =============================================================================================
-constexpr int ATB_MATH_WARPS = 16;
-constexpr int ATB_THREADS = 64 + ATB_MATH_WARPS * 32;   // warp 0: TMA + statistics, warp 1: TMEM alloc + MMA issue
-constexpr int ATB_TMEM_COLS = 512;
-constexpr int ATB_OUT_COL = 192;      // gradient accumulators live in columns [192, 256) of each region
 constexpr int ATB_TAIL_PAD = 8192;    // a 128-row X tile starting at row 128 over-reads a 208-row stage by 6 KB
 
-__global__ void __launch_bounds__(ATB_THREADS, 1)
-attention_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
-                        const bf16* __restrict__ out, const bf16* __restrict__ dout, const float* __restrict__ lse,
-                        bf16* __restrict__ dqkv, int num_heads_total, int T, int Nk, int H, float scale_log2,
-                        float scale) {
-    extern __shared__ uint8_t smem_raw[];
-    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t tile_bytes = (uint32_t)Nk * 128u;
-    const uint32_t tile_stride = (tile_bytes + 1023u) & ~1023u;
-    const uint32_t stage_bytes = 4 * tile_stride;                       // Q, K, V, dO
-    const uint32_t stat_base = smem_base + 2 * stage_bytes + ATB_TAIL_PAD;   // per stage: lse2 [Nk], delta*scale [Nk]
-    const uint32_t bar_base = stat_base + 2u * 2u * Nk * 4u;
-    auto full_bar = [&](int s) { return bar_base + 8u * s; };
-    auto stat_bar = [&](int s) { return bar_base + 16u + 8u * s; };
-    auto empty_bar = [&](int s) { return bar_base + 32u + 8u * s; };
-    const uint32_t s_ready = bar_base + 48u, p_ready = bar_base + 56u, o_ready = bar_base + 64u, t_free = bar_base + 72u;
-    const uint32_t tmem_slot = bar_base + 80u;
-    uint8_t* gen = smem_raw - smem_u32(smem_raw);                       // generic pointer = gen + shared address
-    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen + tmem_slot);
-
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int nt = (T + ATC_BM - 1) / ATC_BM;
-    const int nitems = 2 * nt;
-
-    if (warp == 0 && lane == 0) {
-        prefetch_tmap(&tmQKV);
-        prefetch_tmap(&tmDO);
-        for (int i = 0; i < 2; ++i) {
-            mbar_init(full_bar(i), 1);
-            mbar_init(stat_bar(i), 1);
-            mbar_init(empty_bar(i), 1);
-        }
-        mbar_init(s_ready, 1);
-        mbar_init(p_ready, ATB_MATH_WARPS);
-        mbar_init(o_ready, 1);
-        mbar_init(t_free, ATB_MATH_WARPS);
-        fence_barrier_init();
-    }
-    if (warp == 1) {
-        tmem_alloc<1>(tmem_slot, ATB_TMEM_COLS);
-        tmem_relinquish<1>();
-    }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = *tmem_slot_ptr;
-    const uint32_t acc0 = tmem, acc1 = tmem + 256;
-
-    // column quarters: 16-column chunks dealt 4,3,3,3 (for Nk = 208); cq range = [cq_begin(q), cq_begin(q+1))
-    const int nchunks = Nk / 16;
-    auto cq_begin = [&](int q) { return 16 * ((nchunks * q + 3) / 4); };
-    auto packed_col = [&](int src_col) {       // where the bf16 pair holding source column src_col lives
-        int q = 3;
-        while (q > 0 && src_col < cq_begin(q)) --q;
-        const int c0 = cq_begin(q);
-        return c0 + ((src_col - c0) >> 1);
-    };
-
-    if (warp == 0) {
-        // ===================== TMA producer + per-token statistics =====================
-        const float LOG2E = 1.4426950408889634f;
-        const long long os = (long long)H * 64;
-        int it = 0;
-        for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
-            const int s = it & 1;
-            const uint32_t ph = (it >> 1) & 1;
-            const int b = w / H, h = w % H;
-            if (lane == 0) mbar_wait(empty_bar(s), ph ^ 1u);
-            __syncwarp();
-            if (lane == 0) {
-                const uint32_t sQ = smem_base + s * stage_bytes;
-                mbar_arrive_expect_tx(full_bar(s), 4 * tile_bytes);
-                tma_load_4d(sQ, &tmQKV, full_bar(s), 0, 0, h, b);
-                tma_load_4d(sQ + tile_stride, &tmQKV, full_bar(s), 0, 0, H + h, b);
-                tma_load_4d(sQ + 2 * tile_stride, &tmQKV, full_bar(s), 0, 0, 2 * H + h, b);
-                tma_load_4d(sQ + 3 * tile_stride, &tmDO, full_bar(s), 0, 0, h, b);
-            }
-            float* sLse2 = reinterpret_cast<float*>(gen + stat_base + (uint32_t)s * 2u * Nk * 4u);
-            float* sDelta = sLse2 + Nk;
-            const bf16* gO = out + (long long)b * T * os + (long long)h * 64;
-            const bf16* gdO = dout + (long long)b * T * os + (long long)h * 64;
-            const float* L = lse + (long long)w * T;
-            // one lane per token row (rows are 128 B): all loads of a lane are independent -> deep memory parallelism
-            for (int t = lane; t < Nk; t += 32) {
-                float d = 0.f;
-                if (t < T) {
-                    const uint4* po = reinterpret_cast<const uint4*>(gO + (long long)t * os);
-                    const uint4* pd = reinterpret_cast<const uint4*>(gdO + (long long)t * os);
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const uint4 a = __ldg(po + i), c = __ldg(pd + i);
-                        const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, cw[4] = {c.x, c.y, c.z, c.w};
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            const float2 fa = unpack_bf16(aw[k]), fc = unpack_bf16(cw[k]);
-                            d = fmaf(fa.x, fc.x, fmaf(fa.y, fc.y, d));
-                        }
-                    }
-                }
-                sDelta[t] = d * scale;
-                sLse2[t] = t < T ? L[t] * LOG2E : INFINITY;       // +inf -> P = 0 for padded positions
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(stat_bar(s));
-        }
-    } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        if (lane == 0) {
-            const uint32_t idesc1 = make_idesc_bf16(ATC_BM, Nk, 0, 0);
-            const uint32_t idesc2 = make_idesc_bf16(ATC_BM, 64, 0, 1);
-            const int ksteps = Nk / 16;
-            int it = 0, j = 0;
-            for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
-                const int s = it & 1;
-                const uint32_t ph = (it >> 1) & 1;
-                const uint32_t sQ = smem_base + s * stage_bytes, sK = sQ + tile_stride, sV = sK + tile_stride,
-                               sdO = sV + tile_stride;
-                mbar_wait(full_bar(s), ph);
-                tc_fence_after();
-                for (int item = 0; item < nitems; ++item, ++j) {
-                    const bool kv_item = item < nt;
-                    const uint32_t roff = (uint32_t)(kv_item ? item : item - nt) * (ATC_BM * 128);
-                    const uint32_t sX = (kv_item ? sK : sQ) + roff, sX2 = (kv_item ? sV : sdO) + roff;
-                    const uint32_t sY = kv_item ? sQ : sK, sY2 = kv_item ? sdO : sV;
-                    mbar_wait(t_free, (uint32_t)(j & 1) ^ 1u);
-                    tc_fence_after();
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        umma_bf16<1>(acc0, make_smem_desc_sw128(sX + k * 32, 1024, 0),
-                                     make_smem_desc_sw128(sY + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        umma_bf16<1>(acc1, make_smem_desc_sw128(sX2 + k * 32, 1024, 0),
-                                     make_smem_desc_sw128(sY2 + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
-                    umma_commit(s_ready);
-                    mbar_wait(p_ready, (uint32_t)(j & 1));
-                    tc_fence_after();
-                    if (kv_item) {
-                        for (int k = 0; k < ksteps; ++k)      // dV_t = P^T dO
-                            umma_bf16_ts(acc0 + ATB_OUT_COL, acc0 + packed_col(16 * k),
-                                         make_smem_desc_sw128(sY2 + k * 2048, 1024, 0), idesc2, k > 0 ? 1u : 0u);
-                    }
-                    for (int k = 0; k < ksteps; ++k)          // dK_t = dS^T Q   or   dQ_t = dS K
-                        umma_bf16_ts(acc1 + ATB_OUT_COL, acc1 + packed_col(16 * k),
-                                     make_smem_desc_sw128(sY + k * 2048, 1024, 0), idesc2, k > 0 ? 1u : 0u);
-                    umma_commit(o_ready);
-                }
-                umma_commit(empty_bar(s));      // every MMA reading this stage has retired
-            }
-        }
-        __syncwarp();
-    } else {
-        // ===================== math + epilogue warps =====================
-        const int mw = warp - 2;
-        const int quarter = warp & 3;            // TMEM lane quarter this warp may access
-        const int cq = mw >> 2;                  // column quarter
-        const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
-        const int c_begin = cq_begin(cq), c_end = cq == 3 ? Nk : cq_begin(cq + 1);
-        const long long rs = 3LL * H * 64;
-        int it = 0, j = 0;
-        for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
-            const int s = it & 1;
-            const uint32_t ph = (it >> 1) & 1;
-            const int b = w / H, h = w % H;
-            const float* sLse2 = reinterpret_cast<const float*>(gen + stat_base + (uint32_t)s * 2u * Nk * 4u);
-            const float* sDelta = sLse2 + Nk;
-            mbar_wait(stat_bar(s), ph);
-            for (int item = 0; item < nitems; ++item, ++j) {
-                const bool kv_item = item < nt;
-                const int row = (kv_item ? item : item - nt) * ATC_BM + quarter * 32 + lane;
-                const bool row_ok = row < T;
-                const float row_lse2 = sLse2[min(row, Nk - 1)], row_delta = sDelta[min(row, Nk - 1)];
-                mbar_wait(s_ready, (uint32_t)(j & 1));
-                tc_fence_after();
-                for (int c = c_begin; c < c_end; c += 16) {
-                    uint32_t sv[16], dp[16];
-                    tmem_ld_32x16(acc0 + lane_off + c, sv);
-                    tmem_ld_32x16(acc1 + lane_off + c, dp);
-                    float l2[16], dl[16];
-                    if (kv_item) {
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            const float4 a = reinterpret_cast<const float4*>(sLse2 + c)[i];
-                            const float4 d = reinterpret_cast<const float4*>(sDelta + c)[i];
-                            l2[4 * i] = a.x; l2[4 * i + 1] = a.y; l2[4 * i + 2] = a.z; l2[4 * i + 3] = a.w;
-                            dl[4 * i] = d.x; dl[4 * i + 1] = d.y; dl[4 * i + 2] = d.z; dl[4 * i + 3] = d.w;
-                        }
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) { l2[i] = row_lse2; dl[i] = row_delta; }
-                    }
-                    tmem_ld_wait();
-                    float p[16], ds[16];
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        p[i] = fast_ex2(fmaf(__uint_as_float(sv[i]), scale_log2, -l2[i]));
-                        ds[i] = p[i] * fmaf(__uint_as_float(dp[i]), scale, -dl[i]);
-                    }
-                    if (!kv_item && c + 16 > T) {      // Q item: padded key columns must not contribute to dQ
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) if (c + i >= T) ds[i] = 0.f;
-                    }
-                    uint32_t pk[8];
-                    const int pc = c_begin + ((c - c_begin) >> 1);
-                    if (kv_item) {
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) pk[i] = pack_bf16(p[2 * i], p[2 * i + 1]);
-                        tmem_st_32x8(acc0 + lane_off + pc, pk);
-                    }
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) pk[i] = pack_bf16(ds[2 * i], ds[2 * i + 1]);
-                    tmem_st_32x8(acc1 + lane_off + pc, pk);
-                }
-                tmem_st_wait();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(p_ready);
-
-                // epilogue: each column quarter converts 16 of the 64 gradient columns
-                mbar_wait(o_ready, (uint32_t)(j & 1));
-                tc_fence_after();
-                uint32_t r0[16], r1[16];
-                tmem_ld_32x16(acc1 + lane_off + ATB_OUT_COL + cq * 16, r1);
-                if (kv_item) tmem_ld_32x16(acc0 + lane_off + ATB_OUT_COL + cq * 16, r0);
-                tmem_ld_wait();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(t_free);
-                if (row_ok) {
-                    bf16* base = dqkv + ((long long)b * T + row) * rs + (long long)h * 64 + cq * 16;
-                    auto emit = [&](const uint32_t (&r)[16], bf16* dst) {
-                        uint4 o0, o1;
-                        o0.x = pack_bf16(__uint_as_float(r[0]), __uint_as_float(r[1]));
-                        o0.y = pack_bf16(__uint_as_float(r[2]), __uint_as_float(r[3]));
-                        o0.z = pack_bf16(__uint_as_float(r[4]), __uint_as_float(r[5]));
-                        o0.w = pack_bf16(__uint_as_float(r[6]), __uint_as_float(r[7]));
-                        o1.x = pack_bf16(__uint_as_float(r[8]), __uint_as_float(r[9]));
-                        o1.y = pack_bf16(__uint_as_float(r[10]), __uint_as_float(r[11]));
-                        o1.z = pack_bf16(__uint_as_float(r[12]), __uint_as_float(r[13]));
-                        o1.w = pack_bf16(__uint_as_float(r[14]), __uint_as_float(r[15]));
-                        reinterpret_cast<uint4*>(dst)[0] = o0;
-                        reinterpret_cast<uint4*>(dst)[1] = o1;
-                    };
-                    if (kv_item) {
-                        emit(r1, base + (long long)H * 64);        // dK
-                        emit(r0, base + 2LL * H * 64);             // dV
-                    } else {
-                        emit(r1, base);                            // dQ
-                    }
-                }
-            }
-        }
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 1) {
-        tc_fence_after();
-        tmem_dealloc<1>(tmem, ATB_TMEM_COLS);
-    }
-}
-
 // =============================================================================================
-// Backward, pipelined variant (Nk <= 224, i.e. T <= 224: covers the 197-token case). Same operands and math as the
-// kernel above, but every work item's column range is processed in two chunks of width W <= 112 so that a
-// sub-item needs only 256 TMEM columns:
-//     [0, W) acc0 chunk (packed P in place in [0, W/2)) | [64, 128) out0 (dV) | [128, 128+W) acc1 chunk (packed dS
-//     in place) | [192, 256) out1 (dK or dQ)
-// Two sub-items are therefore in flight per SM, one per TMEM slot, each owned by a group of 4 math warps
-// (thread <-> row); the MMA thread runs a small state machine over both slots, so S/dP MMAs, the exp/dS math,
-// the gradient MMAs and the read-out of neighbouring sub-items overlap. Partial gradients of the two chunks
-// of an item are summed in registers (fp32) by the owning thread and stored once.
-// =============================================================================================
-constexpr int ATP_THREADS = 320;      // warp 0: TMA + statistics, warp 1: TMEM alloc + MMA issue, warps 2-9: 2 math groups
-constexpr int ATP_MAX_W = 112;
-
-__global__ void __launch_bounds__(ATP_THREADS, 1)
-attention_bwd_tc2_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
-                         const bf16* __restrict__ out, const bf16* __restrict__ dout, const float* __restrict__ lse,
-                         bf16* __restrict__ dqkv, int num_heads_total, int T, int Nk, int H, float scale_log2,
-                         float scale) {
-    extern __shared__ uint8_t smem_raw[];
-    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t tile_bytes = (uint32_t)Nk * 128u;
-    const uint32_t tile_stride = (tile_bytes + 1023u) & ~1023u;
-    const uint32_t stage_bytes = 4 * tile_stride;                       // Q, K, V, dO
-    const uint32_t stat_base = smem_base + 2 * stage_bytes + ATB_TAIL_PAD;   // per stage: lse2 [Nk], delta*scale [Nk]
-    const uint32_t bar_base = stat_base + 2u * 2u * Nk * 4u;
-    auto full_bar = [&](int s) { return bar_base + 8u * s; };
-    auto stat_bar = [&](int s) { return bar_base + 16u + 8u * s; };
-    auto empty_bar = [&](int s) { return bar_base + 32u + 8u * s; };
-    auto s_ready = [&](int g) { return bar_base + 48u + 8u * g; };
-    auto p_ready = [&](int g) { return bar_base + 64u + 8u * g; };
-    auto o_ready = [&](int g) { return bar_base + 80u + 8u * g; };
-    auto slot_free = [&](int g) { return bar_base + 96u + 8u * g; };
-    const uint32_t tmem_slot = bar_base + 112u;
-    uint8_t* gen = smem_raw - smem_u32(smem_raw);
-    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen + tmem_slot);
-
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int nt = (T + ATC_BM - 1) / ATC_BM;
-    const int nitems = 2 * nt;
-    const int W0 = ((Nk / 2) + 15) & ~15;          // chunk 0 = columns [0, W0), chunk 1 = [W0, Nk)
-    const int nch = Nk > W0 ? 2 : 1;
-
-    if (warp == 0 && lane == 0) {
-        prefetch_tmap(&tmQKV);
-        prefetch_tmap(&tmDO);
-        for (int i = 0; i < 2; ++i) {
-            mbar_init(full_bar(i), 1);
-            mbar_init(stat_bar(i), 1);
-            mbar_init(empty_bar(i), 1);
-            mbar_init(s_ready(i), 1);
-            mbar_init(p_ready(i), 4);
-            mbar_init(o_ready(i), 1);
-            mbar_init(slot_free(i), 4);
-        }
-        fence_barrier_init();
-    }
-    if (warp == 1) {
-        tmem_alloc<1>(tmem_slot, 512);
-        tmem_relinquish<1>();
-    }
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = *tmem_slot_ptr;
-
-    if (warp == 0) {
-        // ===================== TMA producer + per-token statistics =====================
-        const float LOG2E = 1.4426950408889634f;
-        const long long os = (long long)H * 64;
-        int it = 0;
-        for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
-            const int s = it & 1;
-            const uint32_t ph = (it >> 1) & 1;
-            const int b = w / H, h = w % H;
-            if (lane == 0) mbar_wait(empty_bar(s), ph ^ 1u);
-            __syncwarp();
-            if (lane == 0) {
-                const uint32_t sQ = smem_base + s * stage_bytes;
-                mbar_arrive_expect_tx(full_bar(s), 4 * tile_bytes);
-                tma_load_4d(sQ, &tmQKV, full_bar(s), 0, 0, h, b);
-                tma_load_4d(sQ + tile_stride, &tmQKV, full_bar(s), 0, 0, H + h, b);
-                tma_load_4d(sQ + 2 * tile_stride, &tmQKV, full_bar(s), 0, 0, 2 * H + h, b);
-                tma_load_4d(sQ + 3 * tile_stride, &tmDO, full_bar(s), 0, 0, h, b);
-            }
-            float* sLse2 = reinterpret_cast<float*>(gen + stat_base + (uint32_t)s * 2u * Nk * 4u);
-            float* sDelta = sLse2 + Nk;
-            const bf16* gO = out + (long long)b * T * os + (long long)h * 64;
-            const bf16* gdO = dout + (long long)b * T * os + (long long)h * 64;
-            const float* L = lse + (long long)w * T;
-            for (int t = lane; t < Nk; t += 32) {
-                float d = 0.f;
-                if (t < T) {
-                    const uint4* po = reinterpret_cast<const uint4*>(gO + (long long)t * os);
-                    const uint4* pd = reinterpret_cast<const uint4*>(gdO + (long long)t * os);
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const uint4 a = __ldg(po + i), c = __ldg(pd + i);
-                        const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, cw[4] = {c.x, c.y, c.z, c.w};
-#pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            const float2 fa = unpack_bf16(aw[k]), fc = unpack_bf16(cw[k]);
-                            d = fmaf(fa.x, fc.x, fmaf(fa.y, fc.y, d));
-                        }
-                    }
-                }
-                sDelta[t] = d * scale;
-                sLse2[t] = t < T ? L[t] * LOG2E : INFINITY;
-            }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(stat_bar(s));
-        }
-    } else if (warp == 1) {
-        // ===================== MMA issuer: state machine over the two TMEM slots =====================
-        if (lane == 0) {
-            const uint32_t idesc2 = make_idesc_bf16(ATC_BM, 64, 0, 1);
-            uint32_t n_free[2] = {0, 0}, n_p[2] = {0, 0};      // completed waits on slot_free / p_ready per slot
-            int it = 0;
-            for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
-                const int s = it & 1;
-                const uint32_t ph = (it >> 1) & 1;
-                const uint32_t sQ = smem_base + s * stage_bytes, sK = sQ + tile_stride, sV = sK + tile_stride,
-                               sdO = sV + tile_stride;
-                mbar_wait(full_bar(s), ph);
-                tc_fence_after();
-                int sub[2] = {0, 0};            // next sub-item (item slot * nch + chunk) of each group
-                int phase[2] = {0, 0};          // 0: S/dP MMAs pending, 1: gradient MMAs pending
-                int nsub[2];
-                nsub[0] = ((nitems + 1) / 2) * nch;
-                nsub[1] = (nitems / 2) * nch;
-                while (sub[0] < nsub[0] || sub[1] < nsub[1]) {
-#pragma unroll
-                    for (int g = 0; g < 2; ++g) {
-                        if (sub[g] >= nsub[g]) continue;
-                        const int item = g + 2 * (sub[g] / nch);
-                        const int ch = sub[g] % nch;
-                        const bool kv_item = item < nt;
-                        const uint32_t roff = (uint32_t)(kv_item ? item : item - nt) * (ATC_BM * 128);
-                        const uint32_t sX = (kv_item ? sK : sQ) + roff, sX2 = (kv_item ? sV : sdO) + roff;
-                        const uint32_t sY = kv_item ? sQ : sK, sY2 = kv_item ? sdO : sV;
-                        const int c0 = ch == 0 ? 0 : W0;
-                        const int W = ch == 0 ? W0 : Nk - W0;
-                        const uint32_t slot = tmem + g * 256;
-                        if (phase[g] == 0) {
-                            if (!mbar_try_wait(slot_free(g), (n_free[g] & 1u) ^ 1u)) continue;
-                            ++n_free[g];
-                            tc_fence_after();
-                            const uint32_t idesc1 = make_idesc_bf16(ATC_BM, W, 0, 0);
-                            const uint32_t yoff = (uint32_t)c0 * 128u;
-                            // the two accumulation chains are independent: issue them interleaved so the tensor pipe
-                            // can overlap the (latency-bound) dependent k-steps of one with the other
-#pragma unroll
-                            for (int k = 0; k < 4; ++k) {
-                                umma_bf16<1>(slot, make_smem_desc_sw128(sX + k * 32, 1024, 0),
-                                             make_smem_desc_sw128(sY + yoff + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
-                                umma_bf16<1>(slot + 128, make_smem_desc_sw128(sX2 + k * 32, 1024, 0),
-                                             make_smem_desc_sw128(sY2 + yoff + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
-                            }
-                            umma_commit(s_ready(g));
-                            phase[g] = 1;
-                        } else {
-                            if (!mbar_try_wait(p_ready(g), n_p[g] & 1u)) continue;
-                            ++n_p[g];
-                            tc_fence_after();
-                            const int ksteps = W / 16;
-                            for (int k = 0; k < ksteps; ++k) {
-                                if (kv_item)                          // dV_t = P^T dO over this query chunk
-                                    umma_bf16_ts(slot + 64, slot + 8 * k,
-                                                 make_smem_desc_sw128(sY2 + (uint32_t)(c0 + 16 * k) * 128u, 1024, 0), idesc2,
-                                                 k > 0 ? 1u : 0u);
-                                // dK_t = dS^T Q   or   dQ_t = dS K   (independent chain, interleaved)
-                                umma_bf16_ts(slot + 192, slot + 128 + 8 * k,
-                                             make_smem_desc_sw128(sY + (uint32_t)(c0 + 16 * k) * 128u, 1024, 0), idesc2,
-                                             k > 0 ? 1u : 0u);
-                            }
-                            umma_commit(o_ready(g));
-                            phase[g] = 0;
-                            ++sub[g];
-                        }
-                    }
-                }
-                umma_commit(empty_bar(s));      // every MMA reading this stage has retired
-            }
-        }
-        __syncwarp();
-    } else {
-        // ===================== math + read-out groups =====================
-        const int g = (warp - 2) >> 2;
-        const int quarter = warp & 3;
-        const uint32_t slot = tmem + g * 256 + ((uint32_t)(quarter * 32) << 16);
-        const long long rs = 3LL * H * 64;
-        uint32_t n_s = 0, n_o = 0;
-        int it = 0;
-        for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
-            const int s = it & 1;
-            const uint32_t ph = (it >> 1) & 1;
-            const int b = w / H, h = w % H;
-            const float* sLse2 = reinterpret_cast<const float*>(gen + stat_base + (uint32_t)s * 2u * Nk * 4u);
-            const float* sDelta = sLse2 + Nk;
-            mbar_wait(stat_bar(s), ph);
-            for (int item = g; item < nitems; item += 2) {
-                const bool kv_item = item < nt;
-                const int row = (kv_item ? item : item - nt) * ATC_BM + quarter * 32 + lane;
-                const bool row_ok = row < T;
-                const float row_lse2 = sLse2[min(row, Nk - 1)], row_delta = sDelta[min(row, Nk - 1)];
-                // partial gradients of the first column chunk, kept as packed bf16 pairs until the second chunk's arrive
-                uint32_t part1[32], part0[32];
-                bf16* const gbase = dqkv + ((long long)b * T + row) * rs + (long long)h * 64;
-                for (int ch = 0; ch < nch; ++ch) {
-                    const int c0 = ch == 0 ? 0 : W0;
-                    const int W = ch == 0 ? W0 : Nk - W0;
-                    mbar_wait(s_ready(g), n_s & 1u);
-                    ++n_s;
-                    tc_fence_after();
-                    // software-pipelined over 16-column pieces: the TMEM loads of piece c+16 are in flight while
-                    // piece c is exponentiated, multiplied and packed
-                    uint32_t sv[16], dp[16];
-                    tmem_ld_32x16(slot, sv);
-                    tmem_ld_32x16(slot + 128, dp);
-                    tmem_ld_wait();
-                    for (int c = 0; c < W; c += 16) {
-                        uint32_t svn[16], dpn[16];
-                        const bool more = c + 16 < W;
-                        if (more) {
-                            tmem_ld_32x16(slot + c + 16, svn);
-                            tmem_ld_32x16(slot + 128 + c + 16, dpn);
-                        }
-                        float l2[16], dl[16];
-                        if (kv_item) {
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) {
-                                const float4 a = reinterpret_cast<const float4*>(sLse2 + c0 + c)[i];
-                                const float4 d = reinterpret_cast<const float4*>(sDelta + c0 + c)[i];
-                                l2[4 * i] = a.x; l2[4 * i + 1] = a.y; l2[4 * i + 2] = a.z; l2[4 * i + 3] = a.w;
-                                dl[4 * i] = d.x; dl[4 * i + 1] = d.y; dl[4 * i + 2] = d.z; dl[4 * i + 3] = d.w;
-                            }
-                        } else {
-#pragma unroll
-                            for (int i = 0; i < 16; ++i) { l2[i] = row_lse2; dl[i] = row_delta; }
-                        }
-                        float p[16], ds[16];
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) {
-                            p[i] = fast_ex2(fmaf(__uint_as_float(sv[i]), scale_log2, -l2[i]));
-                            ds[i] = p[i] * fmaf(__uint_as_float(dp[i]), scale, -dl[i]);
-                        }
-                        if (!kv_item && c0 + c + 16 > T) {      // Q item: padded key columns must not contribute to dQ
-#pragma unroll
-                            for (int i = 0; i < 16; ++i) if (c0 + c + i >= T) ds[i] = 0.f;
-                        }
-                        uint32_t pk[8];
-                        if (kv_item) {
-#pragma unroll
-                            for (int i = 0; i < 8; ++i) pk[i] = pack_bf16(p[2 * i], p[2 * i + 1]);
-                            tmem_st_32x8(slot + (c >> 1), pk);
-                        }
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) pk[i] = pack_bf16(ds[2 * i], ds[2 * i + 1]);
-                        tmem_st_32x8(slot + 128 + (c >> 1), pk);
-                        if (more) {
-                            tmem_ld_wait();
-#pragma unroll
-                            for (int i = 0; i < 16; ++i) { sv[i] = svn[i]; dp[i] = dpn[i]; }
-                        }
-                    }
-                    tmem_st_wait();
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(p_ready(g));
-
-                    // read out this chunk's gradients: the first chunk is parked in registers (packed bf16), the last
-                    // chunk is added to it and stored
-                    mbar_wait(o_ready(g), n_o & 1u);
-                    ++n_o;
-                    tc_fence_after();
-                    const bool last = ch == nch - 1;
-                    auto readout = [&](uint32_t tcol, uint32_t (&part)[32], bf16* dst) {
-#pragma unroll
-                        for (int c = 0; c < 64; c += 32) {
-                            uint32_t r[32];
-                            tmem_ld_32x32(slot + tcol + c, r);
-                            tmem_ld_wait();
-                            if (!last) {
-#pragma unroll
-                                for (int i = 0; i < 16; ++i)
-                                    part[c / 2 + i] = pack_bf16(__uint_as_float(r[2 * i]), __uint_as_float(r[2 * i + 1]));
-                            } else {
-                                uint32_t o[16];
-#pragma unroll
-                                for (int i = 0; i < 16; ++i) {
-                                    float x0 = __uint_as_float(r[2 * i]), x1 = __uint_as_float(r[2 * i + 1]);
-                                    if (nch > 1) {
-                                        const float2 pv = unpack_bf16(part[c / 2 + i]);
-                                        x0 += pv.x; x1 += pv.y;
-                                    }
-                                    o[i] = pack_bf16(x0, x1);
-                                }
-                                if (row_ok) {
-#pragma unroll
-                                    for (int i = 0; i < 4; ++i)
-                                        reinterpret_cast<uint4*>(dst + c)[i] = make_uint4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
-                                }
-                            }
-                        }
-                    };
-                    if (kv_item) {
-                        readout(192, part1, gbase + (long long)H * 64);      // dK
-                        readout(64, part0, gbase + 2LL * H * 64);            // dV
-                    } else {
-                        readout(192, part1, gbase);                          // dQ
-                    }
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(slot_free(g));
-                }
-            }
-        }
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 1) {
-        tc_fence_after();
-        tmem_dealloc<1>(tmem, 512);
-    }
-}
-
-// =============================================================================================
-// Backward, single-pass variant (T <= 256). The two kernels above build the probabilities twice per head (once with
-// keys on the TMEM lanes for dK/dV, once with queries on the lanes for dQ). Here they are built ONCE, keys on the
+// Backward (T <= 256), single pass. Earlier versions built the probabilities twice per head (once with keys on
+// the TMEM lanes for dK/dV, once with queries on the lanes for dQ). Here they are built ONCE, keys on the
 // lanes: per 128-key tile t and 64-query chunk c
 //     S^T = K_t Q_c^T, dP^T = V_t dO_c^T  ->  P^T, dS^T (bf16, packed in place)  ->  dV_t += P^T dO_c, dK_t += dS^T Q_c
 // and dS^T is ALSO written to shared memory as bf16, one 128-byte row of 64 queries per key: that is exactly the
@@ -1962,44 +1358,22 @@ int attention_bwd_tc_launch(const bf16* qkv, const bf16* out, const bf16* dout, 
     const size_t tile_stride = ((size_t)Nk * 128 + 1023) & ~(size_t)1023;
     const int total = batch * heads;
     const int grid = total < sm_count() ? total : sm_count();
-    static int variant = -1;       // B200VIT_ATTN_BWD=1 / 2 force the two-pass kernels (A/B measurements)
-    if (variant < 0) {
-        const char* e = getenv("B200VIT_ATTN_BWD");
-        variant = e ? atoi(e) : 0;
-    }
-    if (variant == 0) {
-        const size_t smem3 = 1024 + 4 * tile_stride + ATB_TAIL_PAD + 2 * 32768 + 2 * 2 * (size_t)Nk * 4 + 256 +
-                             (dbias ? (size_t)3 * heads * 64 * 4 : 0);
-        if (smem3 <= 232448) {
-            if (dbias) B200_CUDA(cudaMemsetAsync(dbias, 0, sizeof(float) * 3 * heads * 64, stream));
-            B200_CUDA(cudaFuncSetAttribute(attention_bwd_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
-            B200_CUDA(launch_kernel_pdl(attention_bwd_tc3_kernel, dim3(grid), dim3(AT3_THREADS), smem3, stream, tq, td, out, dout,
-                                        lse, dqkv, dbias, total, tokens, Nk, heads, scale * 1.4426950408889634f, scale));
-            B200_LAUNCH_CHECK();
-            return 0;
-        }
-    }
-    // the two-pass kernels below do not produce the bias gradient themselves
-    struct BiasAfter {
-        const bf16* dqkv; float* dbias; long long rows; int cols; cudaStream_t stream;
-        int run() const { return dbias ? colsum_bf16_launch(dqkv, cols, dbias, rows, cols, stream) : 0; }
-    } bias_after{dqkv, dbias, (long long)batch * tokens, 3 * heads * 64, stream};
-    {
-    const size_t smem = 1024 + 2 * 4 * tile_stride + ATB_TAIL_PAD + 2 * 2 * (size_t)Nk * 4 + 128;
-    B200_CHECK_ARG(smem <= 232448, "attention_bwd: %d tokens need %zu bytes of shared memory", tokens, smem);
-    B200_CUDA(cudaFuncSetAttribute(attention_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    if (((Nk / 2 + 15) & ~15) <= ATP_MAX_W && variant != 1) {
-        B200_CUDA(cudaFuncSetAttribute(attention_bwd_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attention_bwd_tc2_kernel<<<grid, ATP_THREADS, smem, stream>>>(tq, td, out, dout, lse, dqkv, total, tokens, Nk,
-                                                                    heads, scale * 1.4426950408889634f, scale);
-        B200_LAUNCH_CHECK();
-        return bias_after.run();
-    }
-    attention_bwd_tc_kernel<<<grid, ATB_THREADS, smem, stream>>>(tq, td, out, dout, lse, dqkv, total, tokens, Nk, heads,
-                                                               scale * 1.4426950408889634f, scale);
+    const size_t smem_base = 1024 + 4 * tile_stride + ATB_TAIL_PAD + 2 * 32768 + 2 * 2 * (size_t)Nk * 4 + 256;
+    B200_CHECK_ARG(smem_base <= 232448, "attention_bwd: %d tokens need %zu bytes of shared memory", tokens, smem_base);
+    // The in_proj_bias gradient is accumulated in shared memory ([3][heads][64] fp32) when that fits beside the tiles;
+    // with very many heads it comes from a column-sum pass over dqkv afterwards.
+    const size_t smem_bias = (size_t)3 * heads * 64 * 4;
+    const bool fused_bias = dbias != nullptr && smem_base + smem_bias <= 232448;
+    const size_t smem3 = smem_base + (fused_bias ? smem_bias : 0);
+    if (fused_bias) B200_CUDA(cudaMemsetAsync(dbias, 0, sizeof(float) * 3 * heads * 64, stream));
+    B200_CUDA(cudaFuncSetAttribute(attention_bwd_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
+    B200_CUDA(launch_kernel_pdl(attention_bwd_tc3_kernel, dim3(grid), dim3(AT3_THREADS), smem3, stream, tq, td, out, dout, lse,
+                                dqkv, fused_bias ? dbias : (float*)nullptr, total, tokens, Nk, heads,
+                                scale * 1.4426950408889634f, scale));
     B200_LAUNCH_CHECK();
-    return bias_after.run();
-    }
+    if (dbias != nullptr && !fused_bias)
+        return colsum_bf16_launch(dqkv, 3LL * heads * 64, dbias, (long long)batch * tokens, 3 * heads * 64, stream);
+    return 0;
 }
 
 }  // namespace b200vit

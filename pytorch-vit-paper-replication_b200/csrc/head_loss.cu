@@ -158,4 +158,70 @@ int softmax_ce_launch(const float* logits, const long long* labels, float* loss,
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// probs = softmax(logits) per row and labels = argmax (first maximal index): the post-processing of a prediction
+// (going_modular/predictions.py:62-66: torch.softmax(dim=1) then torch.argmax(dim=1)). One block per sample.
+// ---------------------------------------------------------------------------------------------
+__global__ void softmax_top1_kernel(const float* __restrict__ logits, float* __restrict__ probs,
+                                    long long* __restrict__ labels, int B, int C) {
+    __shared__ float s_val[32];
+    __shared__ int s_idx[32];
+    const int b = blockIdx.x;
+    const float* z = logits + (long long)b * C;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    float mx = -INFINITY;
+    int arg = 0x7fffffff;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        const float v = z[c];
+        if (v > mx || (v == mx && c < arg)) { mx = v; arg = c; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, mx, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, arg, o);
+        if (ov > mx || (ov == mx && oi < arg)) { mx = ov; arg = oi; }
+    }
+    if (lane == 0) { s_val[warp] = mx; s_idx[warp] = arg; }
+    __syncthreads();
+    if (warp == 0) {
+        mx = lane < nwarps ? s_val[lane] : -INFINITY;
+        arg = lane < nwarps ? s_idx[lane] : 0x7fffffff;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, mx, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, arg, o);
+            if (ov > mx || (ov == mx && oi < arg)) { mx = ov; arg = oi; }
+        }
+        if (lane == 0) { s_val[0] = mx; s_idx[0] = arg; }
+    }
+    __syncthreads();
+    mx = s_val[0];
+    arg = s_idx[0];
+    __syncthreads();
+    float se = 0.f;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) se += expf(z[c] - mx);
+    se = warp_sum(se);
+    if (lane == 0) s_val[warp] = se;
+    __syncthreads();
+    if (warp == 0) {
+        se = lane < nwarps ? s_val[lane] : 0.f;
+        se = warp_sum(se);
+        if (lane == 0) s_val[0] = se;
+    }
+    __syncthreads();
+    const float inv = 1.0f / s_val[0];
+    if (probs)
+        for (int c = threadIdx.x; c < C; c += blockDim.x) probs[(long long)b * C + c] = expf(z[c] - mx) * inv;
+    if (labels && threadIdx.x == 0) labels[b] = arg;
+}
+
+int softmax_top1_launch(const float* logits, float* probs, long long* labels, int batch, int classes, cudaStream_t stream) {
+    B200_CHECK_ARG(logits && (probs || labels), "softmax_top1: null pointer");
+    B200_CHECK_ARG(batch > 0 && classes > 0, "softmax_top1: bad sizes");
+    const int block = classes >= 512 ? 256 : (classes >= 64 ? 128 : 32);
+    softmax_top1_kernel<<<batch, block, 0, stream>>>(logits, probs, labels, batch, classes);
+    B200_LAUNCH_CHECK();
+    return 0;
+}
+
 }  // namespace b200vit

@@ -62,6 +62,8 @@ int head_bwd_launch(const float* xn, const float* w, const float* dlogits, float
 int softmax_ce_launch(const float* logits, const long long* labels, float* loss, float* dlogits, int* correct,
                       int batch, int classes, cudaStream_t stream);
 
+int softmax_top1_launch(const float* logits, float* probs, long long* labels, int batch, int classes, cudaStream_t stream);
+
 int l2norm_sq_launch(const float* const* ptrs_dev, const long long* sizes_dev, int num_tensors, long long max_size,
                      float* partials, int num_partials, float* out_sumsq, cudaStream_t stream);
 int adam_step_launch(const void* table_dev, int num_tensors, long long max_size, const float* lrs, const float* wds,

@@ -35,7 +35,7 @@ for name, op, epi, M, N, Kd, split in shapes:
     aux = None; ldaux = 0
     if epi == K.EPI_BIAS_RES: aux = torch.randn(M, N, device=dev); ldaux = N
     if epi == K.EPI_DGELU: aux = torch.randn(M, N, device=dev).bfloat16(); ldaux = N
-    if split == 0: split = K.split_k_for(M, N, Kd, dev)
+    if split == 0: split = 0
     for p in (0.0, 0.1) if epi in (K.EPI_BIAS_GELU, K.EPI_BIAS_RES, K.EPI_DGELU) else (0.0,):
         def run():
             K.gemm(op, epi, M, N, Kd, A, lda, B, ldb, C, N, C2=C2, ldc2=N, bias=bias, aux=aux, ldaux=ldaux,

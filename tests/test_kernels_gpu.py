@@ -215,7 +215,12 @@ def test_attention_fwd_bwd(Bn, T, H):
     assert rel_err(dbias, dqkv.float().reshape(Bn * T, -1).sum(0)) < 3e-3           # in_proj_bias gradient
     dqkv_plain = torch.empty_like(dqkv)
     K.attention_bwd(qkv, out, dout, lse, delta, dqkv_plain, Bn, T, H, hd, scale)
-    assert torch.equal(dqkv_plain, dqkv)
+    # Same arithmetic with and without the fused bias gradient. Not bit-equal in general: the two MMA-issuing warps of
+    # the kernel add their chunks' contributions to the dV / dK accumulators in a timing-dependent order (fp32
+    # reassociation), which can move a value across a bf16 rounding boundary: at most one bf16 ulp, on a few elements.
+    diff = (dqkv_plain.float() - dqkv.float()).abs()
+    assert (diff <= dqkv.float().abs() * 2.0 ** -7 + 1e-30).all()
+    assert (diff > 0).float().mean().item() < 1e-3
     ref.backward(dout.float().reshape(Bn, T, H, hd).permute(0, 2, 1, 3))
     for i, t in enumerate((q, k, v)):
         got = dqkv[:, :, i].float().permute(0, 2, 1, 3)
