@@ -212,6 +212,67 @@ int b200vit_adam_step(const void* table_dev, int num_tensors, long long max_size
                       int decoupled, const float* grad_sumsq, float max_norm, float grad_scale, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * One call per encoder block per direction: the launch sequence of TransformerEncoderBlock.forward
+ * (models/vit.py:166-169, with MultiHeadSelfAttentionBlock.forward :92-98 and MLPBlock.forward :128-131 inside) and of
+ * what autograd derives from it, issued from C instead of one Python -> C transition per kernel. The same kernels
+ * run in the same order as through the single-kernel entry points above; every buffer is provided by the caller
+ * (R = batch * tokens token rows, D = dim = heads * 64, M = mlp). Set struct_bytes = sizeof(the struct).
+ * Dropout sites: key1 = after the GELU (vit.py:122), key2 = after fc2 (vit.py:125), attn = on the attention
+ * probabilities (vit.py:86-90, p = 0 by default); mlp_p / attn_p = 0 outside training.
+ * ------------------------------------------------------------------------------------------------ */
+typedef struct b200vit_block_fwd_args {
+    int struct_bytes;
+    int batch, tokens, heads, dim, mlp;
+    float eps_msa, eps_mlp;                 /* nn.LayerNorm eps of the two norms */
+    float mlp_p, attn_p;
+    unsigned long long key1_seed, key1_offset, key2_seed, key2_offset, attn_seed, attn_offset;
+    const float* x;                         /* f32 [R, D] block input (residual stream) */
+    const float *ln1_w, *ln1_b, *b_in, *b_out, *ln2_w, *ln2_b, *b1, *b2;         /* f32 parameters */
+    const void *w_in16, *w_out16, *w1_16, *w2_16;                                /* bf16 copies of [3D,D] [D,D] [M,D] [D,M] */
+    /* outputs; everything but x2 is what the backward call needs again */
+    void *ln1, *qkv, *o, *ln2, *a, *h;      /* bf16 [R,D] [R,3D] [R,D] [R,D] [R,M] [R,M]; a (mask*gelu') may be NULL when no
+                                               backward will follow */
+    float *mean1, *rstd1, *lse, *x1, *mean2, *rstd2, *x2;   /* f32 [R] [R] [B,H,T] [R,D] [R] [R] [R,D] */
+} b200vit_block_fwd_args;
+
+int b200vit_encoder_block_fwd(const b200vit_block_fwd_args* args, void* stream);
+
+typedef struct b200vit_block_bwd_args {
+    int struct_bytes;
+    int batch, tokens, heads, dim, mlp;
+    float mlp_p, attn_p;
+    unsigned long long key1_seed, key1_offset, key2_seed, key2_offset, attn_seed, attn_offset;
+    const float* g;                         /* f32 [R, D] gradient w.r.t. the block output */
+    int g16_ready;                          /* != 0: g16 already holds bf16(mask2 * g) and db2 its column sums (handed
+                                               over by the next block's call, see gx16_out below) */
+    int zero_accumulators;                  /* != 0: dw_in, dw_out, dw1, db1, dw2 are zero-filled first (the GEMM epilogues
+                                               add into them); 0 accumulates on top of their contents */
+    /* saved by the forward call */
+    const float *x, *mean1, *rstd1, *lse, *x1, *mean2, *rstd2;
+    const void *ln1, *qkv, *o, *ln2, *a, *h;
+    const float *ln1_w, *ln2_w;
+    const void *w_in16, *w_out16, *w1_16, *w2_16;
+    /* scratch, caller-allocated: bf16 g16 [R,D], da [R,M], dout [R,D], dqkv [R,3D], g1_16 [R,D]; f32 g1 [R,D], delta [B,H,T] */
+    void *g16, *da, *dout, *dqkv, *g1_16;
+    float *g1, *delta;
+    /* results */
+    float* gx;                              /* f32 [R, D] gradient w.r.t. the block input */
+    float *d_ln1_w, *d_ln1_b, *dw_in, *db_in, *dw_out, *db_out, *d_ln2_w, *d_ln2_b, *dw1, *db1, *dw2, *db2;
+    /* optional: also emit bf16(consumer mask * gx) and its column sums for the block in front (its g16 / db2) */
+    void* gx16_out;
+    float* dbn_out;
+    float consumer_p;
+    unsigned long long consumer_seed, consumer_offset;
+} b200vit_block_bwd_args;
+
+int b200vit_encoder_block_bwd(const b200vit_block_bwd_args* args, void* stream);
+
+/* Tensor-map cache statistics: the GEMM entry points keep the CUtensorMap of every (pointer, shape, leading
+ * dimension, box) they have encoded; torch's allocator hands the same addresses out step after step, so a training
+ * loop re-encodes next to nothing. Either pointer may be NULL. */
+void b200vit_tmap_cache_stats(long long* hits, long long* misses);
+
+/* ------------------------------------------------------------------------------------------------
  * Strict-precision ("fp32 mode") entry points. The reference computes in fp32 end to end (default-dtype nn modules,
  * models/vit.py:28-31, 83, 86-90, 115, 119-124, 216-222, run unchanged by going_modular/engine.py:50-66). In this
  * mode activations stay f32 between kernels and every contraction is still ONE b200vit_gemm launch on the tcgen05

@@ -44,6 +44,8 @@ _SIGNATURES = {
     "b200vit_l2norm_sq": [_p, _p, _i, _ll, _p, _i, _p, _p],
     "b200vit_l2norm_sq_noalloc": [_p, _p, _i, _ll, _p, _p],
     "b200vit_adam_step": [_p, _i, _ll, _p, _p, _i, _f, _f, _f, _i, _i, _p, _f, _f, _p],
+    "b200vit_encoder_block_fwd": [_p, _p],
+    "b200vit_encoder_block_bwd": [_p, _p],
     "b200vit_split_bf16x3": [_p, _ll, _ll, _i, _p, _ll, _ll, _i, _f, _ull, _ull, _i, _p],
     "b200vit_im2col_patches_f32": [_p, _p, _i, _i, _i, _i, _i, _p],
     "b200vit_gelu_f32_fwd": [_p, _p, _ll, _f, _ull, _ull, _p],
@@ -56,6 +58,36 @@ _SIGNATURES = {
 # GEMM enums (include/b200vit.h)
 OP_NT, OP_NN, OP_TN = 0, 1, 2
 EPI_BF16, EPI_BIAS_GELU, EPI_BIAS_RES, EPI_DGELU, EPI_ACCUM, EPI_F32, EPI_PATCH = range(7)
+
+
+class BlockFwdArgs(C.Structure):
+    """b200vit_block_fwd_args (include/b200vit.h)."""
+    _fields_ = ([("struct_bytes", _i), ("batch", _i), ("tokens", _i), ("heads", _i), ("dim", _i), ("mlp", _i),
+                 ("eps_msa", _f), ("eps_mlp", _f), ("mlp_p", _f), ("attn_p", _f),
+                 ("key1_seed", _ull), ("key1_offset", _ull), ("key2_seed", _ull), ("key2_offset", _ull),
+                 ("attn_seed", _ull), ("attn_offset", _ull)] +
+                [(n, _p) for n in ("x", "ln1_w", "ln1_b", "b_in", "b_out", "ln2_w", "ln2_b", "b1", "b2",
+                                   "w_in16", "w_out16", "w1_16", "w2_16",
+                                   "ln1", "qkv", "o", "ln2", "a", "h",
+                                   "mean1", "rstd1", "lse", "x1", "mean2", "rstd2", "x2")])
+
+
+class BlockBwdArgs(C.Structure):
+    """b200vit_block_bwd_args (include/b200vit.h)."""
+    _fields_ = ([("struct_bytes", _i), ("batch", _i), ("tokens", _i), ("heads", _i), ("dim", _i), ("mlp", _i),
+                 ("mlp_p", _f), ("attn_p", _f),
+                 ("key1_seed", _ull), ("key1_offset", _ull), ("key2_seed", _ull), ("key2_offset", _ull),
+                 ("attn_seed", _ull), ("attn_offset", _ull),
+                 ("g", _p), ("g16_ready", _i), ("zero_accumulators", _i)] +
+                [(n, _p) for n in ("x", "mean1", "rstd1", "lse", "x1", "mean2", "rstd2",
+                                   "ln1", "qkv", "o", "ln2", "a", "h",
+                                   "ln1_w", "ln2_w", "w_in16", "w_out16", "w1_16", "w2_16",
+                                   "g16", "da", "dout", "dqkv", "g1_16", "g1", "delta",
+                                   "gx",
+                                   "d_ln1_w", "d_ln1_b", "dw_in", "db_in", "dw_out", "db_out", "d_ln2_w", "d_ln2_b",
+                                   "dw1", "db1", "dw2", "db2",
+                                   "gx16_out", "dbn_out")] +
+                [("consumer_p", _f), ("consumer_seed", _ull), ("consumer_offset", _ull)])
 
 
 class AdamTensor(C.Structure):
@@ -103,12 +135,21 @@ def lib():
             fn = getattr(handle, name)
             fn.restype = _i
             fn.argtypes = argtypes
+        handle.b200vit_tmap_cache_stats.restype = None
+        handle.b200vit_tmap_cache_stats.argtypes = [C.POINTER(_ll), C.POINTER(_ll)]
         _lib = handle
     return _lib
 
 
 def exported_symbols():
-    return ["b200vit_abi_version", "b200vit_last_error", *_SIGNATURES.keys()]
+    return ["b200vit_abi_version", "b200vit_last_error", "b200vit_tmap_cache_stats", *_SIGNATURES.keys()]
+
+
+def tmap_cache_stats():
+    """(hits, misses) of the library's tensor-map cache."""
+    h, m = _ll(0), _ll(0)
+    lib().b200vit_tmap_cache_stats(C.byref(h), C.byref(m))
+    return h.value, m.value
 
 
 def check(rc: int, what: str) -> None:
@@ -121,7 +162,8 @@ def check(rc: int, what: str) -> None:
 
 # CUDA kernels launched by one successful call of each entry point (memsets are not counted).
 KERNELS_PER_CALL = {"b200vit_l2norm_sq": 2, "b200vit_l2norm_sq_noalloc": 2,
-                    "b200vit_head_bwd": 2, "b200vit_attention_f32_bwd": 2}
+                    "b200vit_head_bwd": 2, "b200vit_attention_f32_bwd": 2,
+                    "b200vit_encoder_block_fwd": 7, "b200vit_encoder_block_bwd": 12}
 launch_count = 0
 call_count = 0          # Python -> C transitions (one per entry-point call)
 want_device = None      # CUDA device ordinal of the tensors of the call being prepared (set by kernels.stream_ptr)

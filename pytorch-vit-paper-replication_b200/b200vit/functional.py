@@ -494,6 +494,114 @@ class MLPFn(torch.autograd.Function):
         return gx.view(shape), dgam, dbet, dw1, db1, dw2, db2, None, None, None, None, None, None
 
 
+# ---------------------------------------------------------------------------------------------------------
+# Encoder block through the composite C entry points: ONE Python -> C transition per block per direction
+# (b200vit_encoder_block_fwd / _bwd, csrc/block.cu) instead of one per kernel, and two allocations per direction
+# instead of one per buffer. B200VIT_COMPOSITE=0 falls back to driving the kernels one by one (the helpers above).
+# ---------------------------------------------------------------------------------------------------------
+_COMPOSITE = os.environ.get("B200VIT_COMPOSITE", "1") != "0"
+
+
+def _carve(like: torch.Tensor, dtype, sizes):
+    """One allocation cut into 1-D pieces of `sizes` elements, each starting on a 256-byte boundary."""
+    offs, total = [], 0
+    for n in sizes:
+        offs.append(total)
+        total += (int(n) + 127) // 128 * 128
+    flat = torch.empty(total, dtype=dtype, device=like.device)
+    return [flat[o:o + int(n)] for o, n in zip(offs, sizes)]
+
+
+def _block_forward_c(x2d, bn, t, heads, params, shadows, p, attn_p, eps_msa, eps_mlp, needs_bwd):
+    from . import _C
+    a_ln_w, a_ln_b, w_in, b_in, w_out, b_out, m_ln_w, m_ln_b, w1, b1, w2, b2 = params
+    w_in16, w_out16, w1_16, w2_16 = shadows
+    r, d = x2d.shape
+    m = w1_16.shape[0]
+    if d != heads * HEAD_DIM:
+        raise NotImplementedError(f"b200vit attention kernels need head_dim == 64 (embedding_dim {d}, heads {heads})")
+    dev = x2d.device
+    key1 = next_dropout_key(dev) if p > 0 else (0, 0)
+    key2 = next_dropout_key(dev) if p > 0 else (0, 0)
+    akey = next_dropout_key(dev) if attn_p > 0 else (0, 0)
+    ln1, qkv, o, ln2, a, h = _carve(x2d, torch.bfloat16, [r * d, 3 * r * d, r * d, r * d, r * m if needs_bwd else 0, r * m])
+    mean1, rstd1, lse, x1, mean2, rstd2 = _carve(x2d, torch.float32, [r, r, bn * heads * t, r * d, r, r])
+    x2 = torch.empty((r, d), dtype=torch.float32, device=dev)
+    A = _C.BlockFwdArgs()
+    A.struct_bytes = _C.C.sizeof(_C.BlockFwdArgs)
+    A.batch, A.tokens, A.heads, A.dim, A.mlp = bn, t, heads, d, m
+    A.eps_msa, A.eps_mlp, A.mlp_p, A.attn_p = eps_msa, eps_mlp, p, attn_p
+    A.key1_seed, A.key1_offset, A.key2_seed, A.key2_offset = key1[0], key1[1], key2[0], key2[1]
+    A.attn_seed, A.attn_offset = akey[0], akey[1]
+    A.x = x2d.data_ptr()
+    A.ln1_w, A.ln1_b, A.b_in, A.b_out = a_ln_w.data_ptr(), a_ln_b.data_ptr(), b_in.data_ptr(), b_out.data_ptr()
+    A.ln2_w, A.ln2_b, A.b1, A.b2 = m_ln_w.data_ptr(), m_ln_b.data_ptr(), b1.data_ptr(), b2.data_ptr()
+    A.w_in16, A.w_out16, A.w1_16, A.w2_16 = w_in16.data_ptr(), w_out16.data_ptr(), w1_16.data_ptr(), w2_16.data_ptr()
+    A.ln1, A.qkv, A.o, A.ln2, A.h = ln1.data_ptr(), qkv.data_ptr(), o.data_ptr(), ln2.data_ptr(), h.data_ptr()
+    A.a = a.data_ptr() if needs_bwd else None
+    A.mean1, A.rstd1, A.lse, A.x1 = mean1.data_ptr(), rstd1.data_ptr(), lse.data_ptr(), x1.data_ptr()
+    A.mean2, A.rstd2, A.x2 = mean2.data_ptr(), rstd2.data_ptr(), x2.data_ptr()
+    _C.call("b200vit_encoder_block_fwd", _C.C.byref(A), K.stream_ptr(dev))
+    saved = (x2d, mean1, rstd1, ln1, qkv, o, lse, x1, mean2, rstd2, ln2, a, h)
+    return x2, saved, (p, key1, key2), (attn_p, akey)
+
+
+def _block_backward_c(g2, saved, bn, t, heads, weights, drop, adrop, consumer_drop, grad_params):
+    from . import _C
+    x2d, mean1, rstd1, ln1, qkv, o, lse, x1, mean2, rstd2, ln2, a, h = saved
+    a_ln_w, m_ln_w, w_in16, w_out16, w1_16, w2_16 = weights
+    p, key1, key2 = drop
+    attn_p, akey = adrop
+    r, d = x2d.shape
+    m = w1_16.shape[0]
+    dev = x2d.device
+    side = _GRAD_SIDE.pop(g2.data_ptr(), None)
+    handed = side is not None and side[2] == p and side[3] == tuple(key2) and side[4] == g2._version and \
+        side[0].shape == (r, d)
+    g16, da, dout, dqkv, g1_16 = _carve(x2d, torch.bfloat16, [0 if handed else r * d, r * m, r * d, 3 * r * d, r * d])
+    g1, delta = _carve(x2d, torch.float32, [r * d, bn * heads * t])
+    gx = torch.empty((r, d), dtype=torch.float32, device=dev)
+    gp = grad_params
+    shapes = [(d,), (d,), (3 * d, d), (3 * d,), (d, d), (d,), (d,), (d,), (m, d), (m,), (d, m), (d,)]
+    if any(id(q) in _GRAD_DEST for q in gp):
+        grads = [grad_out(q, shp, x2d, zero=False) for q, shp in zip(gp, shapes)]
+    else:
+        flat = _carve(x2d, torch.float32, [math.prod(shp) for shp in shapes])
+        grads = [f.view(shp) for f, shp in zip(flat, shapes)]
+    if handed:
+        g16, grads[11] = side[0], side[1]       # bf16(mask2 * g) and the fc2 bias gradient came with g
+    gx16 = dbn = None
+    if consumer_drop is not None:
+        gx16 = torch.empty((r, d), dtype=torch.bfloat16, device=dev)
+        dbn = torch.empty((d,), dtype=torch.float32, device=dev)
+    A = _C.BlockBwdArgs()
+    A.struct_bytes = _C.C.sizeof(_C.BlockBwdArgs)
+    A.batch, A.tokens, A.heads, A.dim, A.mlp = bn, t, heads, d, m
+    A.mlp_p, A.attn_p = p, attn_p
+    A.key1_seed, A.key1_offset, A.key2_seed, A.key2_offset = key1[0], key1[1], key2[0], key2[1]
+    A.attn_seed, A.attn_offset = akey[0], akey[1]
+    A.g, A.g16_ready, A.zero_accumulators = g2.data_ptr(), int(handed), 1
+    A.x, A.mean1, A.rstd1, A.lse, A.x1 = x2d.data_ptr(), mean1.data_ptr(), rstd1.data_ptr(), lse.data_ptr(), x1.data_ptr()
+    A.mean2, A.rstd2 = mean2.data_ptr(), rstd2.data_ptr()
+    A.ln1, A.qkv, A.o, A.ln2, A.a, A.h = ln1.data_ptr(), qkv.data_ptr(), o.data_ptr(), ln2.data_ptr(), a.data_ptr(), h.data_ptr()
+    A.ln1_w, A.ln2_w = a_ln_w.data_ptr(), m_ln_w.data_ptr()
+    A.w_in16, A.w_out16, A.w1_16, A.w2_16 = w_in16.data_ptr(), w_out16.data_ptr(), w1_16.data_ptr(), w2_16.data_ptr()
+    A.g16, A.da, A.dout, A.dqkv, A.g1_16 = g16.data_ptr(), da.data_ptr(), dout.data_ptr(), dqkv.data_ptr(), g1_16.data_ptr()
+    A.g1, A.delta, A.gx = g1.data_ptr(), delta.data_ptr(), gx.data_ptr()
+    (A.d_ln1_w, A.d_ln1_b, A.dw_in, A.db_in, A.dw_out, A.db_out, A.d_ln2_w, A.d_ln2_b, A.dw1, A.db1, A.dw2,
+     A.db2) = [t_.data_ptr() for t_ in grads]
+    if consumer_drop is not None:
+        cp, ckey = consumer_drop
+        A.gx16_out, A.dbn_out, A.consumer_p = gx16.data_ptr(), dbn.data_ptr(), cp
+        A.consumer_seed, A.consumer_offset = ckey[0], ckey[1]
+    _C.call("b200vit_encoder_block_bwd", _C.C.byref(A), K.stream_ptr(dev))
+    if consumer_drop is not None:
+        if len(_GRAD_SIDE) > 64:        # never consumed (a graph that was not run to the end): do not grow
+            _GRAD_SIDE.clear()
+        _GRAD_SIDE[gx.data_ptr()] = (gx16, dbn, consumer_drop[0], consumer_drop[1], gx._version)
+    return gx, grads
+
+
 class EncoderBlockFn(torch.autograd.Function):
     """TransformerEncoderBlock.forward (models/vit.py:166-169) as one autograd node:
     x1 = msa(x) + x ; x2 = mlp(x1) + x1, with both residual adds fused into GEMM epilogues."""
@@ -510,6 +618,20 @@ class EncoderBlockFn(torch.autograd.Function):
         x2d = x.view(bn * t, d)
         needs_bwd = bool(grad_mode) and any(ctx.needs_input_grad)
         ctx.consumer_drop = _producer_dropout(x) if needs_bwd else None      # see "cross-block hand-over" above
+        ctx.composite = _COMPOSITE
+        if _COMPOSITE:
+            x2, saved, drop, adrop = _block_forward_c(
+                x2d, bn, t, heads, ctx.grad_params, (w_in16, w_out16, w1_16, w2_16), float(p) if training else 0.0,
+                float(attn_p) if training else 0.0, eps_msa, eps_mlp, needs_bwd)
+            if needs_bwd:
+                ctx.save_for_backward(a_ln_w, m_ln_w, w_in16, w_out16, w1_16, w2_16, *saved)
+            ctx.meta = (bn, t, heads, 0)
+            ctx.drop = drop
+            ctx.adrop = adrop
+            out = x2.view(bn, t, d)
+            if needs_bwd:
+                _note_block_output(out, drop[0], drop[2])
+            return out
         x1, s_msa, adrop = _msa_forward(x2d, bn, t, heads, a_ln_w, a_ln_b, w_in16, b_in, w_out16, b_out, x2d,
                                         float(attn_p) if training else 0.0, eps_msa)
         x2, s_mlp, drop = _mlp_forward(x1, m_ln_w, m_ln_b, w1_16, b1, w2_16, b2, float(p) if training else 0.0, x1,
@@ -528,9 +650,13 @@ class EncoderBlockFn(torch.autograd.Function):
     def backward(ctx, g):
         a_ln_w, m_ln_w, w_in16, w_out16, w1_16, w2_16, *rest = ctx.saved_tensors
         bn, t, heads, n_msa = ctx.meta
-        s_msa, s_mlp = tuple(rest[:n_msa]), tuple(rest[n_msa:])
         d = g.shape[-1]
         g2 = _f32c(g).view(bn * t, d)
+        if ctx.composite:
+            g0, gr = _block_backward_c(g2, tuple(rest), bn, t, heads, (a_ln_w, m_ln_w, w_in16, w_out16, w1_16, w2_16),
+                                       ctx.drop, ctx.adrop, ctx.consumer_drop, ctx.grad_params)
+            return (g0.view(bn, t, d), *gr, None, None, None, None, None, None, None, None, None, None, None)
+        s_msa, s_mlp = tuple(rest[:n_msa]), tuple(rest[n_msa:])
         m = w1_16.shape[0]
         gp = ctx.grad_params
         direct = any(id(q) in _GRAD_DEST for q in gp)

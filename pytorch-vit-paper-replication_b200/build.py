@@ -32,6 +32,7 @@ SOURCES = [
     "head_loss.cu",
     "optim.cu",
     "fp32_mode.cu",
+    "block.cu",
 ]
 
 NVCC_FLAGS = [

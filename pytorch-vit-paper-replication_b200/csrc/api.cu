@@ -17,6 +17,8 @@ int b200vit_gemm(int op, int epilogue, int M, int N, int K, const void* A, long 
                        offset, row_period, split_k, (cudaStream_t)stream);
 }
 
+void b200vit_tmap_cache_stats(long long* hits, long long* misses) { tmap_cache_stats(hits, misses); }
+
 int b200vit_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream) {
     return cast_f32_bf16_launch(src, (bf16*)dst, n, (cudaStream_t)stream);
 }

@@ -816,8 +816,8 @@ static PFN_cuTensorMapEncodeTiled get_encode_fn() {
 }
 
 // 2-D bf16 tensor map: inner dimension `inner` elements (contiguous), `outer` rows of `ld` elements.
-static int make_tmap_bf16(CUtensorMap* tm, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
-                          uint32_t box_inner, uint32_t box_outer) {
+static int encode_tmap_bf16(CUtensorMap* tm, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
+                            uint32_t box_inner, uint32_t box_outer) {
     PFN_cuTensorMapEncodeTiled enc = get_encode_fn();
     if (!enc) return set_error(-2, "cuTensorMapEncodeTiled not available (no CUDA driver?)");
     cuuint64_t dims[2] = {inner, outer};
@@ -830,6 +830,70 @@ static int make_tmap_bf16(CUtensorMap* tm, const void* base, uint64_t inner, uin
     if (r != CUDA_SUCCESS)
         return set_error(-3, "cuTensorMapEncodeTiled failed (%d): base=%p inner=%llu outer=%llu ld=%llu", (int)r,
                          base, (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)ld);
+    return 0;
+}
+
+// Cache of encoded tensor maps. A map depends only on (address, extents, pitch, box) -- not on the memory's contents
+// -- and torch's caching allocator returns the same addresses step after step, so the ~290 encodes of a training step
+// are almost all repeats. Direct-mapped, 1024 entries, one mutex (calls come from the Python main thread and from
+// autograd's backward thread).
+struct TmapKey {
+    const void* base; uint64_t inner, outer, ld; uint32_t box_inner, box_outer;
+    bool operator==(const TmapKey& o) const {
+        return base == o.base && inner == o.inner && outer == o.outer && ld == o.ld && box_inner == o.box_inner &&
+               box_outer == o.box_outer;
+    }
+};
+struct TmapEntry { TmapKey key; CUtensorMap map; bool valid; };
+constexpr int TMAP_CACHE_SIZE = 1024;
+static TmapEntry g_tmap_cache[TMAP_CACHE_SIZE];
+static std::mutex g_tmap_mu;
+static long long g_tmap_hits = 0, g_tmap_misses = 0;
+
+void tmap_cache_stats(long long* hits, long long* misses) {
+    std::lock_guard<std::mutex> lock(g_tmap_mu);
+    if (hits) *hits = g_tmap_hits;
+    if (misses) *misses = g_tmap_misses;
+}
+
+static int make_tmap_bf16(CUtensorMap* tm, const void* base, uint64_t inner, uint64_t outer, uint64_t ld,
+                          uint32_t box_inner, uint32_t box_outer) {
+    const TmapKey key{base, inner, outer, ld, box_inner, box_outer};
+    uint64_t h = (uint64_t)(uintptr_t)base * 0x9E3779B97F4A7C15ull;
+    h ^= (inner * 0xBF58476D1CE4E5B9ull) ^ (outer * 0x94D049BB133111EBull) ^ (ld << 17) ^ ((uint64_t)box_inner << 40) ^
+         ((uint64_t)box_outer << 50);
+    TmapEntry& e = g_tmap_cache[(h >> 20) & (TMAP_CACHE_SIZE - 1)];
+    {
+        std::lock_guard<std::mutex> lock(g_tmap_mu);
+        if (e.valid && e.key == key) {
+            *tm = e.map;
+            ++g_tmap_hits;
+            return 0;
+        }
+    }
+    const int rc = encode_tmap_bf16(tm, base, inner, outer, ld, box_inner, box_outer);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lock(g_tmap_mu);
+    e.key = key;
+    e.map = *tm;
+    e.valid = true;
+    ++g_tmap_misses;
+    return 0;
+}
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (kernel, device) instead of on every launch
+static int ensure_smem_attr(const void* kern, int bytes) {
+    struct Done { const void* kern; int dev; };
+    static Done done[256];
+    static int n_done = 0;
+    static std::mutex mu;
+    int dev = 0;
+    B200_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lock(mu);
+    for (int i = 0; i < n_done; ++i)
+        if (done[i].kern == kern && done[i].dev == dev) return 0;
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    if (n_done < 256) done[n_done++] = Done{kern, dev};
     return 0;
 }
 
@@ -950,14 +1014,14 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
         const bool heavy = (epi == EPI_BIAS_GELU);
         const int smem2 = heavy ? Cfg2<EPI_BIAS_GELU>::SMEM : Cfg2<EPI_BF16>::SMEM;
         const int threads2 = heavy ? Cfg2<EPI_BIAS_GELU>::THREADS : Cfg2<EPI_BF16>::THREADS;
-        B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+        { const int rc2 = ensure_smem_attr((const void*)kern, smem2); if (rc2) return rc2; }
         const int tiles_m2 = (M + 2 * BM - 1) / (2 * BM);
         const int total = tiles_m2 * p.tiles_n * p.splits;
         const int pairs = sm_count() / 2;
         const int grid = 2 * (total < pairs ? total : pairs);
         B200_CUDA(launch_kernel_pdl(kern, dim3(grid), dim3(threads2), (size_t)smem2, stream, tmA, tmB, p));   // cluster dims are compiled in
     } else {
-        B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM_BYTES));
+        { const int rc2 = ensure_smem_attr((const void*)kern, GEMM_SMEM_BYTES); if (rc2) return rc2; }
         const int total = p.tiles_m * p.tiles_n * p.splits;
         const int grid = total < sm_count() ? total : sm_count();
         B200_CUDA(launch_kernel_pdl(kern, dim3(grid), dim3(GEMM_THREADS), (size_t)GEMM_SMEM_BYTES, stream, tmA, tmB, p));

@@ -9,6 +9,8 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
                 long long ldaux, float drop_p, unsigned long long seed, unsigned long long offset, int row_period,
                 int splits, cudaStream_t stream);
 
+void tmap_cache_stats(long long* hits, long long* misses);
+
 int cast_f32_bf16_launch(const float* src, bf16* dst, long long n, cudaStream_t stream);
 int im2col_launch(const float* image, bf16* patches, int batch, int channels, int height, int width, int patch,
                   cudaStream_t stream);
