@@ -119,9 +119,11 @@ def make_gemm_runner(name, op, epi, M, N, Kd, dev):
 
 def gemm_traffic_per_launch(batch):
     """Count-weighted mean DRAM bytes (read + write) per GEMM launch of one step, from the committed ncu --set full
-    capture (profiles/r01_gemm_traffic.json, written by tools/summarize_ncu.py); None when the file is absent or
+    capture (profiles/r02_gemm_traffic.json, written by tools/summarize_ncu.py); None when the file is absent or
     was taken at another batch size."""
-    path = ROOT / "profiles" / "r01_gemm_traffic.json"
+    path = ROOT / "profiles" / "r02_gemm_traffic.json"
+    if not path.exists():
+        path = ROOT / "profiles" / "r01_gemm_traffic.json"
     if not path.exists():
         return None, None
     rec = json.loads(path.read_text())
@@ -140,8 +142,13 @@ def measure_step_kernels(run_steps, n_steps, batch, peaks, classes):
     """CUDA events around every C-ABI call of `n_steps` real training steps -> in-step time per kernel family, the
     GEMM roofline (FLOP-weighted over the step's 146 launches) and the other kernels against their own bounds."""
     from b200vit import _C
-    with _C.CallTimer() as tm:
-        run_steps(n_steps)
+    from b200vit import functional as F_
+    prev = F_.set_composite(False)      # one C call per kernel, so that every launch gets its own pair of events
+    try:
+        with _C.CallTimer() as tm:
+            run_steps(n_steps)
+    finally:
+        F_.set_composite(prev)
     times = tm.by_name()
     by = {k: sum(v) / n_steps for k, v in times.items()}          # ms per step
     calls = {k: len(v) / n_steps for k, v in times.items()}

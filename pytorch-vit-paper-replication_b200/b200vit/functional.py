@@ -502,6 +502,14 @@ class MLPFn(torch.autograd.Function):
 _COMPOSITE = os.environ.get("B200VIT_COMPOSITE", "1") != "0"
 
 
+def set_composite(flag: bool) -> bool:
+    """Drive encoder blocks through the composite C calls (True, default) or kernel by kernel (False: what the
+    per-kernel timers of bench.py need); returns the previous setting."""
+    global _COMPOSITE
+    prev, _COMPOSITE = _COMPOSITE, bool(flag)
+    return prev
+
+
 def _carve(like: torch.Tensor, dtype, sizes):
     """One allocation cut into 1-D pieces of `sizes` elements, each starting on a 256-byte boundary."""
     offs, total = [], 0
