@@ -631,6 +631,421 @@ attention_bwd_tc3_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
 }
 
 // =============================================================================================
+// Backward (T <= 256), single pass, probabilities through SHARED memory ("tc4"). Earlier versions built the probabilities twice per head (once with keys on
+// the TMEM lanes for dK/dV, once with queries on the lanes for dQ). Here they are built ONCE, keys on the
+// lanes: per 128-key tile t and 64-query chunk c
+//     S^T = K_t Q_c^T, dP^T = V_t dO_c^T  ->  P^T, dS^T (bf16, packed in place)  ->  dV_t += P^T dO_c, dK_t += dS^T Q_c
+// and dS^T is ALSO written to shared memory as bf16, one 128-byte row of 64 queries per key: that is exactly the
+// 128B-swizzled MN-major layout of an A operand with M = queries, so after two chunks (128 queries)
+//     dQ_m += dS[128 queries x keys of tile t] K_t
+// is one more UMMA chain, A from shared memory, accumulating over the key tiles in TMEM. All exponentials, the
+// dS math and the S / dP MMAs are done once instead of twice.
+// TMEM: [0,128) chunk accumulators of group 0 (S^T | dP^T), [128,256) of group 1, [256,320) dV_t, [320,384) dK_t,
+//       [384,448) dQ rows 0-127, [448,512) dQ rows 128-255.
+// Warps: 0 = TMA + MMA issue for group 1, 1 = MMA issue for group 0, 2-17 = two math groups (8 warps: thread <-> key row,
+// two warps per row splitting a chunk's 64 query columns), 18-19 = statistics; the groups alternate chunks.
+// Unlike its predecessor (which packed P^T / dS^T back into the chunk accumulators in tensor memory and fed them to
+// the dV / dK MMAs from there), this kernel writes P^T and dS^T as bf16 to SHARED memory -- one 128-byte row of 64
+// queries per key, 128B-swizzled: a K-major A operand for dV_t += P^T dO_c and dK_t += dS^T Q_c, and for dS^T at the
+// same time the MN-major A operand of dQ_m += dS K_t. The chunk accumulators are therefore free again as soon as the
+// math group has LOADED them (acc_free), not only after the dV / dK MMAs have consumed the packed values: the issuer
+// queues the group's next S^T / dP^T MMAs while the group is still computing exponentials, and the group finds its
+// next accumulators ready when it is done. (Before: MMA issue -> commit -> math -> commit -> MMA issue, strictly in
+// series per group; 53 % of all warp samples were mbarrier waits.)
+// =============================================================================================
+
+__global__ void __launch_bounds__(AT3_THREADS, 1)
+attention_bwd_tc4_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
+                         const bf16* __restrict__ out, const bf16* __restrict__ dout, const float* __restrict__ lse,
+                         bf16* __restrict__ dqkv, float* __restrict__ dbias, int num_heads_total, int T, int Nk, int H,
+                         float scale_log2, float scale) {
+    extern __shared__ uint8_t smem_raw[];
+    pdl_launch_dependents();
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t tile_bytes = (uint32_t)Nk * 128u;
+    const uint32_t tile_stride = (tile_bytes + 1023u) & ~1023u;
+    const uint32_t sQ = smem_base, sK = sQ + tile_stride, sV = sK + tile_stride, sdO = sV + tile_stride;
+    const uint32_t ds_base = smem_base + 4 * tile_stride + ATB_TAIL_PAD;     // 2 buffers x [2 query blocks][128 keys][128 B]
+    const uint32_t pt_base = ds_base + 2u * 32768u;                          // P^T of the chunk in flight, one 16 KB tile per group
+    const uint32_t stat_base = pt_base + 2u * 16384u;                        // 2 stages x (lse2 [Nk], delta*scale [Nk])
+    const uint32_t bar_base = stat_base + 2u * 2u * Nk * 4u;
+    const uint32_t full_bar = bar_base, head_empty = bar_base + 8u;
+    auto stat_bar = [&](int s) { return bar_base + 16u + 8u * s; };
+    auto s_ready = [&](int g) { return bar_base + 32u + 8u * g; };
+    auto p_ready = [&](int g) { return bar_base + 48u + 8u * g; };
+    auto ds_free = [&](int m) { return bar_base + 64u + 8u * m; };
+    const uint32_t kv_ready = bar_base + 80u, kv_free = bar_base + 88u, dq_ready = bar_base + 96u, dq_free = bar_base + 104u;
+    auto stat_free = [&](int s) { return bar_base + 112u + 8u * s; };
+    const uint32_t tmem_slot = bar_base + 128u;
+    const uint32_t kv_started = bar_base + 144u;
+    auto ds_half = [&](int m) { return bar_base + 152u + 8u * m; };
+    auto acc_free = [&](int g) { return bar_base + 168u + 8u * g; };     // group g has its chunk accumulators in registers
+    auto pt_free = [&](int g) { return bar_base + 184u + 8u * g; };      // the MMAs that read group g's P^T tile have retired
+    // optional fused in-projection bias gradient: per-CTA column sums of dQ | dK | dV, [3][H][64] fp32, flushed at the end
+    float* sBias = reinterpret_cast<float*>(smem_raw - smem_u32(smem_raw) + bar_base + 256u);
+    if (dbias != nullptr)
+        for (int k = threadIdx.x; k < 3 * H * 64; k += blockDim.x) sBias[k] = 0.f;
+    uint8_t* gen = smem_raw - smem_u32(smem_raw);
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen + tmem_slot);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nt = (T + ATC_BM - 1) / ATC_BM;           // key tiles
+    const int nc = (Nk + AT3_W - 1) / AT3_W;            // query chunks
+    const int nsteps = nt * nc;
+    const int nm = (nc + 1) / 2;                        // 128-query dQ tiles
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmQKV);
+        prefetch_tmap(&tmDO);
+        mbar_init(full_bar, 1);
+        mbar_init(head_empty, 2);       // "2": one commit per MMA-issuing warp
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(stat_bar(i), 2);
+            mbar_init(stat_free(i), 2);
+            mbar_init(s_ready(i), 1);
+            mbar_init(p_ready(i), 8);
+            mbar_init(ds_free(i), 2);       // one commit from the issuer of each of the tile's two chunks
+            mbar_init(ds_half(i), 8);
+            mbar_init(acc_free(i), 8);
+            mbar_init(pt_free(i), 1);
+        }
+        mbar_init(kv_ready, 2);
+        mbar_init(kv_free, 16);
+        mbar_init(kv_started, 1);
+        mbar_init(dq_ready, 2);
+        mbar_init(dq_free, 16);
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc<1>(tmem_slot, 512);
+        tmem_relinquish<1>();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot_ptr;
+    pdl_wait();       // the prologue above overlapped the previous kernel; global memory is touched from here on
+
+    if (warp < 2) {
+        // ===================== two MMA issuers: warp 1 serves math group 0, warp 0 serves group 1 and issues the TMA loads ======
+        // One thread can only issue ~1 small UMMA per 100 cycles, and a head is ~140 of them: with a single issuer that is
+        // half of the head's time. All 32 lanes run the loop (uniform operands); one elected lane issues each instruction.
+        // Cross-issuer ordering: tcgen05.commit only tracks the MMAs of its own thread, so barriers that mean "all MMAs of
+        // the tile / head are done" (kv_ready, dq_ready, head_empty, stat_free) take one commit from EACH issuer; the
+        // issuer of a tile's first chunk (accumulate = 0 into dV/dK) signals kv_started, the other one waits for it;
+        // the dQ MMA waits until the other group's half of the dS tile is in shared memory (ds_half).
+        const int my_g = warp == 1 ? 0 : 1;
+        const uint32_t idesc2 = make_idesc_bf16(ATC_BM, 64, 0, 1);      // A from TMEM, B MN-major
+        const uint32_t idesc3 = make_idesc_bf16(ATC_BM, 64, 1, 1);      // A (dS) and B (K) both MN-major
+        const uint32_t acc = tmem + my_g * 128;
+        uint32_t n_p = 0;
+        uint32_t S0 = 0;                // global step counter at the start of the head
+        int it = 0;
+        for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it, S0 += nsteps) {
+            if (warp == 0) {
+                const int b = w / H, h = w % H;
+                mbar_wait(head_empty, (it & 1) ^ 1u);
+                if (lane == 0) {
+                    mbar_arrive_expect_tx(full_bar, 4 * tile_bytes);
+                    tma_load_4d(sQ, &tmQKV, full_bar, 0, 0, h, b);
+                    tma_load_4d(sK, &tmQKV, full_bar, 0, 0, H + h, b);
+                    tma_load_4d(sV, &tmQKV, full_bar, 0, 0, 2 * H + h, b);
+                    tma_load_4d(sdO, &tmDO, full_bar, 0, 0, h, b);
+                }
+                __syncwarp();
+            }
+            mbar_wait(full_bar, it & 1);
+            tc_fence_after();
+            auto width = [&](int c) { return min(AT3_W, Nk - c * AT3_W); };
+            // (t, c) of step s is carried along instead of divided out: a runtime integer division is ~25 instructions with
+            // two dependent MUFU/I2F round trips, on the critical issue path of every step
+            auto issue_1 = [&](int t, int c) {  // S^T and dP^T of (my) step (t, c) into my group's chunk accumulators
+                const uint32_t xo = (uint32_t)t * (ATC_BM * 128), yo = (uint32_t)c * (AT3_W * 128);
+                const uint32_t idesc1 = make_idesc_bf16(ATC_BM, width(c), 0, 0);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    umma_bf16_ss_elect(acc, make_smem_desc_sw128(sK + xo + k * 32, 1024, 0),
+                                       make_smem_desc_sw128(sQ + yo + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
+                    umma_bf16_ss_elect(acc + 64, make_smem_desc_sw128(sV + xo + k * 32, 1024, 0),
+                                       make_smem_desc_sw128(sdO + yo + k * 32, 1024, 0), idesc1, k > 0 ? 1u : 0u);
+                }
+                umma_commit_elect(s_ready(my_g));
+            };
+            const int s_first = ((S0 & 1u) == (uint32_t)my_g) ? 0 : 1;
+            if (s_first < nsteps) issue_1(nc == 1 ? s_first : 0, nc == 1 ? 0 : s_first);
+            const uint32_t sPT = pt_base + (uint32_t)my_g * 16384u;
+            bool dq_waited = false;
+            for (int t = 0; t < nt; ++t) {
+                const uint32_t tile_idx = (uint32_t)it * nt + t;        // key tiles so far, all heads
+                bool first_mine = true;
+                for (int c = 0; c < nc; ++c) {
+                    const int s = t * nc + c;
+                    if (((S0 + s) & 1u) != (uint32_t)my_g) continue;
+                    // (1) as soon as the math group holds this step's S^T / dP^T in registers, queue its NEXT step's
+                    if (s + 2 < nsteps) {
+                        mbar_wait(acc_free(my_g), n_p & 1u);
+                        tc_fence_after();
+                        int t2 = t, c2 = c + 2;
+                        while (c2 >= nc) { c2 -= nc; ++t2; }
+                        issue_1(t2, c2);
+                    }
+                    // (2) P^T and dS^T of this step are in shared memory
+                    mbar_wait(p_ready(my_g), n_p & 1u);
+                    ++n_p;
+                    if (c == 0) mbar_wait(kv_free, (tile_idx & 1u) ^ 1u);       // the previous tile's dV / dK have been read out
+                    else if (first_mine) mbar_wait(kv_started, tile_idx & 1u);  // ... and this tile's were zero-initialised
+                    first_mine = false;
+                    tc_fence_after();
+                    const uint32_t yo = (uint32_t)c * (AT3_W * 128);
+                    const int m = c >> 1, blk = c & 1;
+                    const uint32_t sDS = ds_base + (uint32_t)m * 32768u + (uint32_t)blk * 16384u;
+                    const int ksteps = width(c) / 16;
+                    for (int k = 0; k < ksteps; ++k) {
+                        const uint32_t accf = (c > 0 || k > 0) ? 1u : 0u;
+                        // A: [128 keys][64 queries] rows of 128 B, K-major, 16 queries (32 B) per step; B: 16 query rows of dO / Q
+                        umma_bf16_ss_elect(tmem + 256, make_smem_desc_sw128(sPT + k * 32, 1024, 0),
+                                           make_smem_desc_sw128(sdO + yo + k * 2048, 1024, 0), idesc2, accf);
+                        umma_bf16_ss_elect(tmem + 320, make_smem_desc_sw128(sDS + k * 32, 1024, 0),
+                                           make_smem_desc_sw128(sQ + yo + k * 2048, 1024, 0), idesc2, accf);
+                    }
+                    umma_commit_elect(pt_free(my_g));                           // my P^T tile may be overwritten
+                    if (c == 0 && nc > 1 && lane == 0) mbar_arrive(kv_started);
+                    if (c + 2 >= nc) umma_commit_elect(kv_ready);               // my last chunk of this tile
+                    if ((c & 1) || c == nc - 1) {
+                        // both chunks of query tile m are in shared memory: dQ_m (+)= dS[m] K_t over this tile's keys
+                        if (c & 1) mbar_wait(ds_half(m), tile_idx & 1u);        // the other group's chunk 2m
+                        if (t == 0 && !dq_waited) {                             // the previous head's dQ has been read out
+                            mbar_wait(dq_free, (it & 1) ^ 1u);
+                            dq_waited = true;
+                        }
+                        tc_fence_after();
+                        const int keys = min(ATC_BM, Nk - t * ATC_BM);
+                        const uint32_t sA = ds_base + (uint32_t)m * 32768u, sB = sK + (uint32_t)t * (ATC_BM * 128);
+                        for (int k = 0; k < keys / 16; ++k)
+                            umma_bf16_ss_elect(tmem + 384 + 64 * m, make_smem_desc_sw128(sA + k * 2048, 1024, 16384),
+                                               make_smem_desc_sw128(sB + k * 2048, 1024, 0), idesc3, (t > 0 || k > 0) ? 1u : 0u);
+                    }
+                    // dS tile m: one arrival per chunk issuer (my dK MMAs, and the dQ MMAs if they were mine); a tile
+                    // with a single chunk gets both arrivals from its only issuer
+                    umma_commit_elect(ds_free(m));
+                    if (!(c & 1) && c == nc - 1) umma_commit_elect(ds_free(m));
+                }
+                if (first_mine) umma_commit_elect(kv_ready);    // no chunk of this tile was mine (single-chunk tiles)
+            }
+            umma_commit_elect(dq_ready);
+            umma_commit_elect(head_empty);
+            umma_commit_elect(stat_free(it & 1));
+        }
+        __syncwarp();
+    } else if (warp >= 18) {
+        // ===================== per-token statistics, one head ahead (two warps, half of the tokens each) ==========
+        const float LOG2E = 1.4426950408889634f;
+        const long long os = (long long)H * 64;
+        const int part = warp - 18;
+        const int half_rows = ((Nk / 2) + 15) & ~15;
+        const int t_begin = part == 0 ? 0 : half_rows, t_end = part == 0 ? half_rows : Nk;
+        int it = 0;
+        for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it) {
+            const int stage = it & 1;
+            const int b = w / H, h = w % H;
+            if (lane == 0) mbar_wait(stat_free(stage), ((it >> 1) & 1) ^ 1u);      // head it-2 no longer reads this stage
+            __syncwarp();
+            float* sLse2 = reinterpret_cast<float*>(gen + stat_base + (uint32_t)stage * 2u * Nk * 4u);
+            float* sDelta = sLse2 + Nk;
+            const bf16* gO = out + (long long)b * T * os + (long long)h * 64;
+            const bf16* gdO = dout + (long long)b * T * os + (long long)h * 64;
+            const float* L = lse + (long long)w * T;
+            for (int t = t_begin + lane; t < t_end; t += 32) {
+                float d = 0.f;
+                if (t < T) {
+                    const uint4* po = reinterpret_cast<const uint4*>(gO + (long long)t * os);
+                    const uint4* pd = reinterpret_cast<const uint4*>(gdO + (long long)t * os);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const uint4 a = __ldg(po + i), c = __ldg(pd + i);
+                        const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, cw[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const float2 fa = unpack_bf16(aw[k]), fc = unpack_bf16(cw[k]);
+                            d = fmaf(fa.x, fc.x, fmaf(fa.y, fc.y, d));
+                        }
+                    }
+                }
+                sDelta[t] = d * scale;
+                sLse2[t] = t < T ? L[t] * LOG2E : INFINITY;      // +inf: padded query columns get P = 0, dS = 0
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(stat_bar(stage));
+        }
+    } else {
+        // ===================== math + read-out groups =====================
+        const int sw = warp - 2;
+        const int g = sw >> 3;
+        const int half = (sw >> 2) & 1;
+        const int quarter = warp & 3;
+        const uint32_t lane_sel = (uint32_t)(quarter * 32) << 16;
+        const uint32_t acc = tmem + g * 128 + lane_sel;
+        const int r_in_tile = quarter * 32 + lane;
+        const long long rs = 3LL * H * 64;
+        const int cb = half * 32;
+        uint32_t n_s = 0, n_kv = 0;
+        uint32_t S0 = 0;
+        int it = 0;
+        for (int w = blockIdx.x; w < num_heads_total; w += gridDim.x, ++it, S0 += nsteps) {
+            const int b = w / H, h = w % H;
+            const float* sL = reinterpret_cast<const float*>(gen + stat_base + (uint32_t)(it & 1) * 2u * Nk * 4u);
+            const float* sD = sL + Nk;
+            mbar_wait(stat_bar(it & 1), (it >> 1) & 1);
+            // dV (group 0) or dK (group 1) of key tile t: this warp converts 32 of the 64 columns of its 32 rows
+            auto read_out_kv = [&](int t) {
+                mbar_wait(kv_ready, n_kv & 1u);
+                ++n_kv;
+                tc_fence_after();
+                uint32_t v[32];
+                tmem_ld_32x32(tmem + lane_sel + 256 + 64 * g + half * 32, v);
+                tmem_ld_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(kv_free);
+                const int row = t * ATC_BM + r_in_tile;
+                if (row < T) {
+                    bf16* dst = dqkv + ((long long)b * T + row) * rs + (long long)(g == 0 ? 2 * H + h : H + h) * 64 + half * 32;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        uint4 q;
+                        q.x = pack_bf16(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1]));
+                        q.y = pack_bf16(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3]));
+                        q.z = pack_bf16(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5]));
+                        q.w = pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7]));
+                        reinterpret_cast<uint4*>(dst)[i] = q;
+                    }
+                }
+                if (dbias != nullptr) {         // column sums over this warp's valid rows -> lane j holds column j
+                    float f[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) f[i] = row < T ? __uint_as_float(v[i]) : 0.f;
+                    const float cs = warp_colsum32(f, lane);
+                    atomicAdd(sBias + ((g == 0 ? 2 : 1) * H + h) * 64 + half * 32 + lane, cs);
+                }
+            };
+            int pending_tile = -1;          // tile whose dV/dK this group still has to read out
+            for (int s = 0, t = 0, c = 0; s < nsteps; ++s, c = (c + 1 == nc ? 0 : c + 1), t += (c == 0)) {
+                if (((S0 + s) & 1) != (uint32_t)g) {
+                    // the other group's step; if it is the last chunk of a tile, this group reads its half of the tile's
+                    // gradients after its own NEXT step (or at the end of the head)
+                    if (c == nc - 1) pending_tile = t;
+                    continue;
+                }
+                const int m = c >> 1, blk = c & 1;
+                const int W = min(AT3_W, Nk - c * AT3_W);
+                const int ce = min(cb + 32, W);
+                mbar_wait(s_ready(g), n_s & 1u);
+                if (n_s > 0) mbar_wait(pt_free(g), (n_s - 1) & 1u);     // the MMAs that read my group's previous P^T have retired
+                ++n_s;
+                if (t > 0 || it > 0) {      // the dK / dQ MMAs that read this dS buffer last (previous tile / head) have retired
+                    const uint32_t uses = (uint32_t)it * nt + t;       // uses of dS buffer m before this tile
+                    mbar_wait(ds_free(m), (uses - 1) & 1u);
+                }
+                tc_fence_after();
+                uint8_t* ds_row = gen + ds_base + (uint32_t)m * 32768u + (uint32_t)blk * 16384u + (uint32_t)r_in_tile * 128u;
+                uint8_t* pt_row = gen + pt_base + (uint32_t)g * 16384u + (uint32_t)r_in_tile * 128u;
+                for (int cc = cb; cc < ce; cc += 16) {
+                    uint32_t sv[16], dp[16];
+                    tmem_ld_32x16(acc + cc, sv);
+                    tmem_ld_32x16(acc + 64 + cc, dp);
+                    tmem_ld_wait();
+                    if (cc + 16 >= ce) {        // last load of this step: the accumulators may be overwritten
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(acc_free(g));
+                    }
+                    float p[16], ds[16];
+#pragma unroll
+                    for (int i4 = 0; i4 < 4; ++i4) {
+                        const float4 a = reinterpret_cast<const float4*>(sL + c * AT3_W + cc)[i4];
+                        const float4 d = reinterpret_cast<const float4*>(sD + c * AT3_W + cc)[i4];
+                        const float l2[4] = {a.x, a.y, a.z, a.w}, dl[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) {
+                            const int i = 4 * i4 + k;
+                            p[i] = fast_ex2(fmaf(__uint_as_float(sv[i]), scale_log2, -l2[k]));
+                            ds[i] = p[i] * fmaf(__uint_as_float(dp[i]), scale, -dl[k]);
+                        }
+                    }
+                    // 16 P values and 16 dS values: two 16-byte pieces each of this key's 128-byte rows
+                    const int j = cc >> 3;
+                    uint32_t pk[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) pk[i] = pack_bf16(p[2 * i], p[2 * i + 1]);
+                    *reinterpret_cast<uint4*>(pt_row + (((j) ^ (r_in_tile & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    *reinterpret_cast<uint4*>(pt_row + (((j + 1) ^ (r_in_tile & 7)) << 4)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) pk[i] = pack_bf16(ds[2 * i], ds[2 * i + 1]);
+                    *reinterpret_cast<uint4*>(ds_row + (((j) ^ (r_in_tile & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                    *reinterpret_cast<uint4*>(ds_row + (((j + 1) ^ (r_in_tile & 7)) << 4)) = make_uint4(pk[4], pk[5], pk[6], pk[7]);
+                }
+                if (cb >= ce) {                 // this warp has no columns in a narrow last chunk: it still takes part
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(acc_free(g));
+                }
+                fence_proxy_async_smem();       // the P^T / dS^T rows are read by the tensor core (async proxy)
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(p_ready(g));
+                    if (!(c & 1) && c + 1 < nc) mbar_arrive(ds_half(m));     // first half of dS tile m is in shared memory
+                }
+                if (pending_tile >= 0) {
+                    read_out_kv(pending_tile);
+                    pending_tile = -1;
+                }
+                if (c == nc - 1) read_out_kv(t);    // own last chunk of the tile: its MMAs follow immediately
+            }
+            if (pending_tile >= 0) read_out_kv(pending_tile);
+            // dQ: group m converts query rows [128 m, 128 m + 128)
+            mbar_wait(dq_ready, it & 1);
+            tc_fence_after();
+            uint32_t v[32];
+            if (g < nm) {
+                tmem_ld_32x32(tmem + lane_sel + 384 + 64 * g + half * 32, v);
+                tmem_ld_wait();
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(dq_free);
+            const int row = g * ATC_BM + r_in_tile;
+            if (g < nm && row < T) {
+                bf16* dst = dqkv + ((long long)b * T + row) * rs + (long long)h * 64 + half * 32;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    uint4 q;
+                    q.x = pack_bf16(__uint_as_float(v[8 * i]), __uint_as_float(v[8 * i + 1]));
+                    q.y = pack_bf16(__uint_as_float(v[8 * i + 2]), __uint_as_float(v[8 * i + 3]));
+                    q.z = pack_bf16(__uint_as_float(v[8 * i + 4]), __uint_as_float(v[8 * i + 5]));
+                    q.w = pack_bf16(__uint_as_float(v[8 * i + 6]), __uint_as_float(v[8 * i + 7]));
+                    reinterpret_cast<uint4*>(dst)[i] = q;
+                }
+            }
+            if (dbias != nullptr && g < nm) {
+                float f[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) f[i] = row < T ? __uint_as_float(v[i]) : 0.f;
+                const float cs = warp_colsum32(f, lane);
+                atomicAdd(sBias + h * 64 + half * 32 + lane, cs);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<1>(tmem, 512);
+    }
+    if (dbias != nullptr)
+        for (int k = threadIdx.x; k < 3 * H * 64; k += blockDim.x) atomicAdd(dbias + k, sBias[k]);
+}
+
+// =============================================================================================
 // Forward for long sequences (T > 256, e.g. the 577 tokens of 384x384 images): flash-style streaming over blocks of
 // 128 keys with an online softmax. A work item is (batch, head, pair of 128-query tiles); the pair shares one
 // stream of K/V blocks (4-deep TMA ring), tile g of the pair lives in TMEM slot g:
@@ -1363,11 +1778,22 @@ int attention_bwd_tc_launch(const bf16* qkv, const bf16* out, const bf16* dout, 
     // The in_proj_bias gradient is accumulated in shared memory ([3][heads][64] fp32) when that fits beside the tiles;
     // with very many heads it comes from a column-sum pass over dqkv afterwards.
     const size_t smem_bias = (size_t)3 * heads * 64 * 4;
-    const bool fused_bias = dbias != nullptr && smem_base + smem_bias <= 232448;
-    const size_t smem3 = smem_base + (fused_bias ? smem_bias : 0);
+    static int variant = -1;       // B200VIT_ATTN_BWD=3 forces the kernel that keeps P^T / dS^T in tensor memory (A/B runs)
+    if (variant < 0) {
+        const char* e = getenv("B200VIT_ATTN_BWD");
+        variant = e ? atoi(e) : 0;
+    }
+    // tc4 (P^T / dS^T through shared memory) needs two more 16 KB tiles: up to 208 tokens with the fused bias gradient,
+    // 224 without; longer sequences (<= 256) run tc3
+    const size_t smem4_base = smem_base + 2 * 16384;
+    const bool use4 = variant != 3 && smem4_base <= 232448;
+    const size_t sb = use4 ? smem4_base : smem_base;
+    const bool fused_bias = dbias != nullptr && sb + smem_bias <= 232448;
+    const size_t smem3 = sb + (fused_bias ? smem_bias : 0);
     if (fused_bias) B200_CUDA(cudaMemsetAsync(dbias, 0, sizeof(float) * 3 * heads * 64, stream));
-    B200_CUDA(cudaFuncSetAttribute(attention_bwd_tc3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
-    B200_CUDA(launch_kernel_pdl(attention_bwd_tc3_kernel, dim3(grid), dim3(AT3_THREADS), smem3, stream, tq, td, out, dout, lse,
+    auto kern = use4 ? attention_bwd_tc4_kernel : attention_bwd_tc3_kernel;
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem3));
+    B200_CUDA(launch_kernel_pdl(kern, dim3(grid), dim3(AT3_THREADS), smem3, stream, tq, td, out, dout, lse,
                                 dqkv, fused_bias ? dbias : (float*)nullptr, total, tokens, Nk, heads,
                                 scale * 1.4426950408889634f, scale));
     B200_LAUNCH_CHECK();
