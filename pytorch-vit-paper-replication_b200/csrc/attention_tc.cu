@@ -920,7 +920,10 @@ attention_bwd_tc4_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid
                         reinterpret_cast<uint4*>(dst)[i] = q;
                     }
                 }
-                if (dbias != nullptr) {         // column sums over this warp's valid rows -> lane j holds column j
+                // Column sums (in_proj_bias gradient) for dV only: the key-bias gradient is sum_keys dK =
+                // sum_q (sum_keys dS[q, :]) Q[q] = 0 exactly (a softmax is invariant to a shift of its logits), so that third
+                // of dbias keeps the launcher's zero fill instead of collecting rounding noise.
+                if (dbias != nullptr && g == 0) {       // column sums over this warp's valid rows -> lane j holds column j
                     float f[32];
 #pragma unroll
                     for (int i = 0; i < 32; ++i) f[i] = row < T ? __uint_as_float(v[i]) : 0.f;
