@@ -71,6 +71,8 @@ class DataParallel(nn.Module):
         # 37.05 ms/step overlapped, 37.39 ms at the end, 36.1 ms single-GPU. B200VIT_DP_OVERLAP=0/1 overrides.
         if overlap is None:
             overlap = os.environ.get("B200VIT_DP_OVERLAP", "1") == "1"
+        if "B200VIT_DP_BUCKET_MB" in os.environ:
+            bucket_mb = float(os.environ["B200VIT_DP_BUCKET_MB"])
         self.overlap = bool(overlap)
         if not dist.is_initialized():
             raise RuntimeError("DataParallel needs torch.distributed to be initialised (one process per GPU)")

@@ -294,19 +294,46 @@ class PatchEmbedFn(torch.autograd.Function):
 #             its incoming gradient up and falls back to the stand-alone kernel if anything does not match (another
 #             consumer, a hook that modified g, a different mask).
 # ---------------------------------------------------------------------------------------------------------
-_LAST_BLOCK_OUT = None      # (data_ptr of the block's output, p, (seed, offset))
-_GRAD_SIDE: dict = {}       # data_ptr of g -> (g16, colsum, p, (seed, offset), version of g)
+# Both records are PER THREAD (a forward runs on the caller's thread, a backward on one autograd thread: producer and
+# consumer of a record always share a thread), so models trained from different threads cannot see each other's. A side
+# entry keeps a strong reference to the gradient tensor it belongs to: while the entry exists the allocator cannot hand
+# that address to another tensor, so a stale entry can never be mistaken for a fresh one; entries left over by a backward
+# that was not run to the end are dropped at the next forward.
+import threading
+
+_TLS = threading.local()
+
+
+def _grad_side() -> dict:       # data_ptr of g -> (g16, colsum, p, (seed, offset), version of g, g itself)
+    d = getattr(_TLS, "grad_side", None)
+    if d is None:
+        d = _TLS.grad_side = {}
+    return d
+
+
+def _side_put(gx: torch.Tensor, gx16, dbn, p: float, key) -> None:
+    _grad_side()[gx.data_ptr()] = (gx16, dbn, p, key, gx._version, gx)
+
+
+def _side_take(g: torch.Tensor, p: float, key, shape):
+    side = _grad_side().pop(g.data_ptr(), None)
+    if side is not None and side[2] == p and side[3] == tuple(key) and side[4] == g._version and \
+            tuple(side[0].shape) == tuple(shape):
+        return side
+    return None
 
 
 def _note_block_output(y: torch.Tensor, p: float, key) -> None:
-    global _LAST_BLOCK_OUT
-    _LAST_BLOCK_OUT = (y.data_ptr(), float(p), tuple(key))
+    _TLS.last_block_out = (y.data_ptr(), float(p), tuple(key))
+    side = getattr(_TLS, "grad_side", None)
+    if side:                    # left over from a backward pass that never reached its consumer
+        side.clear()
 
 
 def _producer_dropout(x: torch.Tensor):
     """(p, key) of the encoder block that produced x, if x is that block's output tensor; else None."""
-    global _LAST_BLOCK_OUT
-    rec, _LAST_BLOCK_OUT = _LAST_BLOCK_OUT, None        # one consumer per record; a stale address must not match later
+    rec = getattr(_TLS, "last_block_out", None)
+    _TLS.last_block_out = None      # one consumer per record; a stale address must not match later
     if rec is not None and rec[0] == x.data_ptr():
         return rec[1], rec[2]
     return None
@@ -371,9 +398,7 @@ def _msa_backward(g, saved, bn, t, heads, ln_w, w_in16, w_out16, has_residual, g
         dbn = _empty((d,), torch.float32, x2d)
         K.layernorm_bwd(dln, None, x2d, d, mean, rstd, ln_w, g if has_residual else None, gx, d, gx16, dgamma, dbeta,
                         dbn, r, d, cp, ckey[0], ckey[1])
-        if len(_GRAD_SIDE) > 64:        # never consumed (a graph that was not run to the end): do not grow
-            _GRAD_SIDE.clear()
-        _GRAD_SIDE[gx.data_ptr()] = (gx16, dbn, cp, ckey, gx._version)
+        _side_put(gx, gx16, dbn, cp, ckey)
     return gx, (dgamma, dbeta, dw_in, db_in, dw_out, db_out)
 
 
@@ -406,9 +431,8 @@ def _mlp_backward(g, saved, drop, ln_w, w1_16, w2_16, has_residual, want_bf16_ou
     m = w1_16.shape[0]
     dev = x2d.device
     P = params if params is not None else (None,) * 6
-    side = _GRAD_SIDE.pop(g.data_ptr(), None)
-    if side is not None and side[2] == p and side[3] == tuple(key2) and side[4] == g._version and \
-            side[0].shape == (r, d):
+    side = _side_take(g, p, key2, (r, d))
+    if side is not None:
         g16, db2 = side[0], side[1]     # produced by the next block's LayerNorm backward together with g
     else:
         g16 = _empty((r, d), torch.bfloat16, x2d)
@@ -563,9 +587,8 @@ def _block_backward_c(g2, saved, bn, t, heads, weights, drop, adrop, consumer_dr
     r, d = x2d.shape
     m = w1_16.shape[0]
     dev = x2d.device
-    side = _GRAD_SIDE.pop(g2.data_ptr(), None)
-    handed = side is not None and side[2] == p and side[3] == tuple(key2) and side[4] == g2._version and \
-        side[0].shape == (r, d)
+    side = _side_take(g2, p, key2, (r, d))
+    handed = side is not None
     g16, da, dout, dqkv, g1_16 = _carve(x2d, torch.bfloat16, [0 if handed else r * d, r * m, r * d, 3 * r * d, r * d])
     g1, delta = _carve(x2d, torch.float32, [r * d, bn * heads * t])
     gx = torch.empty((r, d), dtype=torch.float32, device=dev)
@@ -604,9 +627,7 @@ def _block_backward_c(g2, saved, bn, t, heads, weights, drop, adrop, consumer_dr
         A.consumer_seed, A.consumer_offset = ckey[0], ckey[1]
     _C.call("b200vit_encoder_block_bwd", _C.C.byref(A), K.stream_ptr(dev))
     if consumer_drop is not None:
-        if len(_GRAD_SIDE) > 64:        # never consumed (a graph that was not run to the end): do not grow
-            _GRAD_SIDE.clear()
-        _GRAD_SIDE[gx.data_ptr()] = (gx16, dbn, consumer_drop[0], consumer_drop[1], gx._version)
+        _side_put(gx, gx16, dbn, consumer_drop[0], consumer_drop[1])
     return gx, grads
 
 
