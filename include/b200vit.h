@@ -29,6 +29,13 @@ int b200vit_abi_version(void);
 /* Message describing the last error raised on the calling thread. */
 const char* b200vit_last_error(void);
 
+/* Leave `sms` streaming multiprocessors out of the grids of every kernel launched from now on (0 restores the full
+ * device). The persistent kernels split their work statically over one CTA per SM, so a kernel of another stream that
+ * occupies some SMs (a gradient all-reduce overlapped with backward -- the reference has no counterpart, it is
+ * single-device, going_modular/engine.py:180) would stall whole CTAs; with a reserve it finds free SMs instead. Takes
+ * effect at launch time of each kernel; process-wide. */
+int b200vit_set_sm_reserve(int sms);
+
 /* ------------------------------------------------------------------------------------------------
  * Dense contractions on the tcgen05 tensor cores (bf16 operands, fp32 accumulation in tensor memory).
  *

@@ -44,6 +44,7 @@ _SIGNATURES = {
     "b200vit_l2norm_sq": [_p, _p, _i, _ll, _p, _i, _p, _p],
     "b200vit_l2norm_sq_noalloc": [_p, _p, _i, _ll, _p, _p],
     "b200vit_adam_step": [_p, _i, _ll, _p, _p, _i, _f, _f, _f, _i, _i, _p, _f, _f, _p],
+    "b200vit_set_sm_reserve": [_i],
     "b200vit_encoder_block_fwd": [_p, _p],
     "b200vit_encoder_block_bwd": [_p, _p],
     "b200vit_split_bf16x3": [_p, _ll, _ll, _i, _p, _ll, _ll, _i, _f, _ull, _ull, _i, _p],
@@ -143,6 +144,11 @@ def lib():
 
 def exported_symbols():
     return ["b200vit_abi_version", "b200vit_last_error", "b200vit_tmap_cache_stats", *_SIGNATURES.keys()]
+
+
+def set_sm_reserve(sms: int) -> None:
+    """Keep `sms` SMs out of every grid launched from now on (see include/b200vit.h)."""
+    check(lib().b200vit_set_sm_reserve(int(sms)), "b200vit_set_sm_reserve")
 
 
 def tmap_cache_stats():

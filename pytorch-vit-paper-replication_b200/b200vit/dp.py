@@ -82,6 +82,25 @@ class DataParallel(nn.Module):
         self.rank = dist.get_rank(process_group)
         self.grad_scale = 1.0 / self.world
         self.sync = True
+        # Optional: SMs kept free for the all-reduce kernels while backward runs, and the CTA budget NCCL gets for them
+        # (see _reserve()). OFF by default: measured on 2 B200 (256 images per GPU) 36.7-37.5 ms per step without it,
+        # 36.8-37.3 ms with 4 SMs reserved, 37.8-38.0 ms with 2 or 8 -- no gain beyond the box-to-box spread.
+        # B200VIT_DP_SM_RESERVE=k switches it on.
+        self.sm_reserve = int(os.environ.get("B200VIT_DP_SM_RESERVE", "0")) if self.overlap else 0
+        self._reserved = False
+        self.reduce_group = process_group
+        if self.sm_reserve > 0 and self.world > 1 and dist.get_backend(process_group) == "nccl":
+            try:
+                opts = dist.ProcessGroupNCCL.Options()
+                opts.config.max_ctas = self.sm_reserve
+                opts.config.min_ctas = 1
+                ranks = dist.get_process_group_ranks(process_group) if process_group is not None else None
+                self.reduce_group = dist.new_group(ranks=ranks, backend="nccl", pg_options=opts)
+            except Exception:       # no such option in this torch / NCCL: fall back to sharing SMs
+                self.sm_reserve = 0
+                self.reduce_group = process_group
+        else:
+            self.sm_reserve = 0
         F_.set_dropout_stream(self.rank)
         if broadcast:
             src = dist.get_global_rank(process_group, 0) if process_group else 0
@@ -128,9 +147,10 @@ class DataParallel(nn.Module):
         if not self._callback_queued:
             torch.autograd.Variable._execution_engine.queue_callback(self._finish)
             self._callback_queued = True
+            self._reserve(True)
         b.pending -= 1
         if b.pending == 0 and self.overlap:
-            b.work = dist.all_reduce(b.flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            b.work = dist.all_reduce(b.flat, op=dist.ReduceOp.SUM, group=self.reduce_group, async_op=True)
 
     def _finish(self) -> None:
         for b in self.buckets:
@@ -141,7 +161,8 @@ class DataParallel(nn.Module):
                     for j, p in enumerate(b.params):
                         if p.grad is None:
                             b.view(j).zero_()
-                b.work = dist.all_reduce(b.flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+                b.work = dist.all_reduce(b.flat, op=dist.ReduceOp.SUM, group=self.reduce_group, async_op=True)
+        self._reserve(False)
         for b in self.buckets:
             if b.work is not None:
                 b.work.wait()
@@ -151,6 +172,17 @@ class DataParallel(nn.Module):
                         p.grad._b200vit_reduced = p.grad._version
             b.pending = len(b.params)
         self._callback_queued = False
+
+    def _reserve(self, on: bool) -> None:
+        """The compute kernels are persistent grids of one CTA per SM with a static split of the work, so an all-reduce
+        kernel that takes SMs away can stall whole CTAs of the kernels it overlaps. With `sm_reserve` > 0 the library
+        launches its grids that many SMs short from the first gradient of a synchronised backward until its end, and
+        NCCL's communicator for the gradient buckets is capped at that many CTAs. (Did not pay on 2 GPUs -- see
+        __init__ -- and is therefore off unless asked for.)"""
+        if self.sm_reserve > 0 and on != self._reserved:
+            from . import _C
+            _C.set_sm_reserve(self.sm_reserve if on else 0)
+            self._reserved = on
 
     # -- API -----------------------------------------------------------------------------------------
     def forward(self, *args, **kwargs):

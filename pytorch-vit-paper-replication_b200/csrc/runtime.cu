@@ -18,6 +18,12 @@ int set_error(int code, const char* fmt, ...) {
     return code;
 }
 
+// SMs left to something else (a communication kernel running beside the compute stream). The persistent kernels of this
+// library size their grids to sm_count() CTAs with a STATIC split of the work: a CTA that finds its SM occupied starts
+// only when another CTA has finished its whole share, which doubles the kernel's run time -- so a concurrent kernel
+// must get SMs of its own, not borrow ours. See b200vit_set_sm_reserve().
+static int g_sm_reserve = 0;
+
 int sm_count() {
     static int cached[64] = {0};
     int dev = 0;
@@ -27,7 +33,9 @@ int sm_count() {
         if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
         cached[dev] = n;
     }
-    return cached[dev];
+    int n = cached[dev] - g_sm_reserve;
+    n &= ~1;                    // CTA pairs
+    return n < 2 ? 2 : n;
 }
 
 }  // namespace b200vit
@@ -35,6 +43,13 @@ int sm_count() {
 extern "C" {
 
 int b200vit_abi_version(void) { return 1; }
+
+int b200vit_set_sm_reserve(int sms) {
+    if (sms < 0 || sms > 64) return b200vit::set_error(-1, "set_sm_reserve: %d is outside [0, 64]", sms);
+    const int prev = b200vit::g_sm_reserve;
+    b200vit::g_sm_reserve = sms;
+    return prev >= 0 ? 0 : 0;
+}
 
 const char* b200vit_last_error(void) { return b200vit::last_error_buf(); }
 
