@@ -274,6 +274,32 @@ typedef struct b200vit_block_bwd_args {
 
 int b200vit_encoder_block_bwd(const b200vit_block_bwd_args* args, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * LayerNorm folded into the GEMMs around it, for a forward that no backward will follow (inference):
+ *     LN(x) W^T + b = rstd (x (gamma o W)^T - mean s) + c,   s[n] = sum_k gamma[k] W[n,k],   c[n] = sum_k beta[k] W[n,k] + b[n]
+ * so the projection that consumes a LayerNorm (in_proj models/vit.py:93-97, fc1 :129-130) reads the un-normalised
+ * residual stream as bf16 and applies the row statistics in its epilogue, provided the GEMM that produced the stream
+ * (patch embedding :53-66, out-projection / fc2 with their residual adds :167-168) also wrote that bf16 copy and each
+ * row's (sum, sum of squares). The separate nn.LayerNorm pass (:83, :115) disappears.
+ * b200vit_gemm_ln = b200vit_gemm (op 0 only, no split-K) with four more epilogues:
+ *   7 RES_STATS    epilogue 2, and also x16 bf16 [M, N] (ld ldx16) = C and rowstats[m][0..1] += (sum_n C, sum_n C^2)
+ *   8 PATCH_STATS  epilogue 6 with the same extra outputs (same row mapping as C)
+ *   9 LN_BF16      C bf16 = rstd[m] (acc - mean[m] ln_s[n]) + bias[n]   with mean / rstd from ln_stats[m] = (sum, sum of
+ *                  squares) over ln_dim values and ln_eps; A = the producer's x16, B = the folded weight, bias = c
+ *  10 LN_GELU      a = the same, then epilogue 1
+ * rowstats must be zero-filled before the producing call (b200vit_class_token_rows_ln STORES its rows' entries).
+ * b200vit_fold_ln_weight prepares B, s and c from the f32 master weight [rows, cols], gamma / beta [cols], bias [rows]. */
+int b200vit_gemm_ln(int op, int epilogue, int M, int N, int K, const void* A, long long lda, const void* B, long long ldb,
+                    void* C, long long ldc, void* C2, long long ldc2, const float* bias, const void* aux, long long ldaux,
+                    float dropout_p, unsigned long long seed, unsigned long long offset, int row_period, void* x16,
+                    long long ldx16, float* rowstats, const float* ln_stats, const float* ln_s, int ln_dim, float ln_eps,
+                    void* stream);
+int b200vit_fold_ln_weight(const float* w, const float* gamma, const float* beta, const float* bias, void* w16_bf16,
+                           float* s, float* c, int rows, int cols, void* stream);
+int b200vit_class_token_rows_ln(const float* class_token, const float* pos, float* x, void* x16_bf16, float* rowstats,
+                                int batch, int tokens, int dim, float dropout_p, unsigned long long seed,
+                                unsigned long long offset, void* stream);
+
 /* Tensor-map cache statistics: the GEMM entry points keep the CUtensorMap of every (pointer, shape, leading
  * dimension, box) they have encoded; torch's allocator hands the same addresses out step after step, so a training
  * loop re-encodes next to nothing. Either pointer may be NULL. */

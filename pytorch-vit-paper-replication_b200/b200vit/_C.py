@@ -45,6 +45,10 @@ _SIGNATURES = {
     "b200vit_l2norm_sq_noalloc": [_p, _p, _i, _ll, _p, _p],
     "b200vit_adam_step": [_p, _i, _ll, _p, _p, _i, _f, _f, _f, _i, _i, _p, _f, _f, _p],
     "b200vit_set_sm_reserve": [_i],
+    "b200vit_gemm_ln": [_i, _i, _i, _i, _i, _p, _ll, _p, _ll, _p, _ll, _p, _ll, _p, _p, _ll, _f, _ull, _ull, _i, _p, _ll, _p,
+                        _p, _p, _i, _f, _p],
+    "b200vit_fold_ln_weight": [_p, _p, _p, _p, _p, _p, _p, _i, _i, _p],
+    "b200vit_class_token_rows_ln": [_p, _p, _p, _p, _p, _i, _i, _i, _f, _ull, _ull, _p],
     "b200vit_encoder_block_fwd": [_p, _p],
     "b200vit_encoder_block_bwd": [_p, _p],
     "b200vit_split_bf16x3": [_p, _ll, _ll, _i, _p, _ll, _ll, _i, _f, _ull, _ull, _i, _p],
@@ -59,6 +63,7 @@ _SIGNATURES = {
 # GEMM enums (include/b200vit.h)
 OP_NT, OP_NN, OP_TN = 0, 1, 2
 EPI_BF16, EPI_BIAS_GELU, EPI_BIAS_RES, EPI_DGELU, EPI_ACCUM, EPI_F32, EPI_PATCH = range(7)
+EPI_RES_STATS, EPI_PATCH_STATS, EPI_LN_BF16, EPI_LN_GELU = 7, 8, 9, 10      # LayerNorm fold (b200vit_gemm_ln)
 
 
 class BlockFwdArgs(C.Structure):

@@ -97,6 +97,11 @@ def bf16_shadow(p: torch.Tensor) -> torch.Tensor:
     if not src.is_contiguous():
         src = src.contiguous()
     dst = e.tensor if (e is not None and e.tensor.shape == p.shape and e.tensor.device == p.device) else None
+    if dst is None:
+        # a shadow outlives the call that makes it: allocate it as an ordinary tensor even under torch.inference_mode()
+        # (an inference tensor could not be saved for backward by a later training step of the same model)
+        with torch.inference_mode(False):
+            dst = torch.empty(p.shape, dtype=torch.bfloat16, device=p.device)
     dst = K.cast_bf16(src, dst)
     key = id(p)
     _SHADOWS[key] = _Shadow(dst, ver, ptr, weakref.ref(p, lambda _r, k=key: _SHADOWS.pop(k, None)))
@@ -234,11 +239,145 @@ class _ZeroArena:
 
 
 # ---------------------------------------------------------------------------------------------------------
+# LayerNorm folded into the GEMMs around it -- forward passes that no backward will follow (no_grad / inference_mode).
+#   LN(x) W^T + b = rstd (x (gamma o W)^T - mean s) + c,   s[n] = sum_k gamma[k] W[n,k],   c[n] = sum_k beta[k] W[n,k] + b[n]
+# The GEMM that produces the residual stream (patch embedding, out-projection, fc2) also writes it as bf16 and adds up
+# each row's (sum, sum of squares); the projection that consumes LayerNorm(x) (in_proj, fc1) multiplies that bf16 copy
+# with the gamma-folded weight and applies mean / rstd in its epilogue (csrc/gemm_sm100.cu, epilogues 7-10). The 25
+# stand-alone LayerNorm launches of a ViT-B/16 forward disappear. The backward pass wants LN(x) itself as the operand of
+# the weight gradients, so training forwards keep the LayerNorm kernel. B200VIT_LN_FOLD=0 / set_ln_fold(False) disable it.
+# ---------------------------------------------------------------------------------------------------------
+_LN_FOLD = os.environ.get("B200VIT_LN_FOLD", "1") != "0"
+# Below this many token rows a forward is bound by the host (one C call per kernel on the folded path, one per block on
+# the composite path), not by the 25 LayerNorm launches the fold removes: measured 2.15 vs 1.93 ms at batch 32.
+LN_FOLD_MIN_ROWS = int(os.environ.get("B200VIT_LN_FOLD_MIN_ROWS", "12000"))
+
+
+def set_ln_fold(flag: bool) -> bool:
+    global _LN_FOLD
+    prev, _LN_FOLD = _LN_FOLD, bool(flag)
+    return prev
+
+
+_FOLDS: dict = {}      # id(weight) -> [folded bf16 weight, s, c, stamp, weakrefs of (w, gamma, beta, bias)]
+
+
+def _fold_stamp(w, gamma, beta, bias):
+    return (w._version, gamma._version, beta._version, bias._version, w.data_ptr(), gamma.data_ptr(), beta.data_ptr(),
+            bias.data_ptr())
+
+
+def folded_weight(w: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, bias: torch.Tensor):
+    """(bf16(gamma o W), s, c) for a Linear fed by LayerNorm(gamma, beta); re-made -- in place, so that a recorded
+    CUDA graph keeps seeing it -- when any of the four changed."""
+    key = id(w)
+    stamp = _fold_stamp(w, gamma, beta, bias)
+    e = _FOLDS.get(key)
+    if e is not None and e[4][0]() is w and e[0].device == w.device and e[0].shape == w.shape:
+        if e[3] != stamp:
+            K.fold_ln_weight(w.detach().contiguous(), gamma.detach(), beta.detach(), bias.detach(), e[0], e[1], e[2])
+            e[3] = stamp
+            e[4] = (e[4][0], weakref.ref(gamma), weakref.ref(beta), weakref.ref(bias))
+        return e[0], e[1], e[2]
+    n = w.shape[0]
+    w16 = torch.empty(w.shape, dtype=torch.bfloat16, device=w.device)
+    sv = torch.empty(n, dtype=torch.float32, device=w.device)
+    cv = torch.empty(n, dtype=torch.float32, device=w.device)
+    K.fold_ln_weight(w.detach().contiguous(), gamma.detach(), beta.detach(), bias.detach(), w16, sv, cv)
+    _FOLDS[key] = [w16, sv, cv, stamp, (weakref.ref(w, lambda _r, k=key: _FOLDS.pop(k, None)), weakref.ref(gamma),
+                                         weakref.ref(beta), weakref.ref(bias))]
+    return w16, sv, cv
+
+
+def refresh_folds() -> None:
+    """Re-make (in place) every folded weight whose sources changed since it was made: what a CUDA-graph replay of a
+    folded forward needs after an in-place parameter update (b200vit.inference.GraphedForward calls it)."""
+    for e in list(_FOLDS.values()):
+        w, gamma, beta, bias = (r() for r in e[4])
+        if w is None or gamma is None or beta is None or bias is None:
+            continue
+        if e[3] != _fold_stamp(w, gamma, beta, bias) and e[0].device == w.device:
+            folded_weight(w, gamma, beta, bias)
+
+
+def _ln_side() -> dict:     # data_ptr of a residual-stream tensor -> (its bf16 copy, row statistics, version, the tensor)
+    d = getattr(_TLS, "ln_side", None)
+    if d is None:
+        d = _TLS.ln_side = {}
+    return d
+
+
+def _version_of(x: torch.Tensor) -> int:
+    return -1 if x.is_inference() else x._version      # tensors made under inference_mode carry no version counter
+
+
+def _ln_side_put(x: torch.Tensor, x16: torch.Tensor, stats: torch.Tensor) -> None:
+    d = _ln_side()
+    d.clear()                   # one stream in flight per thread: whatever was not consumed is stale
+    d[x.data_ptr()] = (x16, stats, _version_of(x), x)
+
+
+def _ln_side_take(x: torch.Tensor):
+    e = _ln_side().pop(x.data_ptr(), None)
+    if e is not None and e[2] == _version_of(x) and e[3].shape == x.shape:
+        return e[0], e[1]
+    return None
+
+
+def _block_forward_folded(x, x2d, bn, t, heads, params, shadows, p, attn_p, eps_msa, eps_mlp):
+    """Encoder block forward with both LayerNorms folded (no activations are kept)."""
+    from . import _C
+    a_ln_w, a_ln_b, w_in, b_in, w_out, b_out, m_ln_w, m_ln_b, w1, b1, w2, b2 = params
+    w_in16, w_out16, w1_16, w2_16 = shadows
+    r, d = x2d.shape
+    m = w1_16.shape[0]
+    if d != heads * HEAD_DIM:
+        raise NotImplementedError(f"b200vit attention kernels need head_dim == 64 (embedding_dim {d}, heads {heads})")
+    dev = x2d.device
+    key1 = next_dropout_key(dev) if p > 0 else (0, 0)
+    key2 = next_dropout_key(dev) if p > 0 else (0, 0)
+    akey = next_dropout_key(dev) if attn_p > 0 else (0, 0)
+    side = _ln_side_take(x)
+    qkv = _empty((r, 3 * d), torch.bfloat16, x2d)
+    if side is not None:
+        x16, stats = side
+        wf, sv, cv = folded_weight(w_in, a_ln_w, a_ln_b, b_in)
+        K.gemm_ln(_C.EPI_LN_BF16, r, 3 * d, d, x16, d, wf, d, qkv, 3 * d, bias=cv, ln_stats=stats, ln_s=sv, ln_dim=d,
+                  ln_eps=eps_msa)
+    else:                       # the stream did not come from one of our producers: normalise it the ordinary way
+        ln = _empty((r, d), torch.bfloat16, x2d)
+        mean = _empty((r,), torch.float32, x2d)
+        rstd = _empty((r,), torch.float32, x2d)
+        K.layernorm_fwd(x2d, d, a_ln_w, a_ln_b, ln, None, mean, rstd, r, d, eps_msa)
+        K.gemm(K.OP_NT, K.EPI_BF16, r, 3 * d, d, ln, d, w_in16, d, qkv, 3 * d, bias=b_in)
+    o = _empty((r, d), torch.bfloat16, x2d)
+    lse = _empty((bn, heads, t), torch.float32, x2d)
+    K.attention_fwd(qkv, o, lse, bn, t, heads, HEAD_DIM, 1.0 / math.sqrt(HEAD_DIM), attn_p, akey[0], akey[1])
+    x1 = _empty((r, d), torch.float32, x2d)
+    x1_16 = _empty((r, d), torch.bfloat16, x2d)
+    st1 = _zeros((r, 2), x2d)
+    K.gemm_ln(_C.EPI_RES_STATS, r, d, d, o, d, w_out16, d, x1, d, bias=b_out, aux=x2d, ldaux=d, x16=x1_16, ldx16=d,
+              rowstats=st1)
+    wf, sv, cv = folded_weight(w1, m_ln_w, m_ln_b, b1)
+    h = _empty((r, m), torch.bfloat16, x2d)
+    K.gemm_ln(_C.EPI_LN_GELU, r, m, d, x1_16, d, wf, d, None, m, C2=h, ldc2=m, bias=cv, dropout_p=p, seed=key1[0],
+              offset=key1[1], ln_stats=st1, ln_s=sv, ln_dim=d, ln_eps=eps_mlp)
+    x2 = _empty((r, d), torch.float32, x2d)
+    x2_16 = _empty((r, d), torch.bfloat16, x2d)
+    st2 = _zeros((r, 2), x2d)
+    K.gemm_ln(_C.EPI_RES_STATS, r, d, m, h, m, w2_16, m, x2, d, bias=b2, aux=x1, ldaux=d, dropout_p=p, seed=key2[0],
+              offset=key2[1], x16=x2_16, ldx16=d, rowstats=st2)
+    out = x2.view(bn, t, d)
+    _ln_side_put(out, x2_16, st2)
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------
 # Patch embedding  (reference PatchEmbedding.forward, models/vit.py:45-67)
 # ---------------------------------------------------------------------------------------------------------
 class PatchEmbedFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, img, w, b, cls, pos, w16, patch: int, p_drop: float, training: bool):
+    def forward(ctx, img, w, b, cls, pos, w16, patch: int, p_drop: float, training: bool, grad_mode: bool = True):
         _require_cuda(img, "PatchEmbedding")
         # uint8 images are accepted as they are (converted to [0, 1] inside the im2col kernel: the reference's
         # ToDtype(float32, scale=True) on the device, a 4x smaller host->device copy); anything else becomes fp32
@@ -254,6 +393,17 @@ class PatchEmbedFn(torch.autograd.Function):
         x = _empty((bn, t, d), torch.float32, img)
         p = float(p_drop) if training else 0.0
         seed, off = next_dropout_key(img.device) if p > 0 else (0, 0)
+        if _LN_FOLD and bn * t >= LN_FOLD_MIN_ROWS and not (bool(grad_mode) and any(ctx.needs_input_grad)):
+            # no backward will follow: also emit what the first encoder block's folded LayerNorm needs
+            from . import _C
+            x16 = _empty((bn, t, d), torch.bfloat16, img)
+            stats = _zeros((bn * t, 2), img)
+            K.gemm_ln(_C.EPI_PATCH_STATS, bn * np_, d, kdim, patches, kdim, w16, kdim, x, d, bias=b, aux=pos, ldaux=d,
+                      dropout_p=p, seed=seed, offset=off, row_period=np_, x16=x16, ldx16=d, rowstats=stats)
+            K.class_token_rows_ln(cls, pos, x, x16, stats, bn, t, d, p, seed, off)
+            _ln_side_put(x, x16, stats)
+            ctx.meta = None
+            return x
         K.gemm(K.OP_NT, K.EPI_PATCH, bn * np_, d, kdim, patches, kdim, w16, kdim, x, d, bias=b, aux=pos, ldaux=d,
                dropout_p=p, seed=seed, offset=off, row_period=np_)
         K.class_token_rows(cls, pos, x, bn, t, d, p, seed, off)
@@ -276,7 +426,7 @@ class PatchEmbedFn(torch.autograd.Function):
         gw = _zeros((d, kdim), gx)
         K.gemm(K.OP_TN, K.EPI_ACCUM, d, kdim, rows, gy, d, patches, kdim, gw, kdim,
                split_k=0)
-        return None, gw.view(wshape), g_b, g_cls, g_pos, None, None, None, None
+        return None, gw.view(wshape), g_b, g_cls, g_pos, None, None, None, None, None
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -648,6 +798,9 @@ class EncoderBlockFn(torch.autograd.Function):
         needs_bwd = bool(grad_mode) and any(ctx.needs_input_grad)
         ctx.consumer_drop = _producer_dropout(x) if needs_bwd else None      # see "cross-block hand-over" above
         ctx.composite = _COMPOSITE
+        if _LN_FOLD and not needs_bwd and bn * t >= LN_FOLD_MIN_ROWS:
+            return _block_forward_folded(x, x2d, bn, t, heads, ctx.grad_params, (w_in16, w_out16, w1_16, w2_16),
+                                         float(p) if training else 0.0, float(attn_p) if training else 0.0, eps_msa, eps_mlp)
         if _COMPOSITE:
             x2, saved, drop, adrop = _block_forward_c(
                 x2d, bn, t, heads, ctx.grad_params, (w_in16, w_out16, w1_16, w2_16), float(p) if training else 0.0,

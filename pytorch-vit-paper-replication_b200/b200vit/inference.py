@@ -59,6 +59,7 @@ class GraphedForward:
             for p in self._params:
                 if F_.shadow_entry(p) is not None:
                     F_.bf16_shadow(p)
+            F_.refresh_folds()                      # ... and the LayerNorm-folded weights of the inference path
             self._versions = vers
 
     def _capture(self, x: torch.Tensor) -> _Entry:

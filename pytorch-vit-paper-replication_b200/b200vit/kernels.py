@@ -66,6 +66,27 @@ def gemm(op: int, epi: int, M: int, N: int, K: int, A: torch.Tensor, lda: int, B
             _ptr(aux), ldaux, float(dropout_p), int(seed), int(offset), row_period, split_k, stream_ptr(A.device))
 
 
+def gemm_ln(epi: int, M: int, N: int, K: int, A, lda, B, ldb, C, ldc, *, C2=None, ldc2=0, bias=None, aux=None, ldaux=0,
+            dropout_p=0.0, seed=0, offset=0, row_period=0, x16=None, ldx16=0, rowstats=None, ln_stats=None, ln_s=None,
+            ln_dim=0, ln_eps=0.0) -> None:
+    """b200vit_gemm_ln: forward (NT) GEMM with a LayerNorm-fold epilogue (_C.EPI_RES_STATS .. EPI_LN_GELU)."""
+    _C.call("b200vit_gemm_ln", OP_NT, epi, M, N, K, _ptr(A), lda, _ptr(B), ldb, _ptr(C), ldc, _ptr(C2), ldc2, _ptr(bias),
+            _ptr(aux), ldaux, float(dropout_p), int(seed), int(offset), row_period, _ptr(x16), ldx16, _ptr(rowstats),
+            _ptr(ln_stats), _ptr(ln_s), ln_dim, float(ln_eps), stream_ptr(A.device))
+
+
+def fold_ln_weight(w, gamma, beta, bias, w16, s, c) -> None:
+    rows = w.shape[0]
+    cols = w.numel() // rows
+    _C.call("b200vit_fold_ln_weight", _ptr(w), _ptr(gamma), _ptr(beta), _ptr(bias), _ptr(w16), _ptr(s), _ptr(c), rows, cols,
+            stream_ptr(w.device))
+
+
+def class_token_rows_ln(cls, pos, x, x16, rowstats, batch, tokens, dim, p, seed, offset) -> None:
+    _C.call("b200vit_class_token_rows_ln", _ptr(cls), _ptr(pos), _ptr(x), _ptr(x16), _ptr(rowstats), batch, tokens, dim,
+            float(p), int(seed), int(offset), stream_ptr(x.device))
+
+
 def cast_bf16(src: torch.Tensor, dst: Optional[torch.Tensor] = None) -> torch.Tensor:
     _chk(src, torch.float32, "cast_bf16 src")
     if dst is None:

@@ -67,7 +67,8 @@ class PatchEmbedding(nn.Module):
             return FP_.PatchEmbedF32Fn.apply(x, conv.weight, conv.bias, self.class_token, self.position_embedding,
                                              self.patch_size, self.dropout.p, self.training)
         return F_.PatchEmbedFn.apply(x, conv.weight, conv.bias, self.class_token, self.position_embedding,
-                                     F_.bf16_shadow(conv.weight), self.patch_size, self.dropout.p, self.training)
+                                     F_.bf16_shadow(conv.weight), self.patch_size, self.dropout.p, self.training,
+                                     torch.is_grad_enabled())
 
 
 class MultiHeadSelfAttentionBlock(nn.Module):

@@ -19,6 +19,28 @@ int b200vit_gemm(int op, int epilogue, int M, int N, int K, const void* A, long 
 
 void b200vit_tmap_cache_stats(long long* hits, long long* misses) { tmap_cache_stats(hits, misses); }
 
+int b200vit_gemm_ln(int op, int epilogue, int M, int N, int K, const void* A, long long lda, const void* B, long long ldb,
+                    void* C, long long ldc, void* C2, long long ldc2, const float* bias, const void* aux, long long ldaux,
+                    float dropout_p, unsigned long long seed, unsigned long long offset, int row_period, void* x16,
+                    long long ldx16, float* rowstats, const float* ln_stats, const float* ln_s, int ln_dim, float ln_eps,
+                    void* stream) {
+    GemmLnArgs ln{x16, ldx16, rowstats, ln_stats, ln_s, ln_dim, ln_eps};
+    return gemm_launch_ln(op, epilogue, M, N, K, A, lda, B, ldb, C, ldc, C2, ldc2, bias, aux, ldaux, dropout_p, seed, offset,
+                          row_period, 1, &ln, (cudaStream_t)stream);
+}
+
+int b200vit_fold_ln_weight(const float* w, const float* gamma, const float* beta, const float* bias, void* w16, float* s,
+                           float* c, int rows, int cols, void* stream) {
+    return fold_ln_weight_launch(w, gamma, beta, bias, (bf16*)w16, s, c, rows, cols, (cudaStream_t)stream);
+}
+
+int b200vit_class_token_rows_ln(const float* class_token, const float* pos, float* x, void* x16, float* rowstats, int batch,
+                                int tokens, int dim, float dropout_p, unsigned long long seed, unsigned long long offset,
+                                void* stream) {
+    return cls_rows_launch(class_token, pos, x, batch, tokens, dim, dropout_p, seed, offset, (cudaStream_t)stream, (bf16*)x16,
+                           rowstats);
+}
+
 int b200vit_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream) {
     return cast_f32_bf16_launch(src, (bf16*)dst, n, (cudaStream_t)stream);
 }

@@ -138,21 +138,75 @@ int im2col_launch(const float* image, bf16* patches, int batch, int channels, in
 // expand + cat + add + dropout with zero extra passes over the token tensor.
 // ---------------------------------------------------------------------------------------------
 __global__ void cls_rows_kernel(const float* __restrict__ cls, const float* __restrict__ pos, float* __restrict__ x,
-                                int B, int T, int D, DropoutParams drop) {
+                                int B, int T, int D, DropoutParams drop, bf16* __restrict__ x16, float* __restrict__ rowstats) {
+    __shared__ float red[2][8];
     const int b = blockIdx.x;
+    float sum = 0.f, sq = 0.f;
     for (int d = threadIdx.x; d < D; d += blockDim.x) {
         float v = cls[d] + pos[d];
         const unsigned long long e = (unsigned long long)b * T * D + d;
         if (drop.p > 0.f) v *= dropout_mult1(drop, e);
         x[(long long)b * T * D + d] = v;
+        if (x16) x16[(long long)b * T * D + d] = __float2bfloat16(v);
+        sum += v;
+        sq = fmaf(v, v, sq);
+    }
+    if (rowstats == nullptr) return;
+    // LayerNorm fold: this block owns the whole row, so its (sum, sum of squares) is stored, not accumulated
+    sum = warp_sum(sum);
+    sq = warp_sum(sq);
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = sum; red[1][threadIdx.x >> 5] = sq; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float a = 0.f, c = 0.f;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { a += red[0][w]; c += red[1][w]; }
+        rowstats[2LL * b * T] = a;
+        rowstats[2LL * b * T + 1] = c;
     }
 }
 
 int cls_rows_launch(const float* cls, const float* pos, float* x, int batch, int tokens, int dim, float drop_p,
-                    unsigned long long seed, unsigned long long offset, cudaStream_t stream) {
+                    unsigned long long seed, unsigned long long offset, cudaStream_t stream, bf16* x16, float* rowstats) {
     B200_CHECK_ARG(cls && pos && x, "class_token_rows: null pointer");
     B200_CHECK_ARG(batch > 0 && tokens > 0 && dim > 0, "class_token_rows: bad sizes");
-    cls_rows_kernel<<<batch, 256, 0, stream>>>(cls, pos, x, batch, tokens, dim, make_dropout(drop_p, seed, offset));
+    cls_rows_kernel<<<batch, 256, 0, stream>>>(cls, pos, x, batch, tokens, dim, make_dropout(drop_p, seed, offset), x16,
+                                              rowstats);
+    B200_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// LayerNorm fold, weight side (see gemm_sm100.cu): for a Linear that consumes LayerNorm(x) (models/vit.py:93-97 in_proj,
+// :129-130 fc1)   w16[n,k] = bf16(gamma[k] w[n,k]),  s[n] = sum_k w16[n,k]  (of the ROUNDED values: the tensor core
+// multiplies those),  c[n] = sum_k beta[k] w[n,k] + bias[n].   One warp per output row.
+// ---------------------------------------------------------------------------------------------
+__global__ void fold_ln_weight_kernel(const float* __restrict__ w, const float* __restrict__ gamma,
+                                      const float* __restrict__ beta, const float* __restrict__ bias,
+                                      bf16* __restrict__ w16, float* __restrict__ s, float* __restrict__ c, int rows, int cols) {
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    float ss = 0.f, cc = 0.f;
+    for (int k = lane; k < cols; k += 32) {
+        const float wv = w[(long long)row * cols + k];
+        const bf16 h = __float2bfloat16(wv * gamma[k]);
+        w16[(long long)row * cols + k] = h;
+        ss += __bfloat162float(h);
+        cc = fmaf(wv, beta[k], cc);
+    }
+    ss = warp_sum(ss);
+    cc = warp_sum(cc);
+    if (lane == 0) {
+        s[row] = ss;
+        c[row] = cc + (bias ? bias[row] : 0.f);
+    }
+}
+
+int fold_ln_weight_launch(const float* w, const float* gamma, const float* beta, const float* bias, bf16* w16, float* s,
+                          float* c, int rows, int cols, cudaStream_t stream) {
+    B200_CHECK_ARG(w && gamma && beta && w16 && s && c, "fold_ln_weight: null pointer");
+    B200_CHECK_ARG(rows > 0 && cols > 0, "fold_ln_weight: bad sizes");
+    fold_ln_weight_kernel<<<(rows + 7) / 8, 256, 0, stream>>>(w, gamma, beta, bias, w16, s, c, rows, cols);
     B200_LAUNCH_CHECK();
     return 0;
 }

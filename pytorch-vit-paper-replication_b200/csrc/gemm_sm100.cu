@@ -17,6 +17,7 @@
 // in memory.
 #include "common.cuh"
 #include "ptx_sm100.cuh"
+#include "launchers.h"
 
 #include <cudaTypedefs.h>
 #include <mutex>
@@ -56,8 +57,26 @@ enum GemmEpi {
     EPI_ACCUM = 4,      // C f32 += acc  (atomic; split-K weight gradients)
     EPI_F32 = 5,        // C f32 = acc (+ bias[n])
     EPI_PATCH = 6,      // C f32[m + m/P + 1, n] = dropout(acc + bias[n] + pos[m%P + 1, n])  (vit.py:53-66)
-    EPI_COUNT = 7
+    // LayerNorm folded into the GEMMs around it (forward without a backward to follow; see "LayerNorm fold" below):
+    EPI_RES_STATS = 7,  // EPI_BIAS_RES, and also x16 bf16 = C and rowstats[row] += (sum, sum of squares) of the C row
+    EPI_PATCH_STATS = 8,// EPI_PATCH with the same two extra outputs
+    EPI_LN_BF16 = 9,    // C bf16 = rstd[m] (acc - mean[m] s[n]) + bias[n]      (acc = bf16(x) . (gamma o W)^T)
+    EPI_LN_GELU = 10,   // a = the same ; then as EPI_BIAS_GELU
+    EPI_COUNT = 11
 };
+// LayerNorm fold. LN(x) W^T + b = rstd (x (gamma o W)^T - mean s) + c with s[n] = sum_k gamma[k] W[n,k] and
+// c[n] = sum_k beta[k] W[n,k] + b[n]: the GEMM that CONSUMES a LayerNorm output (QKV projection, fc1: models/vit.py:93-97,
+// 129-130) can read the un-normalised residual stream (as bf16) and apply the row statistics in its epilogue, if the
+// GEMM that PRODUCED the stream (patch embedding, out-projection, fc2) also wrote that bf16 copy and accumulated each
+// row's sum and sum of squares (three column tiles per row, fp32 atomics). The stand-alone LayerNorm kernel -- one
+// read of the f32 stream and one bf16 write per LayerNorm -- disappears. Only used when no backward will follow
+// (the weight gradients want LN(x) itself).
+__host__ __device__ constexpr bool is_res(int e) { return e == EPI_BIAS_RES || e == EPI_RES_STATS; }
+__host__ __device__ constexpr bool is_patch(int e) { return e == EPI_PATCH || e == EPI_PATCH_STATS; }
+__host__ __device__ constexpr bool is_gelu(int e) { return e == EPI_BIAS_GELU || e == EPI_LN_GELU; }
+__host__ __device__ constexpr bool is_bf16out(int e) { return e == EPI_BF16 || e == EPI_LN_BF16; }
+__host__ __device__ constexpr bool has_stats(int e) { return e == EPI_RES_STATS || e == EPI_PATCH_STATS; }
+__host__ __device__ constexpr bool is_lnin(int e) { return e == EPI_LN_BF16 || e == EPI_LN_GELU; }
 
 struct GemmParams {
     int M, N, K;
@@ -69,11 +88,17 @@ struct GemmParams {
     DropoutParams drop;
     int row_period;
     int vec_ok;   // leading dimensions / N allow 16-byte vector access
+    // LayerNorm fold (see the epilogue enum): producer side outputs / consumer side inputs
+    bf16* x16; long long ldx16;     // has_stats: bf16 copy of C (same row mapping as C)
+    float* rowstats;                // has_stats: [rows of C][2] += (sum, sum of squares); zero-filled by the caller
+    const float* ln_stats;          // is_lnin: [M][2] (sum, sum of squares) of the A rows before rounding to bf16
+    const float* ln_s;              // is_lnin: s[N]
+    float ln_inv_dim, ln_eps;       // is_lnin: 1 / (LayerNorm width), eps
 };
 // The ALU-heavy epilogue (GELU value + derivative, with dropout) runs 16 epilogue warps (4 per scheduler, 64 columns each)
 // and give up one pipeline stage for the extra staging tiles; the others run 8 warps and a 6-deep ring.
 template <int EPI> struct Cfg2 {
-    static constexpr int EW = (EPI == EPI_BIAS_GELU) ? 16 : 8;
+    static constexpr int EW = is_gelu(EPI) ? 16 : 8;
     static constexpr int STAGES = EW == 16 ? 5 : 6;
     static constexpr int THREADS = 128 + EW * 32;
     static constexpr int SMEM = STAGES * STAGE2_BYTES + EW * EPI_STAGE_BYTES + 1024 + 256;
@@ -102,14 +127,14 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
 
 // registers of prefetched auxiliary operand per 32x32 chunk, cooperative layout
 template <int EPI> struct AuxRegs {
-    static constexpr bool F32 = (EPI == EPI_BIAS_RES || EPI == EPI_PATCH);
+    static constexpr bool F32 = is_res(EPI) || is_patch(EPI);
     static constexpr bool B16 = (EPI == EPI_DGELU);
     static constexpr int N = F32 ? 32 : (B16 ? 16 : 1);
 };
 
 template <int EPI>
 __device__ __forceinline__ long long epi_out_row(const GemmParams& p, int r) {
-    return EPI == EPI_PATCH ? (long long)r + r / p.row_period + 1 : (long long)r;
+    return is_patch(EPI) ? (long long)r + r / p.row_period + 1 : (long long)r;
 }
 
 // Coalesced fetch of the aux tile of one chunk into registers (cooperative layout); zero where out of range.
@@ -119,7 +144,7 @@ __device__ __forceinline__ void aux_prefetch(const GemmParams& p, int lane, int 
     if (!(AuxRegs<EPI>::F32 || AuxRegs<EPI>::B16)) return;
     if (p.aux == nullptr || col0 >= p.N) return;
     const bool interior = p.vec_ok && col0 + 32 <= p.N && row_base + 32 <= p.M;
-    if (interior && EPI == EPI_BIAS_RES) {
+    if (interior && is_res(EPI)) {
         const float* ptr = reinterpret_cast<const float*>(p.aux) + (long long)(row_base + (lane >> 3)) * p.ldaux + col0 + (lane & 7) * 4;
 #pragma unroll
         for (int it = 0; it < 8; ++it) {
@@ -147,7 +172,7 @@ __device__ __forceinline__ void aux_prefetch(const GemmParams& p, int lane, int 
             const int gr = row_base + r, col = col0 + ch * 4;
             uint4 q = make_uint4(0, 0, 0, 0);
             if (gr < p.M && col < p.N) {
-                const long long ar = EPI == EPI_PATCH ? (long long)(gr % p.row_period + 1) : (long long)gr;
+                const long long ar = is_patch(EPI) ? (long long)(gr % p.row_period + 1) : (long long)gr;
                 const float* src = aux + ar * p.ldaux + col;
                 if (p.vec_ok && col + 4 <= p.N) {
                     q = *reinterpret_cast<const uint4*>(src);
@@ -183,9 +208,15 @@ __device__ __forceinline__ void aux_prefetch(const GemmParams& p, int lane, int 
     }
 }
 
+// Per-row state of the LayerNorm-fold epilogues: mean / rstd of this thread's A row (consumer side), running sum and
+// sum of squares of this thread's C row over the warp's chunks (producer side).
+struct LnRow {
+    float mu, rstd, sum, sq;
+};
+
 template <int EPI>
 __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg, int lane, int row_base, int col0,
-                                               float (&v)[32], const uint32_t (&auxr)[AuxRegs<EPI>::N]) {
+                                               float (&v)[32], const uint32_t (&auxr)[AuxRegs<EPI>::N], LnRow& ln) {
     if (col0 >= p.N) return;                       // warp-uniform
     const int row = row_base + lane;
     const bool fullw = p.vec_ok && col0 + 32 <= p.N;   // warp-uniform: every 16-byte piece of the chunk is valid
@@ -194,7 +225,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
     // warp-uniform: the whole 32x32 chunk is inside the matrix and 16-byte accesses are legal -> no per-piece checks
     const bool interior = fullw && row_base + 32 <= p.M;
     auto store_f32_tile = [&](float* base, long long ld) {
-        if (interior && EPI != EPI_PATCH) {
+        if (interior && !is_patch(EPI)) {
             float* ptr = base + (long long)(row_base + (lane >> 3)) * ld + col0 + (lane & 7) * 4;
 #pragma unroll
             for (int it = 0; it < 8; ++it)
@@ -252,7 +283,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
         }
     };
     auto store_b16_tile = [&](bf16* base, long long ld, uint32_t soff = 0) {
-        if (interior) {
+        if (interior && !is_patch(EPI)) {       // (the patch epilogues remap rows: class-token rows are skipped)
             bf16* ptr = base + (long long)(row_base + (lane >> 2)) * ld + col0 + (lane & 3) * 8;
 #pragma unroll
             for (int it = 0; it < 4; ++it)
@@ -322,8 +353,25 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
         }
     };
 
+    // ---- folded LayerNorm of the A operand: acc -> rstd (acc - mean s[n]); the "+ c[n]" is the bias below --------
+    if (is_lnin(EPI)) {
+        const float a = ln.rstd, b = -ln.mu * ln.rstd;
+        if (fullw) {
+            const float4* s4 = reinterpret_cast<const float4*>(p.ln_s + col0);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float4 q = __ldg(s4 + i);
+                v[4 * i] = fmaf(b, q.x, a * v[4 * i]); v[4 * i + 1] = fmaf(b, q.y, a * v[4 * i + 1]);
+                v[4 * i + 2] = fmaf(b, q.z, a * v[4 * i + 2]); v[4 * i + 3] = fmaf(b, q.w, a * v[4 * i + 3]);
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) if (col0 + i < p.N) v[i] = fmaf(b, __ldg(p.ln_s + col0 + i), a * v[i]);
+        }
+    }
+
     // ---- bias ---------------------------------------------------------------------------------------
-    if (EPI == EPI_BF16 || EPI == EPI_BIAS_GELU || EPI == EPI_BIAS_RES || EPI == EPI_F32 || EPI == EPI_PATCH) {
+    if (is_bf16out(EPI) || is_gelu(EPI) || is_res(EPI) || EPI == EPI_F32 || is_patch(EPI)) {
         if (p.bias != nullptr) {
             if (fullw) {
                 const float4* b4 = reinterpret_cast<const float4*>(p.bias + col0);
@@ -339,7 +387,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
         }
     }
 
-    if (EPI == EPI_BF16) {
+    if (is_bf16out(EPI)) {
         put_row_b16(v);
         __syncwarp();
         store_b16_tile(reinterpret_cast<bf16*>(p.C), p.ldc);
@@ -349,7 +397,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
         __syncwarp();
         store_f32_tile(reinterpret_cast<float*>(p.C), p.ldc);
         __syncwarp();
-    } else if (EPI == EPI_BIAS_GELU) {
+    } else if (is_gelu(EPI)) {
         // Per group of 8 columns: h = scale*gelu(a) (the hidden activation) and gd = scale*gelu'(a) (saved for the
         // backward epilogue), dropout keep-mask ANDed onto the packed bf16 pairs of both. A bf16 tile needs only
         // 2 KB, so both outputs are staged side by side in the warp's 4 KB tile and stored after one warp sync.
@@ -390,9 +438,9 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
         if (want_gd) store_b16_tile(reinterpret_cast<bf16*>(p.C), p.ldc);
         store_b16_tile(reinterpret_cast<bf16*>(p.C2), p.ldc2, 2048);
         __syncwarp();
-    } else if (EPI == EPI_BIAS_RES || EPI == EPI_PATCH) {
-        if (EPI == EPI_BIAS_RES) apply_dropout(v);
-        if (EPI == EPI_PATCH || p.aux != nullptr) {
+    } else if (is_res(EPI) || is_patch(EPI)) {
+        if (is_res(EPI)) apply_dropout(v);
+        if (is_patch(EPI) || p.aux != nullptr) {
             aux_to_stage();
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
@@ -402,11 +450,25 @@ __device__ __forceinline__ void epilogue_chunk(const GemmParams& p, uint32_t stg
             }
             __syncwarp();
         }
-        if (EPI == EPI_PATCH) apply_dropout(v);   // position embedding is added BEFORE dropout (vit.py:63-66)
+        if (is_patch(EPI)) apply_dropout(v);   // position embedding is added BEFORE dropout (vit.py:63-66)
+        if (has_stats(EPI)) {                  // row statistics of what is stored (fp32, before the bf16 rounding)
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const float x = (fullw || col0 + i < p.N) ? v[i] : 0.f;
+                ln.sum += x;
+                ln.sq = fmaf(x, x, ln.sq);
+            }
+        }
         put_row_f32(v);
         __syncwarp();
         store_f32_tile(reinterpret_cast<float*>(p.C), p.ldc);
         __syncwarp();
+        if (has_stats(EPI)) {                  // the same tile once more as bf16: the next GEMM's A operand
+            put_row_b16(v);
+            __syncwarp();
+            store_b16_tile(p.x16, p.ldx16);
+            __syncwarp();
+        }
     } else if (EPI == EPI_DGELU) {
         aux_to_stage();
 #pragma unroll
@@ -583,6 +645,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const int row_base = m0 + quarter * 32;
             const uint32_t stg = smem_stage + ew * EPI_STAGE_BYTES;
             uint32_t aux_next[AuxRegs<EPI>::N], aux_cur[AuxRegs<EPI>::N];
+            LnRow ln = {0.f, 1.f, 0.f, 0.f};
+            if (is_lnin(EPI)) {     // mean / rstd of this thread's row from the producer's (sum, sum of squares)
+                const int lr = row_base + lane;
+                if (lr < p.M) {
+                    const float2 st = __ldg(reinterpret_cast<const float2*>(p.ln_stats) + lr);
+                    ln.mu = st.x * p.ln_inv_dim;
+                    ln.rstd = rsqrtf(fmaxf(fmaf(-ln.mu, ln.mu, st.y * p.ln_inv_dim), 0.f) + p.ln_eps);
+                }
+            }
             aux_prefetch<EPI>(p, lane, row_base, n0 + half * 128, aux_next);   // before the accumulator is even ready
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
@@ -605,7 +676,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 float v[32];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-                epilogue_chunk<EPI>(p, stg, lane, row_base, n0 + col_in_tile, v, aux_cur);
+                epilogue_chunk<EPI>(p, stg, lane, row_base, n0 + col_in_tile, v, aux_cur, ln);
+            }
+            if (has_stats(EPI)) {   // this warp's share of its rows' sums (other column tiles add theirs)
+                const int lr = row_base + lane;
+                if (lr < p.M) {
+                    float* dst = p.rowstats + 2 * epi_out_row<EPI>(p, lr);
+                    atomicAdd(dst, ln.sum);
+                    atomicAdd(dst + 1, ln.sq);
+                }
             }
         }
     }
@@ -765,6 +844,15 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             const int row_base = m0 + quarter * 32;
             const uint32_t stg = smem_stage + ew * EPI_STAGE_BYTES;
             uint32_t aux_next[AuxRegs<EPI>::N], aux_cur[AuxRegs<EPI>::N];
+            LnRow ln = {0.f, 1.f, 0.f, 0.f};
+            if (is_lnin(EPI)) {     // mean / rstd of this thread's row from the producer's (sum, sum of squares)
+                const int lr = row_base + lane;
+                if (lr < p.M) {
+                    const float2 st = __ldg(reinterpret_cast<const float2*>(p.ln_stats) + lr);
+                    ln.mu = st.x * p.ln_inv_dim;
+                    ln.rstd = rsqrtf(fmaxf(fmaf(-ln.mu, ln.mu, st.y * p.ln_inv_dim), 0.f) + p.ln_eps);
+                }
+            }
             aux_prefetch<EPI>(p, lane, row_base, n0 + colgrp * (CHUNKS * 32), aux_next);   // before the accumulator is even ready
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
@@ -786,7 +874,15 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
                 float v[32];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-                epilogue_chunk<EPI>(p, stg, lane, row_base, n0 + col_in_tile, v, aux_cur);
+                epilogue_chunk<EPI>(p, stg, lane, row_base, n0 + col_in_tile, v, aux_cur, ln);
+            }
+            if (has_stats(EPI)) {   // this warp's share of its rows' sums (other column tiles add theirs)
+                const int lr = row_base + lane;
+                if (lr < p.M) {
+                    float* dst = p.rowstats + 2 * epi_out_row<EPI>(p, lr);
+                    atomicAdd(dst, ln.sum);
+                    atomicAdd(dst + 1, ln.sq);
+                }
             }
         }
     }
@@ -910,6 +1006,14 @@ static gemm_kernel_t pick_epi(int epi) {
         case EPI_F32: return gemm_tcgen05_kernel<A_MN, B_MN, EPI_F32>;
         case EPI_PATCH: return gemm_tcgen05_kernel<A_MN, B_MN, EPI_PATCH>;
     }
+    if constexpr (!A_MN && !B_MN) {     // the LayerNorm-fold epilogues exist for forward (NT) products only
+        switch (epi) {
+            case EPI_RES_STATS: return gemm_tcgen05_kernel<false, false, EPI_RES_STATS>;
+            case EPI_PATCH_STATS: return gemm_tcgen05_kernel<false, false, EPI_PATCH_STATS>;
+            case EPI_LN_BF16: return gemm_tcgen05_kernel<false, false, EPI_LN_BF16>;
+            case EPI_LN_GELU: return gemm_tcgen05_kernel<false, false, EPI_LN_GELU>;
+        }
+    }
     return nullptr;
 }
 
@@ -923,6 +1027,14 @@ static gemm_kernel_t pick_epi_2cta(int epi) {
         case EPI_ACCUM: return gemm_tcgen05_2cta_kernel<A_MN, B_MN, EPI_ACCUM>;
         case EPI_F32: return gemm_tcgen05_2cta_kernel<A_MN, B_MN, EPI_F32>;
         case EPI_PATCH: return gemm_tcgen05_2cta_kernel<A_MN, B_MN, EPI_PATCH>;
+    }
+    if constexpr (!A_MN && !B_MN) {
+        switch (epi) {
+            case EPI_RES_STATS: return gemm_tcgen05_2cta_kernel<false, false, EPI_RES_STATS>;
+            case EPI_PATCH_STATS: return gemm_tcgen05_2cta_kernel<false, false, EPI_PATCH_STATS>;
+            case EPI_LN_BF16: return gemm_tcgen05_2cta_kernel<false, false, EPI_LN_BF16>;
+            case EPI_LN_GELU: return gemm_tcgen05_2cta_kernel<false, false, EPI_LN_GELU>;
+        }
     }
     return nullptr;
 }
@@ -940,16 +1052,31 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
                 void* C, long long ldc, void* C2, long long ldc2, const float* bias, const void* aux,
                 long long ldaux, float drop_p, unsigned long long seed, unsigned long long offset, int row_period,
                 int splits, cudaStream_t stream) {
+    return gemm_launch_ln(op, epi, M, N, K, A, lda, B, ldb, C, ldc, C2, ldc2, bias, aux, ldaux, drop_p, seed, offset,
+                          row_period, splits, nullptr, stream);
+}
+
+int gemm_launch_ln(int op, int epi, int M, int N, int K, const void* A, long long lda, const void* B, long long ldb,
+                   void* C, long long ldc, void* C2, long long ldc2, const float* bias, const void* aux,
+                   long long ldaux, float drop_p, unsigned long long seed, unsigned long long offset, int row_period,
+                   int splits, const GemmLnArgs* ln, cudaStream_t stream) {
     B200_CHECK_ARG(op >= 0 && op <= 2, "gemm: bad op %d", op);
     B200_CHECK_ARG(epi >= 0 && epi < EPI_COUNT, "gemm: bad epilogue %d", epi);
     B200_CHECK_ARG(M > 0 && N > 0 && K > 0, "gemm: empty problem M=%d N=%d K=%d", M, N, K);
     // C may be NULL only for the GELU epilogue (forward without a backward to follow: mask*gelu' is not needed)
-    B200_CHECK_ARG(A && B && (C || epi == EPI_BIAS_GELU), "gemm: null operand");
+    B200_CHECK_ARG(A && B && (C || is_gelu(epi)), "gemm: null operand");
+    B200_CHECK_ARG(epi < EPI_RES_STATS || (ln != nullptr && op == OP_NT), "gemm: LayerNorm-fold epilogue %d needs its arguments and op NT", epi);
+    if (has_stats(epi))
+        B200_CHECK_ARG(ln->x16 && ln->rowstats && (ln->ldx16 % 8) == 0 && ((uintptr_t)ln->x16 % 16) == 0,
+                       "gemm: statistics epilogue needs x16 (16-byte aligned, ld %% 8 == 0) and rowstats");
+    if (is_lnin(epi))
+        B200_CHECK_ARG(ln->ln_stats && ln->ln_s && ln->ln_dim > 0 && ((uintptr_t)ln->ln_s % 16) == 0 &&
+                       ((uintptr_t)ln->ln_stats % 8) == 0, "gemm: folded-LayerNorm epilogue needs row statistics, s[] and the width");
     B200_CHECK_ARG((lda % 8) == 0 && (ldb % 8) == 0, "gemm: lda/ldb must be multiples of 8 elements (TMA 16B stride), got %lld %lld", lda, ldb);
     B200_CHECK_ARG(((uintptr_t)A % 16) == 0 && ((uintptr_t)B % 16) == 0, "gemm: A/B must be 16-byte aligned");
-    B200_CHECK_ARG(epi != EPI_BIAS_GELU || C2 != nullptr, "gemm: GELU epilogue needs the second output");
+    B200_CHECK_ARG(!is_gelu(epi) || C2 != nullptr, "gemm: GELU epilogue needs the second output");
     B200_CHECK_ARG(epi != EPI_DGELU || aux != nullptr, "gemm: dGELU epilogue needs the saved mask*gelu' operand");
-    B200_CHECK_ARG(epi != EPI_PATCH || (aux != nullptr && row_period > 0), "gemm: patch epilogue needs pos embedding and period");
+    B200_CHECK_ARG(!is_patch(epi) || (aux != nullptr && row_period > 0), "gemm: patch epilogue needs pos embedding and period");
     B200_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f, "gemm: dropout p must be in [0,1)");
 
     GemmParams p;
@@ -976,7 +1103,7 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
     p.bias = bias; p.aux = aux; p.ldaux = ldaux;
     p.drop = make_dropout(drop_p, seed, offset);
     p.row_period = row_period;
-    const bool out_f32 = (epi == EPI_BIAS_RES || epi == EPI_ACCUM || epi == EPI_F32 || epi == EPI_PATCH);
+    const bool out_f32 = (is_res(epi) || epi == EPI_ACCUM || epi == EPI_F32 || is_patch(epi));
     const int ovec = out_f32 ? 4 : 8;
     bool vec = (ldc % ovec) == 0 && ((uintptr_t)C % 16) == 0;
     if (C2) vec = vec && (ldc2 % 8) == 0 && ((uintptr_t)C2 % 16) == 0;
@@ -986,6 +1113,14 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
         vec = vec && (ldaux % avec) == 0 && ((uintptr_t)aux % 16) == 0;
     }
     p.vec_ok = vec ? 1 : 0;
+    p.x16 = nullptr; p.ldx16 = 0; p.rowstats = nullptr; p.ln_stats = nullptr; p.ln_s = nullptr;
+    p.ln_inv_dim = 0.f; p.ln_eps = 0.f;
+    if (ln != nullptr) {
+        p.x16 = (bf16*)ln->x16; p.ldx16 = ln->ldx16; p.rowstats = ln->rowstats;
+        p.ln_stats = ln->ln_stats; p.ln_s = ln->ln_s;
+        p.ln_inv_dim = ln->ln_dim > 0 ? 1.0f / (float)ln->ln_dim : 0.f;
+        p.ln_eps = ln->ln_eps;
+    }
 
     CUtensorMap tmA, tmB;
     int rc;
@@ -1011,7 +1146,7 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
     B200_CHECK_ARG(kern != nullptr, "gemm: no kernel for op %d epi %d", op, epi);
 
     if (two_cta) {
-        const bool heavy = (epi == EPI_BIAS_GELU);
+        const bool heavy = is_gelu(epi);
         const int smem2 = heavy ? Cfg2<EPI_BIAS_GELU>::SMEM : Cfg2<EPI_BF16>::SMEM;
         const int threads2 = heavy ? Cfg2<EPI_BIAS_GELU>::THREADS : Cfg2<EPI_BF16>::THREADS;
         { const int rc2 = ensure_smem_attr((const void*)kern, smem2); if (rc2) return rc2; }

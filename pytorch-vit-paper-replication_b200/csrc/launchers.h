@@ -11,13 +11,26 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
 
 void tmap_cache_stats(long long* hits, long long* misses);
 
+// LayerNorm fold (gemm_sm100.cu): extra operands of epilogues 7-10
+struct GemmLnArgs {
+    void* x16; long long ldx16; float* rowstats;            // producer side (epilogues 7, 8)
+    const float* ln_stats; const float* ln_s; int ln_dim; float ln_eps;   // consumer side (epilogues 9, 10)
+};
+int gemm_launch_ln(int op, int epi, int M, int N, int K, const void* A, long long lda, const void* B, long long ldb,
+                   void* C, long long ldc, void* C2, long long ldc2, const float* bias, const void* aux,
+                   long long ldaux, float drop_p, unsigned long long seed, unsigned long long offset, int row_period,
+                   int splits, const GemmLnArgs* ln, cudaStream_t stream);
+int fold_ln_weight_launch(const float* w, const float* gamma, const float* beta, const float* bias, bf16* w16, float* s,
+                          float* c, int rows, int cols, cudaStream_t stream);
+
 int cast_f32_bf16_launch(const float* src, bf16* dst, long long n, cudaStream_t stream);
 int im2col_launch(const float* image, bf16* patches, int batch, int channels, int height, int width, int patch,
                   cudaStream_t stream);
 int im2col_u8_launch(const uint8_t* image, bf16* patches, int batch, int channels, int height, int width, int patch,
                      cudaStream_t stream);
 int cls_rows_launch(const float* cls, const float* pos, float* x, int batch, int tokens, int dim, float drop_p,
-                    unsigned long long seed, unsigned long long offset, cudaStream_t stream);
+                    unsigned long long seed, unsigned long long offset, cudaStream_t stream, bf16* x16 = nullptr,
+                    float* rowstats = nullptr);
 int embed_grads_launch(const float* gx, float* g_cls, float* g_pos, float* g_bias, int batch, int tokens, int dim,
                        float drop_p, unsigned long long seed, unsigned long long offset, cudaStream_t stream);
 int patch_grad_rows_launch(const float* gx, bf16* gy, int batch, int tokens, int dim, float drop_p,
