@@ -36,6 +36,31 @@ const char* b200vit_last_error(void);
  * effect at launch time of each kernel; process-wide. */
 int b200vit_set_sm_reserve(int sms);
 
+/* Sum-all-reduce of one fp32 gradient bucket over peer memory (NVLink / NVSwitch), for data-parallel training of the
+ * hot path. No counterpart in the reference, which is single-device (going_modular/engine.py:180); called by
+ * b200vit/dp.py in place of ncclAllReduce. bufs[r] / flags[r] (r < world <= 8) are THIS process's mappings of rank r's
+ * bucket and of rank r's flag words (B200VIT_PEER_FLAG_WORDS zero-initialised 32-bit words, e.g. a torch
+ * symmetric-memory allocation; the library maps and allocates nothing). Every rank must call it once per bucket with the same count (a multiple of 4)
+ * and the same seq, and seq must grow by one from call to call on a given set of flag words, starting at 1. The kernel
+ * waits (bounded, ~20 s, then a launch error) until all ranks' buckets are complete, sums slice `rank` of all of them
+ * in rank order and writes the sum into every rank's bucket, and ends when all slices of the local bucket are final:
+ * stream order after it is enough to read the result. `ctas` CTAs of 64 threads without shared memory are launched (more
+ * than there are SMs is the intended use: all but the first CTA to land on an SM leave at once, the rest claim the
+ * work in chunks), so the kernel shares SMs with the backward kernels it overlaps. Plain 16-byte loads and stores. */
+#define B200VIT_PEER_FLAG_WORDS 320
+int b200vit_allreduce_peer_f32(void* const* bufs, void* const* flags, int world, int rank, long long count,
+                               unsigned seq, int ctas, void* stream);
+
+/* How the persistent 2-CTA tcgen05 GEMM hands out its (tile, split) work items. dynamic != 0 (the default; the
+ * environment variable B200VIT_GEMM_SCHED=static turns it off at load): a cluster works on its own index first and then
+ * claims further items from a counter in device memory (a file-scope array of the library; nothing is allocated), so
+ * a cluster whose SMs are held by another stream's kernel -- the gradient all-reduce that overlaps backward under
+ * b200vit.dp.DataParallel; the single-device reference, going_modular/engine.py:180, has no counterpart -- claims less
+ * instead of delaying the whole product by its static share. dynamic == 0: item i of cluster c is c + i * clusters.
+ * Results do not depend on the setting (each item is computed the same way whoever takes it; split-K sums through
+ * atomics in either case). Process-wide, takes effect at the next launch. */
+int b200vit_set_gemm_schedule(int dynamic);
+
 /* ------------------------------------------------------------------------------------------------
  * Dense contractions on the tcgen05 tensor cores (bf16 operands, fp32 accumulation in tensor memory).
  *

@@ -17,6 +17,7 @@ _i = C.c_int
 _ll = C.c_longlong
 _ull = C.c_ulonglong
 _f = C.c_float
+_u = C.c_uint
 
 # name -> argtypes (return type is always int unless noted)
 _SIGNATURES = {
@@ -45,6 +46,8 @@ _SIGNATURES = {
     "b200vit_l2norm_sq_noalloc": [_p, _p, _i, _ll, _p, _p],
     "b200vit_adam_step": [_p, _i, _ll, _p, _p, _i, _f, _f, _f, _i, _i, _p, _f, _f, _p],
     "b200vit_set_sm_reserve": [_i],
+    "b200vit_set_gemm_schedule": [_i],
+    "b200vit_allreduce_peer_f32": [_p, _p, _i, _i, _ll, _u, _i, _p],
     "b200vit_gemm_ln": [_i, _i, _i, _i, _i, _p, _ll, _p, _ll, _p, _ll, _p, _ll, _p, _p, _ll, _f, _ull, _ull, _i, _p, _ll, _p,
                         _p, _p, _i, _f, _p],
     "b200vit_fold_ln_weight": [_p, _p, _p, _p, _p, _p, _p, _i, _i, _p],
@@ -101,6 +104,7 @@ class AdamTensor(C.Structure):
     _fields_ = [("p", _p), ("g", _p), ("m", _p), ("v", _p), ("shadow", _p), ("n", _ll), ("group", _i), ("pad", _i)]
 
 
+PEER_FLAG_WORDS = 320       # B200VIT_PEER_FLAG_WORDS of include/b200vit.h
 _lib = None
 _override = None  # a test double may be installed with set_library(); never done by product code
 
@@ -154,6 +158,11 @@ def exported_symbols():
 def set_sm_reserve(sms: int) -> None:
     """Keep `sms` SMs out of every grid launched from now on (see include/b200vit.h)."""
     check(lib().b200vit_set_sm_reserve(int(sms)), "b200vit_set_sm_reserve")
+
+
+def set_gemm_schedule(dynamic: bool) -> None:
+    """Dynamic (claimed from a device counter) or static distribution of the 2-CTA GEMM's work items (include/b200vit.h)."""
+    check(lib().b200vit_set_gemm_schedule(1 if dynamic else 0), "b200vit_set_gemm_schedule")
 
 
 def tmap_cache_stats():

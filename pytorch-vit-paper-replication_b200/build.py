@@ -31,6 +31,7 @@ SOURCES = [
     "elementwise.cu",
     "head_loss.cu",
     "optim.cu",
+    "peer_reduce.cu",
     "fp32_mode.cu",
     "block.cu",
 ]

@@ -18,6 +18,7 @@ int b200vit_gemm(int op, int epilogue, int M, int N, int K, const void* A, long 
 }
 
 void b200vit_tmap_cache_stats(long long* hits, long long* misses) { tmap_cache_stats(hits, misses); }
+int b200vit_set_gemm_schedule(int dynamic) { set_gemm_dynamic(dynamic); return 0; }
 
 int b200vit_gemm_ln(int op, int epilogue, int M, int N, int K, const void* A, long long lda, const void* B, long long ldb,
                     void* C, long long ldc, void* C2, long long ldc2, const float* bias, const void* aux, long long ldaux,

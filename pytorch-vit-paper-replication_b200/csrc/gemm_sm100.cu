@@ -20,6 +20,7 @@
 #include "launchers.h"
 
 #include <cudaTypedefs.h>
+#include <atomic>
 #include <mutex>
 #include <stdlib.h>
 
@@ -88,6 +89,7 @@ struct GemmParams {
     DropoutParams drop;
     int row_period;
     int vec_ok;   // leading dimensions / N allow 16-byte vector access
+    int* sched_counter;   // 2-CTA kernel: work items beyond the first are claimed from this counter (NULL: static stride)
     // LayerNorm fold (see the epilogue enum): producer side outputs / consumer side inputs
     bf16* x16; long long ldx16;     // has_stats: bf16 copy of C (same row mapping as C)
     float* rowstats;                // has_stats: [rows of C][2] += (sum, sum of squares); zero-filled by the caller
@@ -721,11 +723,16 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * STAGES2 + 2 + s); }; // used in the leader CTA
     const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES2 + 4);
     uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+    // dynamic work distribution (see the scheduler warp below): a 2-deep ring of work indices per CTA
+    auto sfull_bar = [&](int s) { return bar_base + 8u * (2 * STAGES2 + 5 + s); };      // one per CTA
+    auto sempty_bar = [&](int s) { return bar_base + 8u * (2 * STAGES2 + 7 + s); };     // used in the leader CTA
+    auto sched_slot = [&](int s) { return bar_base + 8u * (2 * STAGES2 + 9) + 4u * s; };
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
     const bool leader = rank == 0;
+    const bool dyn = p.sched_counter != nullptr;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmA);
@@ -734,6 +741,8 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < STAGES2; ++s) { mbar_init(full_bar(s), 2); mbar_init(empty_bar(s), 1); }
         for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 2 * EW); }
+        // readers of a published work index: the TMA lane and the epilogue warps of both CTAs + the MMA warp
+        for (int s = 0; s < 2; ++s) { mbar_init(sfull_bar(s), 1); mbar_init(sempty_bar(s), 2 * (1 + EW) + 1); }
         fence_barrier_init();
     }
     if (warp == 2) {
@@ -759,11 +768,28 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         kb1 = (int)(((long long)(split + 1) * p.kblocks) / p.splits);
     };
 
+    // The it-th work item of this cluster. Static: cluster_id + it * num_clusters. Dynamic: whatever the scheduler
+    // warp published in ring slot it & 1 (-1 = no more work); every lane of the calling warp reads it, one arrives.
+    auto work_item = [&](int it, bool whole_warp) -> int {
+        if (!dyn) {
+            const int w = cluster_id + it * num_clusters;
+            return w < total_work ? w : -1;
+        }
+        const int s = it & 1;
+        mbar_wait_acq_cluster(sfull_bar(s), (uint32_t)(it >> 1) & 1u);
+        const int w = (int)ld_shared_u32(sched_slot(s));
+        if (whole_warp) __syncwarp();
+        // the slot may be overwritten once this arrive lands: make the arrive wait for the load above through a
+        // register dependency (w is never INT_MAX) instead of paying for a cluster-scope release in the epilogue warps
+        if (!whole_warp || lane == 0) mbar_arrive_cluster(sempty_bar(s) + (w == 0x7FFFFFFF ? 8u : 0u), 0);
+        return w;
+    };
+
     if (warp == 0) {
         // ===================== TMA producer (both CTAs) =====================
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
-            for (int w = cluster_id; w < total_work; w += num_clusters) {
+            for (int it = 0, w; (w = work_item(it, false)) >= 0; ++it) {
                 int m0, n0, kb0, kb1;
                 decode(w, m0, n0, kb0, kb1);
                 const int nb0 = n0 + (int)rank * (BN / 2);           // this CTA's half of the B tile
@@ -803,8 +829,7 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             constexpr uint32_t a_kstep = A_MN ? UMMA_K * 128 : UMMA_K * 2;
             constexpr uint32_t b_kstep = B_MN ? UMMA_K * 128 : UMMA_K * 2;
             int stage = 0; uint32_t phase = 0;
-            int iter = 0;
-            for (int w = cluster_id; w < total_work; w += num_clusters, ++iter) {
+            for (int iter = 0, w; (w = work_item(iter, true)) >= 0; ++iter) {
                 int m0, n0, kb0, kb1;
                 decode(w, m0, n0, kb0, kb1);
                 const int acc = iter & 1;
@@ -830,13 +855,41 @@ gemm_tcgen05_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             }
         }
         __syncwarp();
+    } else if (warp == 3) {
+        // ===================== Work scheduler (leader CTA, dynamic distribution only) =====================
+        // The first item of a cluster is its own index; every further one is claimed from a global counter, so a
+        // cluster that starts late (its SMs were held by another stream's kernel, e.g. a gradient all-reduce) simply
+        // claims less instead of holding the whole GEMM back by its share. The index is written into both CTAs' rings
+        // and signalled with cluster-scope release arrives. Every cluster makes exactly one claim that fails; the
+        // one that sees the last of them puts the counter back to zero for the next launch.
+        if (dyn && leader && lane == 0) {
+            const int claims_ok = total_work > num_clusters ? total_work - num_clusters : 0;
+            auto claim = [&]() -> int {
+                const int v = atomicAdd(p.sched_counter, 1);
+                if (v == claims_ok + num_clusters - 1) atomicExch(p.sched_counter, 0);
+                return num_clusters + v;
+            };
+            int w = cluster_id;
+            if (w >= total_work) claim();            // (keeps the count of failing claims at one per cluster)
+            for (int it = 0;; ++it) {
+                if (w >= total_work) w = -1;
+                const int s = it & 1;
+                mbar_wait(sempty_bar(s), ((uint32_t)(it >> 1) & 1u) ^ 1u);
+                st_shared_cluster_u32(sched_slot(s), 0, (uint32_t)w);
+                st_shared_cluster_u32(sched_slot(s), 1, (uint32_t)w);
+                mbar_arrive_cluster_release(sfull_bar(s), 0);
+                mbar_arrive_cluster_release(sfull_bar(s), 1);
+                if (w < 0) break;
+                w = claim();
+            }
+        }
+        __syncwarp();
     } else if (warp >= 4) {
         // ===================== Epilogue (both CTAs, own 128 rows) =====================
         const int ew = warp - 4;
         const int quarter = warp & 3;
         const int colgrp = ew >> 2;          // which (256 / (EW/4))-column slice of the tile
-        int iter = 0;
-        for (int w = cluster_id; w < total_work; w += num_clusters, ++iter) {
+        for (int iter = 0, w; (w = work_item(iter, true)) >= 0; ++iter) {
             int m0, n0, kb0, kb1;
             decode(w, m0, n0, kb0, kb1);
             const int acc = iter & 1;
@@ -995,6 +1048,40 @@ static int ensure_smem_attr(const void* kern, int bytes) {
 
 typedef void (*gemm_kernel_t)(const CUtensorMap, const CUtensorMap, const GemmParams);
 
+// Work counters of the dynamically scheduled 2-CTA GEMM: zero at load, put back to zero by every launch that used one.
+// Launches take them in rotation, so kernels of different streams that overlap do not share one.
+constexpr int SCHED_COUNTERS = 64;
+static __device__ int g_sched_counters[SCHED_COUNTERS];
+static std::atomic<int> g_gemm_dynamic{-1};      // -1: read B200VIT_GEMM_SCHED on first use
+static std::atomic<unsigned> g_sched_next{0};
+
+void set_gemm_dynamic(int on) { g_gemm_dynamic.store(on ? 1 : 0); }
+
+static bool gemm_dynamic() {
+    int v = g_gemm_dynamic.load();
+    if (v < 0) {
+        const char* e = getenv("B200VIT_GEMM_SCHED");
+        v = (e && (e[0] == 's' || e[0] == '0')) ? 0 : 1;      // "static" / "0" turn it off
+        g_gemm_dynamic.store(v);
+    }
+    return v != 0;
+}
+
+static int next_sched_counter(int** out) {
+    constexpr int MAX_DEV = 64;
+    static int* base[MAX_DEV] = {};
+    static std::mutex mu;
+    int dev = 0;
+    B200_CUDA(cudaGetDevice(&dev));
+    B200_CHECK_ARG(dev >= 0 && dev < MAX_DEV, "gemm: device index %d out of range", dev);
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!base[dev]) B200_CUDA(cudaGetSymbolAddress((void**)&base[dev], g_sched_counters));
+        *out = base[dev] + (g_sched_next.fetch_add(1) % SCHED_COUNTERS);
+    }
+    return 0;
+}
+
 template <bool A_MN, bool B_MN>
 static gemm_kernel_t pick_epi(int epi) {
     switch (epi) {
@@ -1113,6 +1200,7 @@ int gemm_launch_ln(int op, int epi, int M, int N, int K, const void* A, long lon
         vec = vec && (ldaux % avec) == 0 && ((uintptr_t)aux % 16) == 0;
     }
     p.vec_ok = vec ? 1 : 0;
+    p.sched_counter = nullptr;
     p.x16 = nullptr; p.ldx16 = 0; p.rowstats = nullptr; p.ln_stats = nullptr; p.ln_s = nullptr;
     p.ln_inv_dim = 0.f; p.ln_eps = 0.f;
     if (ln != nullptr) {
@@ -1154,6 +1242,8 @@ int gemm_launch_ln(int op, int epi, int M, int N, int K, const void* A, long lon
         const int total = tiles_m2 * p.tiles_n * p.splits;
         const int pairs = sm_count() / 2;
         const int grid = 2 * (total < pairs ? total : pairs);
+        p.sched_counter = nullptr;
+        if (gemm_dynamic() && total > pairs) { const int rc3 = next_sched_counter(&p.sched_counter); if (rc3) return rc3; }
         B200_CUDA(launch_kernel_pdl(kern, dim3(grid), dim3(threads2), (size_t)smem2, stream, tmA, tmB, p));   // cluster dims are compiled in
     } else {
         { const int rc2 = ensure_smem_attr((const void*)kern, GEMM_SMEM_BYTES); if (rc2) return rc2; }

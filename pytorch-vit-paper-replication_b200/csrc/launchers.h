@@ -10,6 +10,7 @@ int gemm_launch(int op, int epi, int M, int N, int K, const void* A, long long l
                 int splits, cudaStream_t stream);
 
 void tmap_cache_stats(long long* hits, long long* misses);
+void set_gemm_dynamic(int on);
 
 // LayerNorm fold (gemm_sm100.cu): extra operands of epilogues 7-10
 struct GemmLnArgs {

@@ -85,6 +85,27 @@ def main():
     gathered = [torch.empty_like(acc_w) for _ in range(world)]
     dist.all_gather(gathered, acc_w)
     assert all(torch.equal(gathered[0], t) for t in gathered), "weights diverged after the accumulated step"
+    # the peer-memory all-reduce on its own, against ncclAllReduce on the same values, many calls back to back, with
+    # ranks arriving at different times
+    expect = os.environ.get("B200VIT_DP_ALLREDUCE", "peer")
+    assert (dp.peer is not None) == (expect == "peer" and world <= 8), f"transport: peer={dp.peer is not None}, asked {expect}"
+    if dp.peer is not None:
+        gen = torch.Generator(device=dev).manual_seed(1000 + rank)
+        for it in range(12):
+            b = dp.buckets[it % len(dp.buckets)]
+            b.flat.copy_(torch.randn(b.flat.numel(), device=dev, generator=gen))
+            want = b.flat.clone()
+            dist.all_reduce(want)
+            if it % 3 == rank % 3:
+                torch.cuda._sleep(3_000_000)          # this rank's bucket is late
+            dp.peer.all_reduce(b.flat, b.ready, b.done).wait()
+            err = ((b.flat - want).abs().max() / want.abs().max()).item()
+            assert err < 1e-6, f"rank {rank}: peer all-reduce differs from NCCL by {err} (call {it})"
+            if world == 2:
+                assert torch.equal(b.flat, want)
+            got = [torch.empty_like(b.flat) for _ in range(world)]
+            dist.all_gather(got, b.flat)
+            assert all(torch.equal(got[0], t) for t in got), "ranks hold different sums"
     # LAST (it leaves the gradients in an undefined state): a second synchronised backward without zero_grad() must
     # be refused -- it would reduce the first sum again
     model.zero_grad()
@@ -96,7 +117,8 @@ def main():
         assert "already all-reduced" in str(e), e
     torch.cuda.synchronize()
     if rank == 0:
-        print(f"dp_check ok: world={world} buckets={len(dp.buckets)} worst grad rel err {worst:.2e}", flush=True)
+        print(f"dp_check ok: world={world} buckets={len(dp.buckets)} transport={'peer' if dp.peer is not None else 'nccl'} "
+              f"worst grad rel err {worst:.2e}", flush=True)
     dist.destroy_process_group()
 
 
