@@ -10,7 +10,9 @@ Workload at N=1: BASELINE.json configs[1] -- ViT-B/16, 3-class head, bf16 GEMM o
 batch 256, synthetic 224x224 images, dropout as shipped (0.1 / 0.1 / 0), the notebook's optimizer recipe
 (Adam with coupled L2 0.03 on matrices, warm-up + linear decay stepped per batch, clip at global norm 1) run through
 b200vit.going_modular.engine.train_step. N>1: the same per-GPU batch on every rank (weak scaling) under
-b200vit.dp.DataParallel, gradients summed with NCCL and averaged inside FusedAdam.
+b200vit.dp.DataParallel, gradients summed over NVLink peer memory by the library's own all-reduce kernel (NCCL as
+fallback) and averaged inside FusedAdam; `data_parallel` in the line also times the same steps without the exchange,
+per rank, so the weak-scaling loss splits into "slowest GPU of the box" and "exchange".
 
 A "step" = one optimizer step = one batch through forward, loss, backward, clip, Adam, LR schedule.
   value : images/sec with the batches already resident in HBM (CUDA-event timed, max over ranks)
@@ -172,7 +174,7 @@ def measure_step_kernels(run_steps, n_steps, batch, peaks, classes):
                            "achieved": round(ach, 1), "peak": peak, "unit": unit, "frac": round(ach / peak, 3), "work": note})
     add("attention_fwd_tc_kernel", "b200vit_attention_fwd", attn_fwd_flops, "TFLOP/s", sustained, "tensor",
         "4*B*H*T^2*64 FLOP per layer")
-    add("attention_bwd_tc3_kernel", "b200vit_attention_bwd_bias", 2.5 * attn_fwd_flops, "TFLOP/s", sustained, "tensor",
+    add("attention_bwd_tc4_kernel", "b200vit_attention_bwd_bias", 2.5 * attn_fwd_flops, "TFLOP/s", sustained, "tensor",
         "2.5x the forward (S, dP, dV, dK, dQ)")
     add("layernorm_fwd_kernel", "b200vit_layernorm_fwd", 2 * L * R * D * 6.0, "GB/s", hbm, "hbm",
         "6 B/element: read f32, write bf16 (2 per layer)")
@@ -570,6 +572,25 @@ def main():
     c_calls = _C.call_count - calls0
     barrier()
 
+    # ---- where the weak-scaling loss comes from: the same K steps WITHOUT the gradient exchange (no_sync: every rank steps
+    # on its own gradients -- a diagnostic, the weights diverge, nothing after this uses the model). The engine's
+    # once-per-epoch metric all-reduce at the end lines the ranks up, so every rank measures the SLOWEST rank's time:
+    # what N independent GPUs of this box would give at best. ms_per_step minus it is the cost of the exchange.
+    dp_diag = None
+    if world > 1:
+        barrier()
+        with net.no_sync():
+            engine.train_step(net, [resident[i % n_pool] for i in range(2)], loss_fn, opt, sched, dev)
+            barrier()
+            e0.record()
+            engine.train_step(net, [resident[i % n_pool] for i in range(K_steps)], loss_fn, opt, sched, dev)
+            e1.record()
+            barrier()
+        free_ms = max_over_ranks(e0.elapsed_time(e1)) / K_steps
+        dp_diag = {"transport": "peer" if getattr(net, "peer", None) is not None else "nccl",
+                   "ms_per_step_without_exchange": round(free_ms, 3), "exchange_cost_ms": round(ms_step - free_ms, 3),
+                   "how": "same steps under no_sync (no gradient exchange), slowest rank"}
+
     # ---- the other BASELINE.json configs (every rank takes part) ------------------------------------------------------
     del host, resident
     extra = {}
@@ -645,6 +666,8 @@ def main():
         "final_train_loss": round(train_loss, 4),
         "loss_check": {"finite": True, "band": [0.2, 10.0]},
     }
+    if dp_diag is not None:
+        line["data_parallel"] = dp_diag
     line.update(extra)
     print(json.dumps(line), flush=True)
     if world > 1:
