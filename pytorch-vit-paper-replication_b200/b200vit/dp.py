@@ -85,7 +85,8 @@ class _PeerTransport:
             raise RuntimeError("symmetric memory handle does not describe this process group")
         self.world, self.rank, self.device = world, rank, device
         self.stream = torch.cuda.Stream(device=device)
-        self.ctas = int(os.environ.get("B200VIT_DP_PEER_CTAS", "296"))
+        # twice the SM count: every SM gets a CTA wherever the hardware places them; the surplus ones leave at once
+        self.ctas = int(os.environ.get("B200VIT_DP_PEER_CTAS", 2 * torch.cuda.get_device_properties(device).multi_processor_count))
         self.seq = 0
         import ctypes
         self._flag_table = (ctypes.c_void_p * world)(*self.flag_ptrs)

@@ -38,6 +38,33 @@ def test_gemm_nt_bias(M, N, Kd):
     assert (C.float() - ref).abs().max().item() < 0.05 * ref.abs().max().item() + 1e-2
 
 
+def test_gemm_dynamic_and_static_work_distribution_agree():
+    """b200vit_set_gemm_schedule: work items claimed from the device counter (default) or split statically give
+    bit-identical results (an item is computed the same way whichever cluster takes it), launch after launch -- the
+    counter is put back to zero by every launch."""
+    from b200vit import _C
+    g = torch.Generator().manual_seed(11)
+    M, N, Kd = 12608, 3072, 768                        # 50 x 12 = 600 work items for 74 clusters
+    A = _rand_bf16((M, Kd), g)
+    B = _rand_bf16((N, Kd), g, 0.05)
+    bias = torch.randn(N, generator=g).to(dev())
+    outs = {}
+    try:
+        for mode in (True, False, True):
+            _C.set_gemm_schedule(mode)
+            for rep in range(40):
+                C = torch.zeros((M, N), dtype=torch.bfloat16, device=dev())
+                K.gemm(K.OP_NT, K.EPI_BF16, M, N, Kd, A, Kd, B, Kd, C, N, bias=bias)
+                if mode in outs:
+                    assert torch.equal(C, outs[mode]), f"dynamic={mode}: launch {rep} differs from the first"
+                else:
+                    outs[mode] = C
+    finally:
+        _C.set_gemm_schedule(True)
+    assert torch.equal(outs[True], outs[False])
+    assert rel_err(outs[True], A.float() @ B.float().t() + bias) < 4e-3
+
+
 @pytest.mark.parametrize("M,N,Kd", [(256, 256, 128), (200, 328, 200), (6304, 768, 2304)])
 def test_gemm_nn(M, N, Kd):
     g = torch.Generator().manual_seed(2)
