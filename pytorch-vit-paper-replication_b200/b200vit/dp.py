@@ -92,6 +92,10 @@ class _PeerTransport:
         self._flag_table = (ctypes.c_void_p * world)(*self.flag_ptrs)
         self._ctypes = ctypes
 
+    def make_events(self):
+        """(ready, done) events of one bucket, reused step after step."""
+        return torch.cuda.Event(), torch.cuda.Event()
+
     def all_reduce(self, flat: torch.Tensor, ready: "torch.cuda.Event", done: "torch.cuda.Event") -> _PeerWork:
         from . import _C
         off = flat.data_ptr() - self.arena.data_ptr()
@@ -195,7 +199,7 @@ class DataParallel(nn.Module):
             if self.peer is not None:
                 n = _padded(sum(p.numel() for p in g))
                 b = _Bucket(g, self.peer.arena[off:off + n])
-                b.ready, b.done = torch.cuda.Event(), torch.cuda.Event()
+                b.ready, b.done = self.peer.make_events()
                 off += n
             else:
                 b = _Bucket(g)

@@ -64,16 +64,46 @@ def test_engine_loop_matches_reference_semantics_on_cpu():
     assert set(res) == {"train_loss", "train_acc", "test_loss", "test_acc"} and all(len(v) == 2 for v in res.values())
 
 
-def _dp_worker(rank, world, port, out):
+class _FakeArenaTransport:
+    """Stands in for dp._PeerTransport on CPU: one arena for all buckets (as the symmetric allocation is), the sum done
+    by gloo. Exercises the arena slicing / padding / view logic of DataParallel without a GPU."""
+
+    def __init__(self, floats):
+        self.arena = torch.zeros(floats)
+        self.calls = 0
+
+    def make_events(self):
+        return None, None
+
+    def all_reduce(self, flat, ready, done):
+        assert flat.numel() % 64 == 0 and flat.data_ptr() >= self.arena.data_ptr()
+        assert flat.data_ptr() + flat.numel() * 4 <= self.arena.data_ptr() + self.arena.numel() * 4
+        self.calls += 1
+        return dist.all_reduce(flat, op=dist.ReduceOp.SUM, async_op=True)
+
+
+def _dp_worker(rank, world, port, out, arena=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
+        from b200vit import dp as dpmod
         from b200vit.dp import DataParallel
+        if arena:
+            def fake(self, groups):
+                return _FakeArenaTransport(sum(dpmod._padded(sum(p.numel() for p in g)) for g in groups))
+            DataParallel._make_peer_transport = fake
         torch.manual_seed(100 + rank)                      # different init per rank: broadcast must fix it
         net = nn.Sequential(nn.Linear(10, 32), nn.ReLU(), nn.Linear(32, 32), nn.ReLU(), nn.Linear(32, 4))
         dp = DataParallel(net, bucket_mb=0.002)            # tiny buckets -> several of them
         assert len(dp.buckets) >= 2
+        if arena:       # every bucket is a 256-byte aligned, zero-padded slice of the one arena, back to back
+            off = 0
+            for b in dp.buckets:
+                n = sum(p.numel() for p in b.params)
+                assert b.flat.data_ptr() == dp.peer.arena.data_ptr() + 4 * off and b.flat.numel() == dpmod._padded(n)
+                off += b.flat.numel()
+            assert off == dp.peer.arena.numel()
         g = torch.Generator().manual_seed(7)
         X = torch.randn(8 * world, 10, generator=g)
         y = torch.randint(0, 4, (8 * world,), generator=g)
@@ -116,17 +146,23 @@ def _dp_worker(rank, world, port, out):
         assert abs(l - (world + 1) / 2) < 1e-12 and a == 0.5
         from b200vit import functional as F_
         assert F_._dropout_stream == rank
+        if arena:
+            assert dp.peer.calls >= 2 * len(dp.buckets)
+            for b in dp.buckets:            # the padding behind each bucket's parameters stays zero
+                n = sum(p.numel() for p in b.params)
+                assert float(b.flat[n:].abs().sum()) == 0.0
         out.put((rank, err, same, err2))
     finally:
         dist.destroy_process_group()
 
 
-def test_data_parallel_gloo_world2():
+@pytest.mark.parametrize("arena", [False, True])
+def test_data_parallel_gloo_world2(arena):
     world = 2
     ctx = mp.get_context("spawn")
     out = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_dp_worker, args=(r, world, port, out)) for r in range(world)]
+    procs = [ctx.Process(target=_dp_worker, args=(r, world, port, out, arena)) for r in range(world)]
     for p in procs:
         p.start()
     res = [out.get(timeout=120) for _ in range(world)]
