@@ -254,7 +254,12 @@ class ClockSampler:
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
-        self.index = index
+        # nvidia-smi numbers GPUs without regard to CUDA_VISIBLE_DEVICES: address the device by its UUID
+        self.index = str(index)
+        try:
+            self.index = "GPU-" + str(torch.cuda.get_device_properties(index).uuid)
+        except Exception:
+            pass
         self.proc = None
 
     def start(self):
