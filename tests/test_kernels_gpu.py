@@ -113,6 +113,15 @@ def test_gemm_gelu_and_dgelu():
     K.gemm(K.OP_NN, K.EPI_DGELU, M, N, Kd, G, Kd, W, N, out2, N, bias=colsum, aux=gd, ldaux=N)
     assert torch.equal(out2, out)
     assert rel_err(colsum - 1.0, ((G.float() @ W.float()) * gd.float()).sum(0)) < 2e-3
+    # ragged shape (edge tiles)
+    Mr, Nr, Kr = 328, 200, 136
+    Gr, Wr = _rand_bf16((Mr, Kr), g), _rand_bf16((Kr, Nr), g, 0.08)
+    gdr = _rand_bf16((Mr, Nr), g)
+    outr = torch.empty((Mr, Nr), dtype=torch.bfloat16, device=dev())
+    csr = torch.zeros(Nr, dtype=torch.float32, device=dev())
+    K.gemm(K.OP_NN, K.EPI_DGELU, Mr, Nr, Kr, Gr, Kr, Wr, Nr, outr, Nr, bias=csr, aux=gdr, ldaux=Nr)
+    assert rel_err(outr, (Gr.float() @ Wr.float()) * gdr.float()) < 8e-3
+    assert rel_err(csr, ((Gr.float() @ Wr.float()) * gdr.float()).sum(0)) < 3e-3
     # with dropout: hidden and saved derivative carry the SAME mask, scaled by 1/(1-p); mask == dropout_cast's
     p = 0.25
     gd2, h2 = torch.empty_like(gd), torch.empty_like(h)
